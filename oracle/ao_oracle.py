@@ -1,0 +1,375 @@
+"""CPU oracle for the weight-only quantized linear path (TEST INFRASTRUCTURE ONLY).
+
+This file is a numpy restatement of the reference algorithm.  It is the checker
+for the CUDA kernels; it is never the product.  Only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
+reference`` legs may import it.
+
+Parity status: PINNED.  ``tests/test_oracle_golden.py`` checks every function
+below bit-for-bit against ``tests/golden/*.npz``, which were produced by the
+reference's own Python functions run on CPU in the build container
+(``tests/golden/make_golden.py``; torch 2.11.0).
+
+Conventions
+-----------
+* bf16 values are carried as ``np.float32`` arrays whose values are exactly
+  bf16-representable; ``to_bits``/``from_bits`` convert to the uint16 pattern.
+* The reference runs eager torch ops on bf16 tensors.  Each eager op computes
+  in fp32 ("opmath") and rounds its result to bf16 (round-to-nearest-even).
+  Every function here therefore rounds after every op, exactly where the
+  reference has an op boundary.
+* ``div_mode``: how ``tensor / python_scalar`` is evaluated.
+    - ``"ieee"``  : fp32 IEEE division  (torch CPU eager; the golden vectors)
+    - ``"recip"`` : multiply by the fp32 reciprocal of the scalar (torch CUDA
+      eager: ATen's div_true_kernel_cuda multiplies by 1/b when b is a CPU
+      scalar).  This is what the reference does when it quantizes a model that
+      lives on the GPU, so it is the product kernels' default.
+  ``tensor / tensor`` is IEEE division on both devices.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+F32 = np.float32
+
+
+# --------------------------------------------------------------------------
+# bf16 helpers
+# --------------------------------------------------------------------------
+def bf16_round(x):
+    """fp32 -> nearest-even bf16, returned as fp32 (what ``.to(bfloat16)`` does)."""
+    x = np.ascontiguousarray(x, dtype=F32)
+    u = x.view(np.uint32).astype(np.uint64)
+    bias = ((u >> 16) & 1) + 0x7FFF
+    r = ((u + bias) & 0xFFFF0000).astype(np.uint32)
+    out = r.view(F32).copy()
+    nan = np.isnan(x)
+    if nan.any():
+        out[nan] = np.nan
+    return out.reshape(x.shape)
+
+
+def to_bits(x):
+    """bf16-valued fp32 array -> uint16 bit pattern."""
+    x = np.ascontiguousarray(x, dtype=F32)
+    return (x.view(np.uint32) >> 16).astype(np.uint16).reshape(x.shape)
+
+
+def from_bits(b):
+    """uint16 bf16 bit pattern -> fp32 array."""
+    b = np.ascontiguousarray(b, dtype=np.uint16)
+    return (b.astype(np.uint32) << 16).view(F32).reshape(b.shape)
+
+
+def _div_scalar(x, c, div_mode):
+    if div_mode == "ieee":
+        return bf16_round(x.astype(F32) / F32(c))
+    if div_mode == "recip":
+        inv = F32(1.0) / F32(c)
+        return bf16_round(x.astype(F32) * inv)
+    raise ValueError(div_mode)
+
+
+# --------------------------------------------------------------------------
+# int4 (tinygemm flavour): qparams / quantize / dequantize
+# --------------------------------------------------------------------------
+def choose_qparams_tinygemm(w, group_size, eps=1e-6, div_mode="ieee"):
+    """Reference: torchao/quantization/quant_primitives.py:1238-1306
+    (_choose_qparams_affine_tinygemm, ASYMMETRIC, qmin 0, qmax 15, bf16 qparams).
+
+    w: [N][K] bf16-valued.  Returns (scale, zero) each [N][K/G], bf16-valued.
+    """
+    n, k = w.shape
+    assert k % group_size == 0
+    wg = w.reshape(n, k // group_size, group_size).astype(F32)
+    mn = wg.min(axis=-1)                              # :1287 amin
+    mx = wg.max(axis=-1)                              # :1288 amax
+    d = bf16_round(mx - mn)                           # :1294 (max - min)
+    scale = _div_scalar(d, 15.0, div_mode)            # :1294  / float(qmax-qmin)
+    scale = bf16_round(np.maximum(scale, F32(eps)))   # :1295 clamp(min=eps)
+    t = bf16_round(scale * F32(8.0))                  # :1300 scale * mid_point
+    zero = bf16_round(mn + t)                         # :1300 min + ...
+    return scale, zero
+
+
+def quantize_tinygemm(w, scale, zero, group_size):
+    """Reference: quant_primitives.py:541-573 (_quantize_affine_tinygemm_no_dtype_cast).
+    Returns int32 [N][K] in 0..15."""
+    n, k = w.shape
+    wg = w.reshape(n, k // group_size, group_size).astype(F32)
+    s = scale.reshape(n, -1, 1).astype(F32)
+    z = zero.reshape(n, -1, 1).astype(F32)
+    t = bf16_round(s * F32(8.0))                      # :569 scale * mid_point
+    min_val = bf16_round(z - t)                       # :569 zero - ...
+    a = bf16_round(wg - min_val)                      # :570 input - min_val
+    with np.errstate(divide="ignore", invalid="ignore"):
+        b = bf16_round(a / s)                         # :570 / scale  (tensor/tensor: IEEE)
+    q = np.clip(np.rint(b), 0, 15)                    # :570 round-half-even, clamp
+    return q.astype(np.int32).reshape(n, k)
+
+
+def pack_scales_and_zeros(scale, zero):
+    """Reference: torchao/quantization/utils.py:395-409 -> [K/G][N][2]."""
+    return np.ascontiguousarray(np.stack([scale, zero], axis=-1).transpose(1, 0, 2))
+
+
+def unpack_scales_and_zeros(sz):
+    """Reference: utils.py:412-414 -> scale, zero each [N][K/G]."""
+    t = sz.transpose(1, 0, 2)
+    return np.ascontiguousarray(t[..., 0]), np.ascontiguousarray(t[..., 1])
+
+
+def _bf16_fma_exact(a, b, c):
+    """round_bf16(a*b + c) with ONE rounding (what fma.rn.bf16 does).
+
+    a*b is exact in float64 (a is a small int, b has 8 significant bits).  The
+    float64 sum is exact unless the exponents of the two terms are > ~40 bits
+    apart; those elements are redone with exact rational arithmetic.
+    """
+    a64 = a.astype(np.float64)
+    b64 = b.astype(np.float64)
+    c64 = c.astype(np.float64)
+    p = a64 * b64
+    s = p + c64
+    out = bf16_round(_f64_to_f32_round_odd(s))
+    # exactness check of the float64 addition (TwoSum residual)
+    bb = s - p
+    err = (p - (s - bb)) + (c64 - bb)
+    bad = np.argwhere(err != 0)
+    if bad.size:
+        from fractions import Fraction
+        for idx in map(tuple, bad):
+            exact = Fraction(float(p[idx])) + Fraction(float(c64[idx]))
+            out[idx] = _round_fraction_to_bf16(exact)
+    return out
+
+
+def _f64_to_f32_round_odd(x):
+    """float64 -> float32 with round-to-odd so that a later bf16 RNE rounding
+    equals a single rounding of the float64 value."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    f = x.astype(F32)
+    inexact = f.astype(np.float64) != x
+    u = f.view(np.uint32).copy()
+    # move toward zero if we rounded away, then force the low bit to 1
+    away = inexact & (np.abs(f.astype(np.float64)) > np.abs(x))
+    u[away] -= 1
+    u[inexact] |= 1
+    return u.view(F32).reshape(x.shape)
+
+
+def _round_fraction_to_bf16(fr):
+    from fractions import Fraction
+    if fr == 0:
+        return F32(0.0)
+    sign = -1 if fr < 0 else 1
+    a = abs(fr)
+    import math
+    e = math.floor(math.log2(float(a))) if a > 0 else 0
+    while Fraction(2) ** e > a:
+        e -= 1
+    while Fraction(2) ** (e + 1) <= a:
+        e += 1
+    ulp = Fraction(2) ** (e - 7)
+    qn = a / ulp
+    fl = qn.numerator // qn.denominator
+    rem = qn - fl
+    if rem > Fraction(1, 2) or (rem == Fraction(1, 2) and (fl & 1)):
+        fl += 1
+    return F32(sign * float(fl * ulp))
+
+
+def dequantize_tinygemm(q, scale, zero, group_size):
+    """W'[n][k] = bf16_rn((q-8)*s + z), ONE rounding.
+
+    Reference: tensor_core_tiled_layout.cu:41-117 (q-8 exact via the 0x4300
+    magic + fma.rn.bf16x2) and :194 (__hfma2(v, scale, zero)); python spelling
+    test/test_ops.py:319-336.  Same arithmetic as aten._weight_int4pack_mm's
+    in-register dequant."""
+    n, k = q.shape
+    qg = (q.reshape(n, k // group_size, group_size).astype(F32) - F32(8.0))
+    s = np.broadcast_to(scale.reshape(n, -1, 1).astype(F32), qg.shape)
+    z = np.broadcast_to(zero.reshape(n, -1, 1).astype(F32), qg.shape)
+    return _bf16_fma_exact(qg, s, z).reshape(n, k)
+
+
+def dequantize_affine_tinygemm_2round(q, scale, zero, group_size):
+    """Reference python dequant (quant_primitives.py:939-1031,
+    _dequantize_affine_tinygemm): (q - 8) * scale + zero with a bf16 rounding
+    after the multiply AND after the add.  Used by AQT.dequantize()."""
+    n, k = q.shape
+    qg = q.reshape(n, k // group_size, group_size).astype(F32) - F32(8.0)
+    s = scale.reshape(n, -1, 1).astype(F32)
+    z = zero.reshape(n, -1, 1).astype(F32)
+    return bf16_round(bf16_round(qg * s) + z).reshape(n, k)
+
+
+# --------------------------------------------------------------------------
+# packed layouts
+# --------------------------------------------------------------------------
+def nibble_pair_u8(q):
+    """Reference: tensor_core_tiled_layout.py:276  (q[:, ::2] << 4 | q[:, 1::2]) -> uint8 [N][K/2]."""
+    return ((q[:, ::2] << 4) | q[:, 1::2]).astype(np.uint8)
+
+
+# nibble slot (bit offset / 4) of the i-th of 8 values inside one uint32 word:
+# value order v0..v7 -> slots 0,4,1,5,2,6,3,7 (i.e. slot order v0,v2,v4,v6,v1,v3,v5,v7).
+# Same in-word order as the reference (tensor_core_tiled_layout.cu:201-208); it is
+# what makes "(w >> 4i) & 0x000f000f" yield the bf16x2 pair (v[2i], v[2i+1]).
+_SLOT = np.array([0, 4, 1, 5, 2, 6, 3, 7], dtype=np.uint32)
+
+
+def _pack_words(v):
+    """v: [..., 8] ints in 0..15 -> uint32 words."""
+    v = v.astype(np.uint32)
+    w = np.zeros(v.shape[:-1], dtype=np.uint32)
+    for i in range(8):
+        w |= (v[..., i] & 0xF) << (4 * _SLOT[i])
+    return w
+
+
+def _unpack_words(w):
+    w = w.astype(np.uint32)
+    out = np.zeros(w.shape + (8,), dtype=np.int32)
+    for i in range(8):
+        out[..., i] = (w >> (4 * _SLOT[i])) & 0xF
+    return out
+
+
+def pack_tinygemm(q, inner_k_tiles=8):
+    """Restatement of aten._convert_weight_to_int4pack's output layout, recovered
+    from its inverse kernel, tensor_core_tiled_layout.cu:128-215.
+
+    q int32 [N][K] -> int32 [N/8][K/(ikt*16)][32][ikt/2]."""
+    n, k = q.shape
+    ikt = inner_k_tiles
+    assert n % 8 == 0 and k % (ikt * 16) == 0
+    out = np.zeros((n // 8, k // (ikt * 16), 32, ikt // 2), dtype=np.uint32)
+    t = np.arange(32)
+    row_in_tile = t // 4
+    for j in range(ikt // 2):
+        for ko in range(k // (ikt * 16)):
+            kbase0 = (ko * ikt + 2 * j) * 16                     # .cu:146
+            ks0 = kbase0 + (t % 4) * 2                           # .cu:147
+            ks = np.stack([ks0, ks0 + 1, ks0 + 8, ks0 + 9,       # .cu:148
+                           ks0 + 16, ks0 + 17, ks0 + 24, ks0 + 25], axis=-1)  # .cu:151-153
+            for nt in range(n // 8):
+                rows = nt * 8 + row_in_tile                      # .cu:136
+                vals = q[rows[:, None], ks]                      # [32][8]
+                out[nt, ko, :, j] = _pack_words(vals)
+    return out.view(np.int32)
+
+
+def unpack_tinygemm(packed, inner_k_tiles=8):
+    """torchao::unpack_tensor_core_tiled_layout semantics (tensor_core_tiled_layout.cu:197-215, :320-368)."""
+    p = packed.view(np.uint32)
+    ikt = inner_k_tiles
+    nt_, ko_, _, half = p.shape
+    assert half == ikt // 2
+    n, k = nt_ * 8, ko_ * ikt * 16
+    q = np.zeros((n, k), dtype=np.int32)
+    t = np.arange(32)
+    for j in range(half):
+        for ko in range(ko_):
+            kbase0 = (ko * ikt + 2 * j) * 16
+            ks0 = kbase0 + (t % 4) * 2
+            ks = np.stack([ks0, ks0 + 1, ks0 + 8, ks0 + 9,
+                           ks0 + 16, ks0 + 17, ks0 + 24, ks0 + 25], axis=-1)
+            for nt in range(nt_):
+                rows = nt * 8 + t // 4
+                q[rows[:, None], ks] = _unpack_words(p[nt, ko, :, j])
+    return q
+
+
+# ---- the B200 strip layout (this build's own; see DESIGN.md "HBM layout") ----
+# packed uint32 [N/16][K/64][32][4]; tile (strip, kt), lane l=(g=l>>2, c=l&3), word j:
+#   row = 16*strip + g + 8*(j&1);  k0 = 64*kt + 32*(j>>1) + 8*c;  word holds k0..k0+7.
+def pack_b200(q):
+    n, k = q.shape
+    assert n % 16 == 0 and k % 64 == 0
+    lane = np.arange(32)
+    g, c = lane >> 2, lane & 3
+    out = np.zeros((n // 16, k // 64, 32, 4), dtype=np.uint32)
+    q5 = q.reshape(n // 16, 16, k // 64, 8, 8)       # [strip][row][kt][chunk][8]
+    for j in range(4):
+        rows = g + 8 * (j & 1)
+        chunks = c + 4 * (j >> 1)
+        vals = q5[:, rows, :, chunks, :]              # -> [32][strip][kt][8]
+        out[:, :, :, j] = _pack_words(vals).transpose(1, 2, 0)
+    return out.view(np.int32)
+
+
+def unpack_b200(packed):
+    p = packed.view(np.uint32)
+    s_, kt_, _, _ = p.shape
+    n, k = s_ * 16, kt_ * 64
+    lane = np.arange(32)
+    g, c = lane >> 2, lane & 3
+    q5 = np.zeros((s_, 16, kt_, 8, 8), dtype=np.int32)
+    for j in range(4):
+        rows = g + 8 * (j & 1)
+        chunks = c + 4 * (j >> 1)
+        vals = _unpack_words(p[:, :, :, j])           # [strip][kt][32][8]
+        q5[:, rows, :, chunks, :] = vals.transpose(2, 0, 1, 3)
+    return q5.reshape(n, k)
+
+
+# --------------------------------------------------------------------------
+# linear
+# --------------------------------------------------------------------------
+def int4_weight_only_mm(x, q, scale, zero, group_size):
+    """y[m][n] = bf16( sum_k fp32(x[m][k] * W'[n][k]) ), W' = dequantize_tinygemm.
+    Semantics of aten._weight_int4pack_mm; summation order is
+    unspecified there, here it is float64 (tolerance-compared, not bit-compared)."""
+    wd = dequantize_tinygemm(q, scale, zero, group_size).astype(np.float64)
+    return bf16_round((x.astype(np.float64) @ wd.T).astype(F32))
+
+
+# --------------------------------------------------------------------------
+# int8 weight-only
+# --------------------------------------------------------------------------
+def choose_qparams_int8_symmetric(w, eps=float(np.finfo(np.float32).eps), div_mode="ieee"):
+    """Reference: quant_primitives.py:1537-1565 (SYMMETRIC, int8 -128..127, per row,
+    scale dtype = input dtype bf16); caller quant_api.py:1223-1240.
+    Returns scale [N] bf16-valued (zero_point is int64 zeros)."""
+    wf = w.astype(F32)
+    mn = wf.min(axis=-1)
+    mx = wf.max(axis=-1)
+    mn_neg = np.minimum(mn, F32(0))                    # :1540
+    mx_pos = np.maximum(mx, F32(0))                    # :1541
+    amax = np.maximum(-mn_neg, mx_pos)                 # :1549 (negation exact)
+    scale = _div_scalar(amax, 127.5, div_mode)         # :1550  / (255/2)
+    scale = bf16_round(np.maximum(scale, F32(eps)))    # :1565 clamp(min=eps)
+    return scale
+
+
+def quantize_int8_symmetric(w, scale):
+    """Reference: quant_primitives.py:453-456: clamp(round(w * (1.0/scale)) + zp, -128, 127),
+    zp = 0; `1.0/scale` and the product each round to bf16."""
+    s = scale.reshape(-1, 1).astype(F32)
+    inv = bf16_round(F32(1.0) / s)
+    p = bf16_round(w.astype(F32) * inv)
+    q = np.clip(np.rint(p), -128, 127)
+    return q.astype(np.int8)
+
+
+def int8_weight_only_mm(x, q, scale):
+    """Reference: plain_layout.py:250-266:  y = bf16(bf16(x @ q^T) * scale)."""
+    m = bf16_round((x.astype(np.float64) @ q.astype(np.float64).T).astype(F32))
+    return bf16_round(m * scale.reshape(1, -1).astype(F32))
+
+
+def dequantize_int8(q, scale):
+    """Reference: quant_primitives.py:828-833 with zp=0: bf16(q) * scale."""
+    return bf16_round(q.astype(F32) * scale.reshape(-1, 1).astype(F32))
+
+
+def sqnr_db(ref, x):
+    """Reference: torchao/quantization/utils.py:51-55 compute_error."""
+    ref = ref.astype(np.float64)
+    x = x.astype(np.float64)
+    ps = np.linalg.norm(ref)
+    pn = np.linalg.norm(ref - x)
+    if pn == 0:
+        return float("inf")
+    return float(20 * np.log10(ps / pn))
