@@ -1,0 +1,142 @@
+/*
+ * ao_b200.h — C ABI of libao_b200.so: B200 (sm_100a) kernels for torchao's
+ * weight-only quantized linear path.
+ *
+ * Boundary rules (mirror SURVEY.md §8(b)):
+ *   - plain pointers + sizes + cudaStream_t (passed as void*); no torch / ATen types;
+ *   - every pointer is a DEVICE pointer on the current CUDA device unless noted;
+ *   - the library never allocates, frees, synchronises or retains pointers: all
+ *     outputs and workspaces are caller-provided, every launch goes to `stream`,
+ *     so every entry point is CUDA-graph-capturable and re-entrant;
+ *   - return value: 0 = ok, otherwise an AO_B200_ERR_* code (never throws/aborts).
+ *     ao_b200_error_string() turns a code into text for the host wrapper's
+ *     RuntimeError (the reference raises c10::Error from TORCH_CHECK,
+ *     torchao/csrc/cuda/tensor_core_tiled_layout/tensor_core_tiled_layout.cu:236-254).
+ *
+ * bf16 tensors are passed as `const void*` to 2-byte elements, row-major.
+ *
+ * HBM layouts
+ *   "strip" layout (this library's int4 weight format), uint32 [Np/16][Kp/64][32][4]:
+ *       tile (strip s, k-tile t) = 16 rows x 64 k = 512 contiguous bytes;
+ *       lane l = (g = l>>2, c = l&3) owns the 16 bytes at word index ((s*Kp/64+t)*32+l)*4;
+ *       word j of the lane: row = 16 s + g + 8 (j&1),  k0 = 64 t + 32 (j>>1) + 8 c,
+ *       and holds k0..k0+7 in nibble slots [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7]
+ *       (slot i = bits 4i..4i+3).  Np % 16 == 0, Kp % 64 == 0.
+ *   scale_and_zero: bf16 [Kp/G][Np][2] = (scale, zero) — identical to the reference's
+ *       pack_tinygemm_scales_and_zeros (torchao/quantization/utils.py:395-409).
+ *   "tinygemm" layout: int32 [N/8][K/(ikt*16)][32][ikt/2], the output format of
+ *       aten._convert_weight_to_int4pack (tensor_core_tiled_layout.cu:128-215).
+ */
+#ifndef AO_B200_H_
+#define AO_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define AO_B200_API __attribute__((visibility("default")))
+#else
+#define AO_B200_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  AO_B200_OK = 0,
+  AO_B200_ERR_INVALID_ARG = 1,   /* null pointer, bad shape, misaligned pointer */
+  AO_B200_ERR_UNSUPPORTED = 2,   /* group size / M / arch not supported        */
+  AO_B200_ERR_CUDA = 3,          /* a CUDA launch failed (cudaGetLastError)    */
+  AO_B200_ERR_WORKSPACE = 4      /* caller-provided workspace too small        */
+};
+
+/* how `tensor / python_scalar` is evaluated when restating the reference's eager ops */
+enum {
+  AO_B200_DIV_IEEE = 0,  /* fp32 IEEE division      (torch CPU eager)               */
+  AO_B200_DIV_RECIP = 1  /* x * (1.0f / c) in fp32  (torch CUDA eager; the default) */
+};
+
+AO_B200_API const char* ao_b200_error_string(int code);
+AO_B200_API int ao_b200_abi_version(void);
+
+/* ---------------------------------------------------------------- int4: quantize ---- */
+
+/* Fused replacement for TensorCoreTiledLayout.pre_process (zero pad) +
+ * _choose_qparams_affine_tinygemm (quant_primitives.py:1238-1306) +
+ * _quantize_affine_tinygemm (quant_primitives.py:462-573) +
+ * TensorCoreTiledAQTTensorImpl.from_plain (tensor_core_tiled_layout.py:262-307):
+ * one pass over W.  w: bf16 [N][K] with row stride ldw (elements, % 8 == 0).
+ * Rows >= N / columns >= K of the padded [Np][Kp] problem read as zero.
+ * Outputs: packed (strip layout, Np x Kp), scale_and_zero bf16 [Kp/G][Np][2].
+ * G in {32,64,128,256}; K % G == 0; Kp % max(G,64) == 0; Np % 16 == 0. */
+AO_B200_API int ao_b200_int4_quantize_pack(const void* w, int64_t N, int64_t K, int64_t ldw,
+                               int64_t Np, int64_t Kp, int group_size, float eps, int div_mode,
+                               void* packed, void* scale_and_zero, void* stream);
+
+/* _choose_qparams_affine_tinygemm alone: scale, zero bf16 [N][K/G]. */
+AO_B200_API int ao_b200_int4_choose_qparams(const void* w, int64_t N, int64_t K, int64_t ldw, int group_size,
+                                float eps, int div_mode, void* scale, void* zero, void* stream);
+
+/* _quantize_affine_tinygemm alone: q int32 [N][K] in 0..15 from given bf16 scale/zero [N][K/G]. */
+AO_B200_API int ao_b200_int4_quantize(const void* w, int64_t N, int64_t K, int64_t ldw, int group_size,
+                          const void* scale, const void* zero, int32_t* q, void* stream);
+
+/* ---------------------------------------------------------------- int4: layouts ----- */
+
+/* from_plain: q int32 [N][K] (values 0..15; rows>=N / cols>=K pad with `pad_value`) -> strip layout. */
+AO_B200_API int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp,
+                      int pad_value, void* packed, void* stream);
+/* strip layout -> int32 [Np][Kp]. */
+AO_B200_API int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, int32_t* q, void* stream);
+/* strip layout + scale_and_zero -> bf16 [Np][Kp], W' = bf16_rn((q-8)*s + z) (single rounding,
+ * the dequant of aten._weight_int4pack_mm; tensor_core_tiled_layout.cu:41-117,194). */
+AO_B200_API int ao_b200_int4_dequant(const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
+                         int group_size, void* out, void* stream);
+
+/* torchao::unpack_tensor_core_tiled_layout (torchao/ops.py:255-296, .cu:320-368):
+ * tinygemm layout -> int32 [N][K]. inner_k_tiles in {2,4,8}. */
+AO_B200_API int ao_b200_tinygemm_unpack(const int32_t* packed, int64_t N, int64_t K, int inner_k_tiles,
+                            int32_t* q, void* stream);
+/* torchao::dequantize_tensor_core_tiled_layout (ops.py:299-377, .cu:223-318). */
+AO_B200_API int ao_b200_tinygemm_dequant(const int32_t* packed, const void* scale_and_zero, int64_t N, int64_t K,
+                             int group_size, int inner_k_tiles, void* out, void* stream);
+/* inverse of the above unpack == aten._convert_weight_to_int4pack on already-paired nibbles:
+ * q int32 [N][K] -> tinygemm layout (for interchange with reference-packed checkpoints). */
+AO_B200_API int ao_b200_tinygemm_pack(const int32_t* q, int64_t N, int64_t K, int inner_k_tiles,
+                          int32_t* packed, void* stream);
+
+/* ---------------------------------------------------------------- int4: linear ------ */
+
+/* Replacement for aten._weight_int4pack_mm(x, packed, G, scale_and_zero)
+ * (call site tensor_core_tiled_layout.py:104):
+ *   y[m][n] = bf16( sum_k fp32( x[m][k] * W'[n][k] ) ),  n < N_out.
+ * x: bf16 [M][Kx] row stride ldx (Kx <= Kp, Kx % 8 == 0; k >= Kx reads as zero — no
+ * host-side F.pad of the activation); y: bf16 [M][N_out] row stride ldy.
+ * M <= 16 -> HBM-bound split-K tensor-core GEMV; larger M -> tcgen05 GEMM.
+ * workspace: ao_b200_int4_mm_workspace_bytes(...) bytes, zero-initialised once by the
+ * caller (the kernels leave it zeroed on exit); may be NULL when that returns 0. */
+AO_B200_API int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp);
+AO_B200_API int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx,
+                    const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
+                    int group_size, void* y, int64_t N_out, int64_t ldy,
+                    void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- int8 -------------- */
+
+/* choose_qparams_affine(SYMMETRIC, int8, block (1,K), eps=fp32 eps) + quantize_affine
+ * (quant_primitives.py:1537-1565, :398-459; caller quant_api.py:1223-1240).
+ * w bf16 [N][K] -> q int8 [N][K] (plain, row-major: PlainAQTTensorImpl.int_data),
+ * scale bf16 [N].  zero_point is identically 0. */
+AO_B200_API int ao_b200_int8_quantize(const void* w, int64_t N, int64_t K, int64_t ldw, float eps, int div_mode,
+                          int8_t* q, void* scale, void* stream);
+
+/* Replacement for _linear_fp_act_int8_weight_impl (plain_layout.py:250-266):
+ *   y = bf16( bf16( x @ q^T ) * scale ).   x bf16 [M][K] (ldx), q int8 [N][K], scale bf16 [N]. */
+AO_B200_API int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx,
+                    const int8_t* q, const void* scale, int64_t N,
+                    void* y, int64_t ldy, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AO_B200_H_ */

@@ -1,0 +1,58 @@
+"""ctypes binding of libao_b200.so (include/ao_b200.h).
+
+The product path has NO fallback: if the library is missing or a call fails, this raises.
+Build with ``python -m torchao_fork_b200.build`` (nvcc, sm_100a)."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libao_b200.so")
+
+_vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+
+# name -> argtypes (all return int unless listed in _RESTYPES)
+SIGNATURES = {
+    "ao_b200_error_string": [_i32],
+    "ao_b200_abi_version": [],
+    "ao_b200_int4_quantize_pack": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _vp],
+    "ao_b200_int4_choose_qparams": [_vp, _i64, _i64, _i64, _i32, _f32, _i32, _vp, _vp, _vp],
+    "ao_b200_int4_quantize": [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _vp],
+    "ao_b200_int4_pack": [_vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp],
+    "ao_b200_int4_unpack": [_vp, _i64, _i64, _vp, _vp],
+    "ao_b200_int4_dequant": [_vp, _vp, _i64, _i64, _i32, _vp, _vp],
+    "ao_b200_tinygemm_unpack": [_vp, _i64, _i64, _i32, _vp, _vp],
+    "ao_b200_tinygemm_dequant": [_vp, _vp, _i64, _i64, _i32, _i32, _vp, _vp],
+    "ao_b200_tinygemm_pack": [_vp, _i64, _i64, _i32, _vp, _vp],
+    "ao_b200_int4_mm_workspace_bytes": [_i64, _i64, _i64],
+    "ao_b200_int4_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _i64, _i64, _vp, _i64, _vp],
+    "ao_b200_int8_quantize": [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp],
+    "ao_b200_int8_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp],
+}
+_RESTYPES = {"ao_b200_error_string": ctypes.c_char_p, "ao_b200_int4_mm_workspace_bytes": _i64}
+
+DIV_IEEE, DIV_RECIP = 0, 1
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: the B200 CUDA library is not built "
+                "(python -m torchao_fork_b200.build). There is no fallback path."
+            )
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the symbol is not exported
+            fn.argtypes = argtypes
+            fn.restype = _RESTYPES.get(name, _i32)
+        _lib = handle
+    return _lib
+
+
+def check(code, what):
+    if code != 0:
+        msg = lib().ao_b200_error_string(code).decode()
+        raise RuntimeError(f"libao_b200: {what} failed: {msg} (code {code})")

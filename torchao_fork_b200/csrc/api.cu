@@ -1,0 +1,65 @@
+// C-ABI entry points that dispatch between kernels + misc.
+#include "common.cuh"
+
+namespace ao {
+int int4_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+              int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, cudaStream_t s);
+int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
+              void* y, int64_t ldy, cudaStream_t s);
+}  // namespace ao
+
+extern "C" const char* ao_b200_error_string(int code) {
+  switch (code) {
+    case AO_B200_OK: return "ok";
+    case AO_B200_ERR_INVALID_ARG: return "invalid argument (null/misaligned pointer or bad shape)";
+    case AO_B200_ERR_UNSUPPORTED: return "unsupported configuration";
+    case AO_B200_ERR_CUDA: return "CUDA launch failed";
+    case AO_B200_ERR_WORKSPACE: return "workspace too small";
+  }
+  return "unknown error";
+}
+
+extern "C" int ao_b200_abi_version(void) { return 1; }
+
+extern "C" int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
+  (void)M; (void)Np; (void)Kp;
+  return 0;
+}
+
+extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
+                               const void* scale_and_zero, int64_t Np, int64_t Kp, int group_size, void* y,
+                               int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, void* stream) {
+  (void)workspace; (void)workspace_bytes;
+  AO_CHECK_ARG(x && packed && scale_and_zero && y);
+  AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
+  AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx && ldy >= N_out);
+  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 4) && ao_aligned(y, 2));
+  if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
+  AO_CHECK_ARG(Kp % group_size == 0);
+  auto s = static_cast<cudaStream_t>(stream);
+  auto xb = static_cast<const __nv_bfloat16*>(x);
+  auto yb = static_cast<__nv_bfloat16*>(y);
+  for (int64_t m0 = 0; m0 < M; m0 += 16) {
+    const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
+    int e = ao::int4_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
+                          N_out, ldy, s);
+    if (e) return e;
+  }
+  return AO_B200_OK;
+}
+
+extern "C" int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale,
+                               int64_t N, void* y, int64_t ldy, void* stream) {
+  AO_CHECK_ARG(x && q && scale && y && M > 0 && N > 0 && K > 0);
+  AO_CHECK_ARG(ldx % 8 == 0 && ldx >= K && ldy >= N && ao_aligned(x, 16) && ao_aligned(q, 16));
+  if (K % 16 != 0) return AO_B200_ERR_UNSUPPORTED;
+  auto s = static_cast<cudaStream_t>(stream);
+  auto xb = static_cast<const __nv_bfloat16*>(x);
+  auto yb = static_cast<__nv_bfloat16*>(y);
+  for (int64_t m0 = 0; m0 < M; m0 += 16) {
+    const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
+    int e = ao::int8_gemv(xb + m0 * ldx, mc, K, ldx, q, scale, N, yb + m0 * ldy, ldy, s);
+    if (e) return e;
+  }
+  return AO_B200_OK;
+}

@@ -1,0 +1,85 @@
+// Shared device helpers for libao_b200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ao_b200.h"
+
+#define AO_CHECK_ARG(cond) \
+  do {                     \
+    if (!(cond)) return AO_B200_ERR_INVALID_ARG; \
+  } while (0)
+
+static inline int ao_launch_status() {
+  return cudaGetLastError() == cudaSuccess ? AO_B200_OK : AO_B200_ERR_CUDA;
+}
+
+static inline bool ao_aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+namespace ao {
+
+constexpr int kNumSMs = 148;
+
+// fp32 -> bf16 (nearest even) -> fp32: the rounding every torch eager op on a bf16 tensor applies.
+__device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+__device__ __forceinline__ float bf16_bits_to_float(uint32_t b) { return __uint_as_float(b << 16); }
+__device__ __forceinline__ uint32_t float_to_bf16_bits(float x) {
+  return static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(x)));
+}
+
+// 8 bf16 (one uint4) -> 8 floats
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  const uint32_t r[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(r[i] << 16);
+    f[2 * i + 1] = __uint_as_float(r[i] & 0xFFFF0000u);
+  }
+}
+
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+// One packed word (8 nibbles, slot order k0,k2,k4,k6,k1,k3,k5,k7) -> 4 bf16x2 registers
+// out[i] = ( W'[k0+2i], W'[k0+2i+1] ),  W' = bf16_rn((q-8)*s + z)   [single rounding].
+// Same arithmetic as the reference's convert_i4x8_to_bf16x2x4 + __hfma2
+// (tensor_core_tiled_layout.cu:41-117,194): (q | 0x4300) is the bf16 128+q, one exact
+// bf16 fma with (1, -136) gives q-8, a second bf16 fma applies scale and zero.
+__device__ __forceinline__ void dequant_word(uint32_t w, uint32_t s2, uint32_t z2, uint32_t (&out)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint32_t h;
+    const uint32_t t = w >> (4 * i);
+    asm("lop3.b32 %0, %1, 0x000f000f, 0x43004300, 0xea;" : "=r"(h) : "r"(t));  // (t & m) | magic
+    h = fma_bf16x2(h, 0x3F803F80u, 0xC308C308u);                               // -> q - 8
+    out[i] = fma_bf16x2(h, s2, z2);
+  }
+}
+
+// D(16x8, f32) += A(16x16, bf16, row) * B(16x8, bf16, col)
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                               uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// nibble slot of value i (0..7) inside a word
+__host__ __device__ __forceinline__ constexpr int nib_slot(int i) { return (i & 1) * 4 + (i >> 1); }
+
+}  // namespace ao

@@ -1,0 +1,425 @@
+"""torch.library registration of the B200 kernels under the reference's `torchao` namespace.
+
+Mirrors torchao/ops.py: `lib = torch.library.Library("torchao", "FRAGMENT")`, `lib.define(schema)`
+(ops.py:12-21), fake/meta impls via `torch.library.register_fake` (ops.py:73-77, 274-296, 328-377);
+the CUDA impls, which in the reference are `TORCH_LIBRARY_IMPL(torchao, CUDA, m)` in C++
+(tensor_core_tiled_layout.cu:370-374), are Python functions that pass raw device pointers and the
+current CUDA stream to the C ABI of libao_b200.so (include/ao_b200.h).  There is no CPU impl.
+"""
+from typing import Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+
+lib = torch.library.Library("torchao", "FRAGMENT")
+
+_SCHEMAS = {
+    # kept verbatim from the reference (ops.py:16-21)
+    "unpack_tensor_core_tiled_layout": "(Tensor packed_w, int inner_k_tiles) -> Tensor",
+    "dequantize_tensor_core_tiled_layout": "(Tensor packed_w, Tensor scales_and_zeros, int group_size, int inner_k_tiles) -> Tensor",
+    # new ops of the B200 path
+    "b200_int4_quantize_pack": "(Tensor w, int group_size, float eps, bool cuda_div_semantics) -> (Tensor, Tensor)",
+    "b200_int4_choose_qparams": "(Tensor w, int group_size, float eps, bool cuda_div_semantics) -> (Tensor, Tensor)",
+    "b200_int4_quantize": "(Tensor w, Tensor scale, Tensor zero, int group_size) -> Tensor",
+    "b200_int4_pack": "(Tensor int_data) -> Tensor",
+    "b200_int4_unpack": "(Tensor packed_w) -> Tensor",
+    "b200_int4_dequantize": "(Tensor packed_w, Tensor scales_and_zeros, int group_size) -> Tensor",
+    "b200_tinygemm_pack": "(Tensor int_data, int inner_k_tiles) -> Tensor",
+    "b200_int4_weight_only_mm": "(Tensor x, Tensor packed_w, int group_size, Tensor scales_and_zeros, int out_features) -> Tensor",
+    "b200_int8_quantize": "(Tensor w, float eps, bool cuda_div_semantics) -> (Tensor, Tensor)",
+    "b200_int8_weight_only_mm": "(Tensor x, Tensor int_data, Tensor scale) -> Tensor",
+}
+
+
+def _defined(name):
+    try:
+        getattr(torch.ops.torchao, name)
+        return True
+    except (AttributeError, RuntimeError):
+        return False
+
+
+for _name, _schema in _SCHEMAS.items():
+    # if the reference's torchao/ops.py was imported first its two schemas already exist
+    if not _defined(_name):
+        lib.define(_name + _schema)
+
+
+def register_custom_op(name):
+    def decorator(func):
+        return torch.library.register_fake(f"{name}")(func)
+
+    return decorator
+
+
+def _impl_cuda(name):
+    def decorator(func):
+        lib.impl(name, func, "CUDA")
+        return func
+
+    return decorator
+
+
+def _stream(t: Tensor):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _round_up(a, b):
+    return (a + b - 1) // b * b
+
+
+def padded_int4_shape(n: int, k: int, group_size: int) -> Tuple[int, int]:
+    """Strip layout needs N % 16 == 0 and K % max(G, 64) == 0 (the reference pads to N % 8, K % 1024,
+    tensor_core_tiled_layout.py:127-135; padding only ever adds whole all-zero groups)."""
+    return _round_up(n, 16), _round_up(k, max(group_size, 64))
+
+
+def _check_cuda_bf16(t, what):
+    torch._check(t.is_cuda, lambda: f"{what} must be a CUDA tensor (the B200 path has no CPU fallback)")
+    torch._check(t.dtype is torch.bfloat16, lambda: f"{what} must be bfloat16, got {t.dtype}")
+
+
+def _check_group(group_size):
+    torch._check(group_size in (32, 64, 128, 256), lambda: "qGroupSize must be 32, 64, 128, or 256")
+
+
+# ------------------------------------------------------------------ reference-schema ops
+def unpack_tensor_core_tiled_layout(packed_w: Tensor, inner_k_tiles: int) -> Tensor:
+    """Inverse of aten._convert_weight_to_int4pack: (N/8, K/(ikt*16), 32, ikt/2) int32 -> (N, K) int32.
+    Reference wrapper: torchao/ops.py:255-272."""
+    return torch.ops.torchao.unpack_tensor_core_tiled_layout.default(packed_w=packed_w, inner_k_tiles=inner_k_tiles)
+
+
+def _tinygemm_shape_checks(packed_w, inner_k_tiles):
+    torch._check(packed_w.dim() == 4, lambda: f"packed weight should be a 4d tensor, got {packed_w.dim()}D")
+    torch._check(packed_w.dtype is torch.int32, lambda: f"weight must be INT32, got {packed_w.dtype}")
+    torch._check(inner_k_tiles in (2, 4, 8), lambda: "inner_k_tiles must be 2, 4, or 8")
+    torch._check(packed_w.size(2) == 32, lambda: "packed weight must have 32 at dim 2")
+    torch._check(packed_w.size(3) == inner_k_tiles // 2, lambda: "packed weight must have inner_k_tiles/2 at dim 3")
+    return packed_w.size(0) * 8, packed_w.size(1) * inner_k_tiles * 16
+
+
+@register_custom_op("torchao::unpack_tensor_core_tiled_layout")
+def _(packed_w: Tensor, inner_k_tiles: int) -> Tensor:
+    n, k = _tinygemm_shape_checks(packed_w, inner_k_tiles)
+    return torch.empty((n, k), dtype=torch.int32, device=packed_w.device)
+
+
+@_impl_cuda("unpack_tensor_core_tiled_layout")
+def _unpack_tinygemm_cuda(packed_w: Tensor, inner_k_tiles: int) -> Tensor:
+    n, k = _tinygemm_shape_checks(packed_w, inner_k_tiles)
+    torch._check(packed_w.is_contiguous(), lambda: "packed weight must be contiguous")
+    out = torch.empty((n, k), dtype=torch.int32, device=packed_w.device)
+    with torch.cuda.device(packed_w.device):
+        _lib.check(_lib.lib().ao_b200_tinygemm_unpack(packed_w.data_ptr(), n, k, inner_k_tiles, out.data_ptr(),
+                                                      _stream(packed_w)), "tinygemm_unpack")
+    return out
+
+
+def dequantize_tensor_core_tiled_layout(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int,
+                                        inner_k_tiles: int) -> Tensor:
+    """tinygemm-packed int4 + (K/G, N, 2) bf16 scales_and_zeros -> (N, K) bf16, with the single-rounding
+    bf16 fma dequant of aten._weight_int4pack_mm.  Reference wrapper: torchao/ops.py:299-325."""
+    return torch.ops.torchao.dequantize_tensor_core_tiled_layout.default(packed_w, scales_and_zeros, group_size,
+                                                                         inner_k_tiles)
+
+
+def _sz_checks(scales_and_zeros, n, k, group_size):
+    torch._check(scales_and_zeros.dtype is torch.bfloat16, lambda: "scales_and_zeros must be bfloat16")
+    torch._check(scales_and_zeros.dim() == 3, lambda: f"scales_and_zeros must be 3D, got {scales_and_zeros.dim()}")
+    _check_group(group_size)
+    torch._check(scales_and_zeros.size(0) == k // group_size, lambda: "scales_and_zeros must have K // qGroupSize at dim 0")
+    torch._check(scales_and_zeros.size(1) == n, lambda: "scales_and_zeros must have N at dim 1")
+    torch._check(scales_and_zeros.size(2) == 2, lambda: "scales_and_zeros must have 2 at dim 2")
+
+
+@register_custom_op("torchao::dequantize_tensor_core_tiled_layout")
+def _(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int, inner_k_tiles: int) -> Tensor:
+    n, k = _tinygemm_shape_checks(packed_w, inner_k_tiles)
+    _sz_checks(scales_and_zeros, n, k, group_size)
+    return torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
+
+
+@_impl_cuda("dequantize_tensor_core_tiled_layout")
+def _dequant_tinygemm_cuda(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int, inner_k_tiles: int) -> Tensor:
+    n, k = _tinygemm_shape_checks(packed_w, inner_k_tiles)
+    _sz_checks(scales_and_zeros, n, k, group_size)
+    torch._check(packed_w.is_contiguous() and scales_and_zeros.is_contiguous(), lambda: "inputs must be contiguous")
+    out = torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
+    with torch.cuda.device(packed_w.device):
+        _lib.check(_lib.lib().ao_b200_tinygemm_dequant(packed_w.data_ptr(), scales_and_zeros.data_ptr(), n, k,
+                                                       group_size, inner_k_tiles, out.data_ptr(), _stream(packed_w)),
+                   "tinygemm_dequant")
+    return out
+
+
+# ------------------------------------------------------------------ B200 int4 ops
+def _w_checks(w, group_size):
+    torch._check(w.dim() == 2, lambda: f"weight must be 2-D, got {w.dim()}D")
+    _check_cuda_bf16(w, "weight")
+    _check_group(group_size)
+    torch._check(w.size(1) % group_size == 0, lambda: f"in_features {w.size(1)} not divisible by group_size {group_size}")
+
+
+def _rows(w):
+    """(tensor, leading dimension) for a 2-D bf16 tensor whose rows are contiguous and 16-byte aligned."""
+    if w.stride(1) != 1 or w.stride(0) % 8 != 0 or w.stride(0) < w.size(1) or w.data_ptr() % 16 != 0:
+        w = w.contiguous()
+        if w.stride(0) % 8 != 0:
+            w = torch.nn.functional.pad(w, (0, (-w.size(1)) % 8))[:, : w.size(1)]
+    return w, w.stride(0)
+
+
+@register_custom_op("torchao::b200_int4_quantize_pack")
+def _(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
+    _check_group(group_size)
+    torch._check(w.dim() == 2, lambda: "weight must be 2-D")
+    np_, kp = padded_int4_shape(w.size(0), w.size(1), group_size)
+    return (torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device),
+            torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device))
+
+
+@_impl_cuda("b200_int4_quantize_pack")
+def _int4_quantize_pack_cuda(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
+    _w_checks(w, group_size)
+    n, k = w.shape
+    np_, kp = padded_int4_shape(n, k, group_size)
+    w, ldw = _rows(w)
+    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device)
+    sz = torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.lib().ao_b200_int4_quantize_pack(
+            w.data_ptr(), n, k, ldw, np_, kp, group_size, eps,
+            _lib.DIV_RECIP if cuda_div_semantics else _lib.DIV_IEEE,
+            packed.data_ptr(), sz.data_ptr(), _stream(w)), "int4_quantize_pack")
+    return packed, sz
+
+
+@register_custom_op("torchao::b200_int4_choose_qparams")
+def _(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
+    shape = (w.size(0), w.size(1) // group_size)
+    return (torch.empty(shape, dtype=torch.bfloat16, device=w.device),
+            torch.empty(shape, dtype=torch.bfloat16, device=w.device))
+
+
+@_impl_cuda("b200_int4_choose_qparams")
+def _int4_choose_qparams_cuda(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
+    torch._check(w.dim() == 2 and w.size(1) % group_size == 0, lambda: "bad weight shape for group_size")
+    _check_cuda_bf16(w, "weight")
+    w = w.contiguous()
+    n, k = w.shape
+    scale = torch.empty((n, k // group_size), dtype=torch.bfloat16, device=w.device)
+    zero = torch.empty_like(scale)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.lib().ao_b200_int4_choose_qparams(
+            w.data_ptr(), n, k, k, group_size, eps, _lib.DIV_RECIP if cuda_div_semantics else _lib.DIV_IEEE,
+            scale.data_ptr(), zero.data_ptr(), _stream(w)), "int4_choose_qparams")
+    return scale, zero
+
+
+@register_custom_op("torchao::b200_int4_quantize")
+def _(w: Tensor, scale: Tensor, zero: Tensor, group_size: int):
+    return torch.empty(w.shape, dtype=torch.int32, device=w.device)
+
+
+@_impl_cuda("b200_int4_quantize")
+def _int4_quantize_cuda(w: Tensor, scale: Tensor, zero: Tensor, group_size: int):
+    torch._check(w.dim() == 2 and w.size(1) % group_size == 0, lambda: "bad weight shape for group_size")
+    _check_cuda_bf16(w, "weight")
+    _check_cuda_bf16(scale, "scale")
+    _check_cuda_bf16(zero, "zero_point")
+    n, k = w.shape
+    torch._check(scale.numel() == n * (k // group_size) and zero.numel() == scale.numel(), lambda: "qparam size mismatch")
+    w, scale, zero = w.contiguous(), scale.contiguous(), zero.contiguous()
+    q = torch.empty((n, k), dtype=torch.int32, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.lib().ao_b200_int4_quantize(w.data_ptr(), n, k, k, group_size, scale.data_ptr(),
+                                                    zero.data_ptr(), q.data_ptr(), _stream(w)), "int4_quantize")
+    return q
+
+
+@register_custom_op("torchao::b200_int4_pack")
+def _(int_data: Tensor):
+    np_, kp = _round_up(int_data.size(0), 16), _round_up(int_data.size(1), 64)
+    return torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
+
+
+@_impl_cuda("b200_int4_pack")
+def _int4_pack_cuda(int_data: Tensor):
+    torch._check(int_data.dim() == 2 and int_data.dtype is torch.int32, lambda: "int_data must be 2-D int32")
+    int_data = int_data.contiguous()
+    n, k = int_data.shape
+    np_, kp = _round_up(n, 16), _round_up(k, 64)
+    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
+    with torch.cuda.device(int_data.device):
+        _lib.check(_lib.lib().ao_b200_int4_pack(int_data.data_ptr(), n, k, np_, kp, 0, packed.data_ptr(),
+                                                _stream(int_data)), "int4_pack")
+    return packed
+
+
+def _strip_shape_checks(packed_w):
+    torch._check(packed_w.dim() == 4 and packed_w.size(2) == 32 and packed_w.size(3) == 4,
+                 lambda: f"strip-layout weight must be (N/16, K/64, 32, 4), got {tuple(packed_w.shape)}")
+    torch._check(packed_w.dtype is torch.int32, lambda: f"weight must be INT32, got {packed_w.dtype}")
+    return packed_w.size(0) * 16, packed_w.size(1) * 64
+
+
+@register_custom_op("torchao::b200_int4_unpack")
+def _(packed_w: Tensor):
+    n, k = _strip_shape_checks(packed_w)
+    return torch.empty((n, k), dtype=torch.int32, device=packed_w.device)
+
+
+@_impl_cuda("b200_int4_unpack")
+def _int4_unpack_cuda(packed_w: Tensor):
+    n, k = _strip_shape_checks(packed_w)
+    packed_w = packed_w.contiguous()
+    out = torch.empty((n, k), dtype=torch.int32, device=packed_w.device)
+    with torch.cuda.device(packed_w.device):
+        _lib.check(_lib.lib().ao_b200_int4_unpack(packed_w.data_ptr(), n, k, out.data_ptr(), _stream(packed_w)),
+                   "int4_unpack")
+    return out
+
+
+@register_custom_op("torchao::b200_int4_dequantize")
+def _(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int):
+    n, k = _strip_shape_checks(packed_w)
+    _sz_checks(scales_and_zeros, n, k, group_size)
+    return torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
+
+
+@_impl_cuda("b200_int4_dequantize")
+def _int4_dequant_cuda(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int):
+    n, k = _strip_shape_checks(packed_w)
+    _sz_checks(scales_and_zeros, n, k, group_size)
+    packed_w, scales_and_zeros = packed_w.contiguous(), scales_and_zeros.contiguous()
+    out = torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
+    with torch.cuda.device(packed_w.device):
+        _lib.check(_lib.lib().ao_b200_int4_dequant(packed_w.data_ptr(), scales_and_zeros.data_ptr(), n, k, group_size,
+                                                   out.data_ptr(), _stream(packed_w)), "int4_dequant")
+    return out
+
+
+@register_custom_op("torchao::b200_tinygemm_pack")
+def _(int_data: Tensor, inner_k_tiles: int):
+    n, k = int_data.shape
+    return torch.empty((n // 8, k // (inner_k_tiles * 16), 32, inner_k_tiles // 2), dtype=torch.int32,
+                       device=int_data.device)
+
+
+@_impl_cuda("b200_tinygemm_pack")
+def _tinygemm_pack_cuda(int_data: Tensor, inner_k_tiles: int):
+    torch._check(int_data.dim() == 2 and int_data.dtype is torch.int32, lambda: "int_data must be 2-D int32")
+    n, k = int_data.shape
+    torch._check(inner_k_tiles in (2, 4, 8), lambda: "inner_k_tiles must be 2, 4, or 8")
+    torch._check(n % 8 == 0 and k % (inner_k_tiles * 16) == 0, lambda: "N % 8 and K % (inner_k_tiles*16) must be 0")
+    int_data = int_data.contiguous()
+    out = torch.empty((n // 8, k // (inner_k_tiles * 16), 32, inner_k_tiles // 2), dtype=torch.int32,
+                      device=int_data.device)
+    with torch.cuda.device(int_data.device):
+        _lib.check(_lib.lib().ao_b200_tinygemm_pack(int_data.data_ptr(), n, k, inner_k_tiles, out.data_ptr(),
+                                                    _stream(int_data)), "tinygemm_pack")
+    return out
+
+
+def convert_tinygemm_to_b200(packed_w: Tensor, inner_k_tiles: int) -> Tensor:
+    """Re-tile a weight packed by aten._convert_weight_to_int4pack (reference checkpoints) into the strip layout."""
+    return torch.ops.torchao.b200_int4_pack(unpack_tensor_core_tiled_layout(packed_w, inner_k_tiles))
+
+
+# ------------------------------------------------------------------ linear ops
+@register_custom_op("torchao::b200_int4_weight_only_mm")
+def _(x: Tensor, packed_w: Tensor, group_size: int, scales_and_zeros: Tensor, out_features: int):
+    torch._check(x.dim() == 2, lambda: "x must be 2-D")
+    return torch.empty((x.size(0), out_features), dtype=torch.bfloat16, device=x.device)
+
+
+_WORKSPACES = {}
+
+
+def _workspace(device, nbytes):
+    if nbytes == 0:
+        return None
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WORKSPACES.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+@_impl_cuda("b200_int4_weight_only_mm")
+def _int4_mm_cuda(x: Tensor, packed_w: Tensor, group_size: int, scales_and_zeros: Tensor, out_features: int):
+    """Same contract as aten._weight_int4pack_mm(x, packed, G, scale_and_zero)
+    (call site torchao/dtypes/uintx/tensor_core_tiled_layout.py:104) on the strip layout."""
+    np_, kp = _strip_shape_checks(packed_w)
+    _sz_checks(scales_and_zeros, np_, kp, group_size)
+    _check_cuda_bf16(x, "activation")
+    torch._check(x.dim() == 2 and x.size(1) <= kp, lambda: f"x must be (M, K<= {kp}), got {tuple(x.shape)}")
+    torch._check(0 < out_features <= np_, lambda: "out_features out of range")
+    torch._check(packed_w.is_contiguous() and scales_and_zeros.is_contiguous(), lambda: "weights must be contiguous")
+    m = x.size(0)
+    y = torch.empty((m, out_features), dtype=torch.bfloat16, device=x.device)
+    if m == 0:
+        return y
+    if x.size(1) % 8 != 0:
+        x = torch.nn.functional.pad(x, (0, (-x.size(1)) % 8))
+    x, ldx = _rows(x)
+    L = _lib.lib()
+    ws_bytes = L.ao_b200_int4_mm_workspace_bytes(m, np_, kp)
+    ws = _workspace(x.device, ws_bytes)
+    with torch.cuda.device(x.device):
+        _lib.check(L.ao_b200_int4_mm(x.data_ptr(), m, x.size(1), ldx, packed_w.data_ptr(), scales_and_zeros.data_ptr(),
+                                     np_, kp, group_size, y.data_ptr(), out_features, out_features,
+                                     ws.data_ptr() if ws is not None else None, ws_bytes, _stream(x)), "int4_mm")
+    return y
+
+
+@register_custom_op("torchao::b200_int8_quantize")
+def _(w: Tensor, eps: float, cuda_div_semantics: bool):
+    return (torch.empty(w.shape, dtype=torch.int8, device=w.device),
+            torch.empty((w.size(0),), dtype=torch.bfloat16, device=w.device))
+
+
+@_impl_cuda("b200_int8_quantize")
+def _int8_quantize_cuda(w: Tensor, eps: float, cuda_div_semantics: bool):
+    torch._check(w.dim() == 2, lambda: "weight must be 2-D")
+    _check_cuda_bf16(w, "weight")
+    w = w.contiguous()
+    n, k = w.shape
+    q = torch.empty((n, k), dtype=torch.int8, device=w.device)
+    scale = torch.empty((n,), dtype=torch.bfloat16, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.lib().ao_b200_int8_quantize(w.data_ptr(), n, k, k, eps,
+                                                    _lib.DIV_RECIP if cuda_div_semantics else _lib.DIV_IEEE,
+                                                    q.data_ptr(), scale.data_ptr(), _stream(w)), "int8_quantize")
+    return q, scale
+
+
+@register_custom_op("torchao::b200_int8_weight_only_mm")
+def _(x: Tensor, int_data: Tensor, scale: Tensor):
+    return torch.empty((x.size(0), int_data.size(0)), dtype=torch.bfloat16, device=x.device)
+
+
+@_impl_cuda("b200_int8_weight_only_mm")
+def _int8_mm_cuda(x: Tensor, int_data: Tensor, scale: Tensor):
+    """y = (x @ int_data.T.to(bf16)) * scale with the reference's two bf16 roundings
+    (torchao/dtypes/uintx/plain_layout.py:250-266)."""
+    _check_cuda_bf16(x, "activation")
+    _check_cuda_bf16(scale, "scale")
+    torch._check(int_data.dtype is torch.int8 and int_data.dim() == 2, lambda: "int_data must be 2-D int8")
+    torch._check(x.dim() == 2 and x.size(1) == int_data.size(1), lambda: "x / weight K mismatch")
+    torch._check(int_data.size(1) % 16 == 0, lambda: "int8 weight-only mm needs in_features % 16 == 0")
+    torch._check(scale.numel() == int_data.size(0), lambda: "scale must have one entry per output row")
+    int_data, scale = int_data.contiguous(), scale.contiguous()
+    m, n = x.size(0), int_data.size(0)
+    y = torch.empty((m, n), dtype=torch.bfloat16, device=x.device)
+    if m == 0:
+        return y
+    x, ldx = _rows(x)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ao_b200_int8_mm(x.data_ptr(), m, x.size(1), ldx, int_data.data_ptr(), scale.data_ptr(),
+                                              n, y.data_ptr(), n, _stream(x)), "int8_mm")
+    return y
