@@ -16,12 +16,15 @@
  * bf16 tensors are passed as `const void*` to 2-byte elements, row-major.
  *
  * HBM layouts
- *   "strip" layout (this library's int4 weight format), uint32 [Np/16][Kp/64][32][4]:
- *       tile (strip s, k-tile t) = 16 rows x 64 k = 512 contiguous bytes;
- *       lane l = (g = l>>2, c = l&3) owns the 16 bytes at word index ((s*Kp/64+t)*32+l)*4;
- *       word j of the lane: row = 16 s + g + 8 (j&1),  k0 = 64 t + 32 (j>>1) + 8 c,
- *       and holds k0..k0+7 in nibble slots [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7]
- *       (slot i = bits 4i..4i+3).  Np % 16 == 0, Kp % 64 == 0.
+ *   "super-tile" layout (this library's int4 weight format), uint32 [Np/128][Kp/64][8][32][4]:
+ *       super-tile (S, kt) = 128 rows x 64 k = 4096 contiguous bytes (one TMA bulk copy), made of
+ *       8 sub-tiles r of 16 rows x 64 k = 512 bytes; inside a sub-tile lane l = (g = l>>2, c = l&3)
+ *       owns 16 bytes; word j of the lane: row = 128 S + 16 r + g + 8 (j&1),
+ *       k0 = 64 kt + 32 (j>>1) + 8 c, and holds k0..k0+7 in nibble slots
+ *       [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7] (slot i = bits 4i..4i+3) so that
+ *       "(w >> 4i) & 0x000f000f" yields the pair (k0+2i, k0+2i+1).  Np % 128 == 0, Kp % 64 == 0.
+ *       A lane's 4 words are exactly the A-operand rows (g, g+8) of two m16n8k16 MMAs per k-half,
+ *       and each word is one 16-byte chunk of a K-major UMMA shared-memory operand row.
  *   scale_and_zero: bf16 [Kp/G][Np][2] = (scale, zero) — identical to the reference's
  *       pack_tinygemm_scales_and_zeros (torchao/quantization/utils.py:395-409).
  *   "tinygemm" layout: int32 [N/8][K/(ikt*16)][32][ikt/2], the output format of
@@ -67,8 +70,8 @@ AO_B200_API int ao_b200_abi_version(void);
  * TensorCoreTiledAQTTensorImpl.from_plain (tensor_core_tiled_layout.py:262-307):
  * one pass over W.  w: bf16 [N][K] with row stride ldw (elements, % 8 == 0).
  * Rows >= N / columns >= K of the padded [Np][Kp] problem read as zero.
- * Outputs: packed (strip layout, Np x Kp), scale_and_zero bf16 [Kp/G][Np][2].
- * G in {32,64,128,256}; K % G == 0; Kp % max(G,64) == 0; Np % 16 == 0. */
+ * Outputs: packed (super-tile layout, Np x Kp), scale_and_zero bf16 [Kp/G][Np][2].
+ * G in {32,64,128,256}; K % G == 0; Kp % max(G,64) == 0; Np % 128 == 0. */
 AO_B200_API int ao_b200_int4_quantize_pack(const void* w, int64_t N, int64_t K, int64_t ldw,
                                int64_t Np, int64_t Kp, int group_size, float eps, int div_mode,
                                void* packed, void* scale_and_zero, void* stream);
@@ -83,12 +86,12 @@ AO_B200_API int ao_b200_int4_quantize(const void* w, int64_t N, int64_t K, int64
 
 /* ---------------------------------------------------------------- int4: layouts ----- */
 
-/* from_plain: q int32 [N][K] (values 0..15; rows>=N / cols>=K pad with `pad_value`) -> strip layout. */
+/* from_plain: q int32 [N][K] (values 0..15; rows>=N / cols>=K pad with `pad_value`) -> super-tile layout. */
 AO_B200_API int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp,
                       int pad_value, void* packed, void* stream);
-/* strip layout -> int32 [Np][Kp]. */
+/* super-tile layout -> int32 [Np][Kp]. */
 AO_B200_API int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, int32_t* q, void* stream);
-/* strip layout + scale_and_zero -> bf16 [Np][Kp], W' = bf16_rn((q-8)*s + z) (single rounding,
+/* super-tile layout + scale_and_zero -> bf16 [Np][Kp], W' = bf16_rn((q-8)*s + z) (single rounding,
  * the dequant of aten._weight_int4pack_mm; tensor_core_tiled_layout.cu:41-117,194). */
 AO_B200_API int ao_b200_int4_dequant(const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                          int group_size, void* out, void* stream);

@@ -281,37 +281,38 @@ def unpack_tinygemm(packed, inner_k_tiles=8):
     return q
 
 
-# ---- the B200 strip layout (this build's own; see DESIGN.md "HBM layout") ----
-# packed uint32 [N/16][K/64][32][4]; tile (strip, kt), lane l=(g=l>>2, c=l&3), word j:
-#   row = 16*strip + g + 8*(j&1);  k0 = 64*kt + 32*(j>>1) + 8*c;  word holds k0..k0+7.
+# ---- the B200 "super-tile" layout (this build's own; see DESIGN.md "HBM layout") ----
+# packed uint32 [N/128][K/64][8][32][4]: super-tile (S, kt) = 128 rows x 64 k = 4096 contiguous bytes,
+# made of 8 sub-tiles r (16 rows each, 512 bytes); in a sub-tile lane l=(g=l>>2, c=l&3) owns 16 bytes,
+# word j:  row = 128*S + 16*r + g + 8*(j&1);  k0 = 64*kt + 32*(j>>1) + 8*c;  word holds k0..k0+7.
 def pack_b200(q):
     n, k = q.shape
-    assert n % 16 == 0 and k % 64 == 0
+    assert n % 128 == 0 and k % 64 == 0
     lane = np.arange(32)
     g, c = lane >> 2, lane & 3
-    out = np.zeros((n // 16, k // 64, 32, 4), dtype=np.uint32)
-    q5 = q.reshape(n // 16, 16, k // 64, 8, 8)       # [strip][row][kt][chunk][8]
+    out = np.zeros((n // 128, k // 64, 8, 32, 4), dtype=np.uint32)
+    q6 = q.reshape(n // 128, 8, 16, k // 64, 8, 8)   # [S][r][row][kt][chunk][8]
     for j in range(4):
         rows = g + 8 * (j & 1)
         chunks = c + 4 * (j >> 1)
-        vals = q5[:, rows, :, chunks, :]              # -> [32][strip][kt][8]
-        out[:, :, :, j] = _pack_words(vals).transpose(1, 2, 0)
+        vals = q6[:, :, rows, :, chunks, :]           # -> [32][S][r][kt][8]
+        out[:, :, :, :, j] = _pack_words(vals).transpose(1, 3, 2, 0)
     return out.view(np.int32)
 
 
 def unpack_b200(packed):
     p = packed.view(np.uint32)
-    s_, kt_, _, _ = p.shape
-    n, k = s_ * 16, kt_ * 64
+    s_, kt_ = p.shape[0], p.shape[1]
+    n, k = s_ * 128, kt_ * 64
     lane = np.arange(32)
     g, c = lane >> 2, lane & 3
-    q5 = np.zeros((s_, 16, kt_, 8, 8), dtype=np.int32)
+    q6 = np.zeros((s_, 8, 16, kt_, 8, 8), dtype=np.int32)
     for j in range(4):
         rows = g + 8 * (j & 1)
         chunks = c + 4 * (j >> 1)
-        vals = _unpack_words(p[:, :, :, j])           # [strip][kt][32][8]
-        q5[:, rows, :, chunks, :] = vals.transpose(2, 0, 1, 3)
-    return q5.reshape(n, k)
+        vals = _unpack_words(p[:, :, :, :, j])        # [S][kt][r][32][8]
+        q6[:, :, rows, :, chunks, :] = vals.transpose(3, 0, 2, 1, 4)
+    return q6.reshape(n, k)
 
 
 # --------------------------------------------------------------------------

@@ -102,8 +102,10 @@ def test_int4_quantize_pack_matches_golden(path):
     np_, kp = aops.padded_int4_shape(n, k, gs)
     qpad = np.zeros((np_, kp), dtype=np.int32)
     qpad[:n, :k] = g["q"]
-    if (np_, kp) == (n, k):
-        assert np.array_equal(packed.cpu().numpy(), o.pack_b200(qpad))
+    # (padded rows quantize zeros under eps-clamped qparams: q = 8)
+    qpad[n:, :] = T.b200_int4_unpack(packed).cpu().numpy()[n:, :]
+    qpad[:n, k:] = T.b200_int4_unpack(packed).cpu().numpy()[:n, k:]
+    assert np.array_equal(packed.cpu().numpy(), o.pack_b200(qpad))
 
 
 def test_int4_padded_matches_golden():
@@ -112,7 +114,7 @@ def test_int4_padded_matches_golden():
     w = bf16_from_bits(g["w"])
     packed, sz = T.b200_int4_quantize_pack(w, gs, 1e-6, False)
     n_ref, k_ref = [int(v) for v in g["padded_shape"]]     # reference pads to (328, 1024)
-    np_, kp = packed.shape[0] * 16, packed.shape[1] * 64    # we pad to (336, 256)
+    np_, kp = packed.shape[0] * 128, packed.shape[1] * 64   # we pad to (384, 256)
     q = T.b200_int4_unpack(packed).cpu().numpy()
     nn, kk = min(np_, n_ref), min(kp, k_ref)
     assert np.array_equal(q[:nn, :kk].astype(np.uint8), g["q"][:nn, :kk])
@@ -145,10 +147,10 @@ def test_int4_pack_unpack_roundtrip_and_oracle():
     packed = T.b200_int4_pack(q)
     assert torch.equal(T.b200_int4_unpack(packed), q)
     assert np.array_equal(packed.cpu().numpy(), o.pack_b200(q.cpu().numpy()))
-    # ragged: pads rows to x16 and columns to x64 with zeros
+    # ragged: pads rows to x128 and columns to x64 with zeros
     q2 = torch.randint(0, 16, (321, 200), dtype=torch.int32, device=DEV)
     u = T.b200_int4_unpack(T.b200_int4_pack(q2))
-    assert u.shape == (336, 256) and torch.equal(u[:321, :200], q2) and int(u[321:].abs().sum()) == 0
+    assert u.shape == (384, 256) and torch.equal(u[:321, :200], q2) and int(u[321:].abs().sum()) == 0
 
 
 # ------------------------------------------------------------------------------------------------
@@ -203,11 +205,11 @@ def test_int4_dequant_matches_oracle(path):
     gs = int(g["group_size"])
     q = g["q"].astype(np.int32)
     n, k = q.shape
-    if n % 16 or k % 64:
-        pytest.skip("needs x16 / x64")
     packed = T.b200_int4_pack(torch.from_numpy(q).to(DEV))
     sz = bf16_from_bits(g["scale_and_zero"])
-    dq = T.b200_int4_dequantize(packed, sz, gs)
+    np_ = packed.shape[0] * 128
+    sz = torch.nn.functional.pad(sz, (0, 0, 0, np_ - n))
+    dq = T.b200_int4_dequantize(packed, sz, gs)[:n]
     ref = o.dequantize_tinygemm(q, o.from_bits(g["scale"]), o.from_bits(g["zero"]), gs)
     a, b = bits_of(dq), o.to_bits(ref)
     finite = np.isfinite(ref)

@@ -103,11 +103,20 @@ def test_int8_mm_vs_cpu_reference(path):
     assert o.sqnr_db(ref, y) >= 40.0
 
 
-@pytest.mark.parametrize("shape", [(16, 64), (32, 256), (48, 1024)])
+@pytest.mark.parametrize("shape", [(128, 64), (256, 256), (384, 1024)])
 def test_layout_round_trips(shape):
     rng = np.random.default_rng(shape[1])
     q = rng.integers(0, 16, shape).astype(np.int32)
-    assert np.array_equal(o.unpack_b200(o.pack_b200(q)), q)
+    p = o.pack_b200(q)
+    assert p.shape == (shape[0] // 128, shape[1] // 64, 8, 32, 4)
+    assert np.array_equal(o.unpack_b200(p), q)
+    # the layout definition of include/ao_b200.h, spelled out element by element
+    pu = p.view(np.uint32)
+    for (S, kt, r, lane, j) in [(0, 0, 0, 0, 0), (shape[0] // 128 - 1, shape[1] // 64 - 1, 7, 31, 3), (0, 0, 5, 13, 2)]:
+        g, c = lane >> 2, lane & 3
+        row, k0 = 128 * S + 16 * r + g + 8 * (j & 1), 64 * kt + 32 * (j >> 1) + 8 * c
+        w = int(pu[S, kt, r, lane, j])
+        assert [(w >> (4 * s)) & 15 for s in (0, 4, 1, 5, 2, 6, 3, 7)] == list(q[row, k0:k0 + 8])
     if shape[1] % 128 == 0:
         for ikt in (2, 4, 8):
             assert np.array_equal(o.unpack_tinygemm(o.pack_tinygemm(q, ikt), ikt), q)

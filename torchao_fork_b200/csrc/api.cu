@@ -4,6 +4,10 @@
 namespace ao {
 int int4_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
               int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, cudaStream_t s);
+int int4_gemv_stream(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz,
+                     int64_t Np, int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, void* workspace,
+                     int64_t workspace_bytes, int stages, bool pdl, cudaStream_t s);
+int64_t int4_gemv_stream_workspace_bytes(int64_t Np);
 int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
               void* y, int64_t ldy, cudaStream_t s);
 }  // namespace ao
@@ -21,17 +25,37 @@ extern "C" const char* ao_b200_error_string(int code) {
 
 extern "C" int ao_b200_abi_version(void) { return 1; }
 
+#include <cstdlib>
+namespace {
+struct Tunables {
+  int gemv_version, stages, pdl;
+  Tunables() {
+    const char* v = std::getenv("AO_B200_GEMV");
+    gemv_version = v ? std::atoi(v) : 2;
+    const char* st = std::getenv("AO_B200_STAGES");
+    stages = st ? std::atoi(st) : 8;
+    if (stages < 2) stages = 2;
+    if (stages > 9) stages = 9;
+    const char* pd = std::getenv("AO_B200_PDL");
+    pdl = pd ? std::atoi(pd) : 1;
+  }
+};
+const Tunables& tunables() {
+  static Tunables t;
+  return t;
+}
+}  // namespace
+
 extern "C" int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
-  (void)M; (void)Np; (void)Kp;
-  return 0;
+  (void)M; (void)Kp;
+  return ao::int4_gemv_stream_workspace_bytes(Np);
 }
 
 extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
                                const void* scale_and_zero, int64_t Np, int64_t Kp, int group_size, void* y,
                                int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, void* stream) {
-  (void)workspace; (void)workspace_bytes;
   AO_CHECK_ARG(x && packed && scale_and_zero && y);
-  AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
+  AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
   AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx && ldy >= N_out);
   AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 4) && ao_aligned(y, 2));
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
@@ -41,8 +65,14 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   auto yb = static_cast<__nv_bfloat16*>(y);
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
-    int e = ao::int4_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
-                          N_out, ldy, s);
+    int e;
+    if (tunables().gemv_version == 1)
+      e = ao::int4_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out,
+                        ldy, s);
+    else
+      e = ao::int4_gemv_stream(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size,
+                               yb + m0 * ldy, N_out, ldy, workspace, workspace_bytes, tunables().stages,
+                               tunables().pdl != 0, s);
     if (e) return e;
   }
   return AO_B200_OK;

@@ -1,0 +1,290 @@
+// Non-GEMM remainder of one Llama decode step: fused residual-add + RMSNorm,
+// RoPE + KV-cache append, GQA decode attention, SiLU*mul.  All read the token position from DEVICE
+// memory so a captured CUDA graph can be replayed for every token.
+#include "common.cuh"
+
+namespace ao {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------
+// h = bf16(x + residual) (optional); y = bf16( bf16(h * rsqrt(mean(h^2) + eps)) * w )
+// (model.py:489-503: norm in fp32, cast back, then multiply by the bf16 weight).  One CTA per row.
+// ---------------------------------------------------------------------------------------
+template <int kThreads>
+__global__ void __launch_bounds__(kThreads) rmsnorm_kernel(const __nv_bfloat16* __restrict__ x,
+                                                           const __nv_bfloat16* __restrict__ residual,
+                                                           const __nv_bfloat16* __restrict__ weight,
+                                                           __nv_bfloat16* __restrict__ h_out,
+                                                           __nv_bfloat16* __restrict__ y, int64_t dim, float eps) {
+  extern __shared__ float s_row[];  // dim floats
+  __shared__ float s_part[kThreads / 32];
+  const int64_t row = blockIdx.x;
+  const __nv_bfloat16* xr = x + row * dim;
+  const __nv_bfloat16* rr = residual ? residual + row * dim : nullptr;
+  float ss = 0.f;
+  for (int64_t i = threadIdx.x * 8; i < dim; i += kThreads * 8) {
+    float f[8];
+    unpack8(*reinterpret_cast<const uint4*>(xr + i), f);
+    if (rr) {
+      float r[8];
+      unpack8(*reinterpret_cast<const uint4*>(rr + i), r);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = bf16r(f[e] + r[e]);
+      if (h_out) {
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
+        *reinterpret_cast<uint4*>(h_out + row * dim + i) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      s_row[i + e] = f[e];
+      ss += f[e] * f[e];
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < kThreads / 32; ++i) tot += s_part[i];
+  const float rs = rsqrtf(tot / static_cast<float>(dim) + eps);
+  for (int64_t i = threadIdx.x * 8; i < dim; i += kThreads * 8) {
+    float wv[8];
+    unpack8(*reinterpret_cast<const uint4*>(weight + i), wv);
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float a = bf16r(s_row[i + 2 * e] * rs) * wv[2 * e];
+      const float b = bf16r(s_row[i + 2 * e + 1] * rs) * wv[2 * e + 1];
+      o[e] = float_to_bf16_bits(a) | (float_to_bf16_bits(b) << 16);
+    }
+    *reinterpret_cast<uint4*>(y + row * dim + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// RoPE (model.py:547-559, fp32 math on bf16 cos/sin) on q and k + KV-cache append at *input_pos
+// (KVCache.update, model.py:175-192).  qkv: [B][(H + 2 Hkv) * hd]; caches [B][Hkv][S][hd].
+// One thread per (b, head, pair).
+// ---------------------------------------------------------------------------------------
+__global__ void rope_kv_append_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ freqs,
+                                      const int32_t* __restrict__ input_pos, __nv_bfloat16* __restrict__ q_out,
+                                      __nv_bfloat16* __restrict__ k_cache, __nv_bfloat16* __restrict__ v_cache, int B,
+                                      int H, int Hkv, int hd, int S) {
+  const int pos = *input_pos;
+  const int half = hd / 2;
+  const int heads = H + 2 * Hkv;
+  const int64_t total = (int64_t)B * heads * half;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int p = i % half;
+    const int head = (i / half) % heads;
+    const int b = i / ((int64_t)half * heads);
+    const __nv_bfloat162 v2 = *reinterpret_cast<const __nv_bfloat162*>(qkv + ((int64_t)b * heads + head) * hd + 2 * p);
+    if (head < H + Hkv) {
+      const __nv_bfloat162 cs = *reinterpret_cast<const __nv_bfloat162*>(freqs + ((int64_t)pos * half + p) * 2);
+      const float x0 = __bfloat162float(v2.x), x1 = __bfloat162float(v2.y);
+      const float c = __bfloat162float(cs.x), s = __bfloat162float(cs.y);
+      __nv_bfloat162 o;
+      o.x = __float2bfloat16_rn(x0 * c - x1 * s);
+      o.y = __float2bfloat16_rn(x1 * c + x0 * s);
+      if (head < H)
+        *reinterpret_cast<__nv_bfloat162*>(q_out + ((int64_t)b * H + head) * hd + 2 * p) = o;
+      else
+        *reinterpret_cast<__nv_bfloat162*>(k_cache + (((int64_t)b * Hkv + (head - H)) * S + pos) * hd + 2 * p) = o;
+    } else {
+      *reinterpret_cast<__nv_bfloat162*>(v_cache + (((int64_t)b * Hkv + (head - H - Hkv)) * S + pos) * hd + 2 * p) = v2;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// GQA decode attention for one new token: out[b][h][:] = softmax(q.K^T * scale)[0..pos] . V
+// One CTA per (b, kv head, split); each warp owns one q head of the group and walks the key
+// positions with an online softmax; hd == 128 (4 dims per lane), lanes reduce each dot product.
+// Splits over the sequence are merged by a tiny second kernel when n_split > 1.
+// ---------------------------------------------------------------------------------------
+template <int kGroup>  // q heads per kv head (<= 8)
+__global__ void __launch_bounds__(kGroup * 32) decode_attn_kernel(
+    const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k_cache,
+    const __nv_bfloat16* __restrict__ v_cache, const int32_t* __restrict__ input_pos, __nv_bfloat16* __restrict__ out,
+    float* __restrict__ part_o, float* __restrict__ part_ml, int H, int Hkv, int S, float scale, int n_split) {
+  constexpr int hd = 128;
+  const int pos = *input_pos;
+  const int kvh = blockIdx.x, b = blockIdx.y, split = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = kvh * kGroup + warp;
+  const int len = pos + 1;
+  const int chunk = (len + n_split - 1) / n_split;
+  const int j0 = split * chunk, j1 = min(len, j0 + chunk);
+
+  float qv[4];
+  {
+    const uint2 raw = *reinterpret_cast<const uint2*>(q + ((int64_t)b * H + h) * hd + lane * 4);
+    qv[0] = __uint_as_float(raw.x << 16) * scale;
+    qv[1] = __uint_as_float(raw.x & 0xFFFF0000u) * scale;
+    qv[2] = __uint_as_float(raw.y << 16) * scale;
+    qv[3] = __uint_as_float(raw.y & 0xFFFF0000u) * scale;
+  }
+  const __nv_bfloat16* kb = k_cache + ((int64_t)b * Hkv + kvh) * S * hd + lane * 4;
+  const __nv_bfloat16* vb = v_cache + ((int64_t)b * Hkv + kvh) * S * hd + lane * 4;
+  float m = -INFINITY, l = 0.f, acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = j0; j < j1; ++j) {
+    const uint2 kr = *reinterpret_cast<const uint2*>(kb + (int64_t)j * hd);
+    float s = qv[0] * __uint_as_float(kr.x << 16) + qv[1] * __uint_as_float(kr.x & 0xFFFF0000u) +
+              qv[2] * __uint_as_float(kr.y << 16) + qv[3] * __uint_as_float(kr.y & 0xFFFF0000u);
+    s = warp_sum(s);
+    const float m_new = fmaxf(m, s);
+    const float corr = __expf(m - m_new);
+    const float p = __expf(s - m_new);
+    const uint2 vr = *reinterpret_cast<const uint2*>(vb + (int64_t)j * hd);
+    l = l * corr + p;
+    acc[0] = acc[0] * corr + p * __uint_as_float(vr.x << 16);
+    acc[1] = acc[1] * corr + p * __uint_as_float(vr.x & 0xFFFF0000u);
+    acc[2] = acc[2] * corr + p * __uint_as_float(vr.y << 16);
+    acc[3] = acc[3] * corr + p * __uint_as_float(vr.y & 0xFFFF0000u);
+    m = m_new;
+  }
+  if (n_split == 1) {
+    const float inv = 1.f / l;
+    uint2 o;
+    o.x = float_to_bf16_bits(acc[0] * inv) | (float_to_bf16_bits(acc[1] * inv) << 16);
+    o.y = float_to_bf16_bits(acc[2] * inv) | (float_to_bf16_bits(acc[3] * inv) << 16);
+    *reinterpret_cast<uint2*>(out + ((int64_t)b * H + h) * hd + lane * 4) = o;
+  } else {
+    const int64_t slot = ((int64_t)b * H + h) * n_split + split;
+    *reinterpret_cast<float4*>(part_o + slot * hd + lane * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    if (lane == 0) {
+      part_ml[slot * 2] = m;
+      part_ml[slot * 2 + 1] = l;
+    }
+  }
+}
+
+__global__ void decode_attn_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                                         __nv_bfloat16* __restrict__ out, int n_split) {
+  constexpr int hd = 128;
+  const int64_t bh = blockIdx.x;
+  const int d = threadIdx.x;  // 128 threads
+  float m = -INFINITY;
+  for (int s = 0; s < n_split; ++s) m = fmaxf(m, part_ml[(bh * n_split + s) * 2]);
+  float l = 0.f, acc = 0.f;
+  for (int s = 0; s < n_split; ++s) {
+    const float ms = part_ml[(bh * n_split + s) * 2], ls = part_ml[(bh * n_split + s) * 2 + 1];
+    const float w = (ls > 0.f) ? __expf(ms - m) : 0.f;
+    l += ls * w;
+    acc += part_o[(bh * n_split + s) * hd + d] * w;
+  }
+  out[bh * hd + d] = __float2bfloat16_rn(acc / l);
+}
+
+// out = bf16( bf16(silu(gate)) * up ), gate_up = [B][2I] (rows of w1 then rows of w3) — model.py:486
+__global__ void silu_mul_kernel(const __nv_bfloat16* __restrict__ gate_up, __nv_bfloat16* __restrict__ out, int64_t B,
+                                int64_t I) {
+  const int64_t total = B * I / 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = (i * 8) / I, c = (i * 8) % I;
+    float g[8], u[8];
+    unpack8(*reinterpret_cast<const uint4*>(gate_up + b * 2 * I + c), g);
+    unpack8(*reinterpret_cast<const uint4*>(gate_up + b * 2 * I + I + c), u);
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float a0 = bf16r(g[2 * e] / (1.f + __expf(-g[2 * e]))) * u[2 * e];
+      const float a1 = bf16r(g[2 * e + 1] / (1.f + __expf(-g[2 * e + 1]))) * u[2 * e + 1];
+      o[e] = float_to_bf16_bits(a0) | (float_to_bf16_bits(a1) << 16);
+    }
+    *reinterpret_cast<uint4*>(out + b * I + c) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+}  // namespace ao
+
+using namespace ao;
+
+extern "C" int ao_b200_rmsnorm(const void* x, const void* residual, const void* weight, void* h_out, void* y,
+                               int64_t rows, int64_t dim, float eps, void* stream) {
+  AO_CHECK_ARG(x && weight && y && rows > 0 && dim > 0 && dim % 8 == 0 && dim * 4 <= 200 * 1024);
+  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(weight, 16) && ao_aligned(y, 16));
+  AO_CHECK_ARG((!residual || ao_aligned(residual, 16)) && (!h_out || ao_aligned(h_out, 16)));
+  const size_t smem = dim * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set && smem > 48 * 1024) {
+    cudaFuncSetAttribute(rmsnorm_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set = true;
+  }
+  rmsnorm_kernel<512><<<static_cast<unsigned>(rows), 512, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual),
+      static_cast<const __nv_bfloat16*>(weight), static_cast<__nv_bfloat16*>(h_out), static_cast<__nv_bfloat16*>(y),
+      dim, eps);
+  return ao_launch_status();
+}
+
+extern "C" int ao_b200_rope_kv_append(const void* qkv, const void* freqs_cis, const int32_t* input_pos, void* q_out,
+                                      void* k_cache, void* v_cache, int B, int H, int Hkv, int head_dim, int S,
+                                      void* stream) {
+  AO_CHECK_ARG(qkv && freqs_cis && input_pos && q_out && k_cache && v_cache);
+  AO_CHECK_ARG(B > 0 && H > 0 && Hkv > 0 && head_dim > 0 && head_dim % 2 == 0 && S > 0);
+  const int64_t total = (int64_t)B * (H + 2 * Hkv) * (head_dim / 2);
+  const int grid = static_cast<int>((total + 255) / 256);
+  rope_kv_append_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(qkv), static_cast<const __nv_bfloat16*>(freqs_cis), input_pos,
+      static_cast<__nv_bfloat16*>(q_out), static_cast<__nv_bfloat16*>(k_cache), static_cast<__nv_bfloat16*>(v_cache),
+      B, H, Hkv, head_dim, S);
+  return ao_launch_status();
+}
+
+extern "C" int64_t ao_b200_decode_attention_workspace_bytes(int B, int H, int n_split) {
+  return n_split <= 1 ? 0 : (int64_t)B * H * n_split * (128 + 2) * sizeof(float);
+}
+
+extern "C" int ao_b200_decode_attention(const void* q, const void* k_cache, const void* v_cache,
+                                        const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim,
+                                        int S, float scale, int n_split, void* workspace, int64_t workspace_bytes,
+                                        void* stream) {
+  AO_CHECK_ARG(q && k_cache && v_cache && input_pos && out && B > 0 && H > 0 && Hkv > 0 && S > 0 && n_split >= 1);
+  if (head_dim != 128 || H % Hkv != 0) return AO_B200_ERR_UNSUPPORTED;
+  const int group = H / Hkv;
+  if (workspace_bytes < ao_b200_decode_attention_workspace_bytes(B, H, n_split)) return AO_B200_ERR_WORKSPACE;
+  float* part_o = static_cast<float*>(workspace);
+  float* part_ml = part_o ? part_o + (int64_t)B * H * n_split * 128 : nullptr;
+  auto s = static_cast<cudaStream_t>(stream);
+  dim3 grid(Hkv, B, n_split);
+  auto qp = static_cast<const __nv_bfloat16*>(q);
+  auto kp = static_cast<const __nv_bfloat16*>(k_cache);
+  auto vp = static_cast<const __nv_bfloat16*>(v_cache);
+  auto op = static_cast<__nv_bfloat16*>(out);
+#define AO_ATTN(G) \
+  decode_attn_kernel<G><<<grid, G * 32, 0, s>>>(qp, kp, vp, input_pos, op, part_o, part_ml, H, Hkv, S, scale, n_split)
+  switch (group) {
+    case 1: AO_ATTN(1); break;
+    case 2: AO_ATTN(2); break;
+    case 4: AO_ATTN(4); break;
+    case 8: AO_ATTN(8); break;
+    default: return AO_B200_ERR_UNSUPPORTED;
+  }
+#undef AO_ATTN
+  if (n_split > 1)
+    decode_attn_merge_kernel<<<B * H, 128, 0, s>>>(part_o, part_ml, op, n_split);
+  return ao_launch_status();
+}
+
+extern "C" int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64_t I, void* stream) {
+  AO_CHECK_ARG(gate_up && out && B > 0 && I > 0 && I % 8 == 0 && ao_aligned(gate_up, 16) && ao_aligned(out, 16));
+  const int64_t total = B * I / 8;
+  const int grid = static_cast<int>((total + 255) / 256);
+  silu_mul_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(gate_up),
+                                                                      static_cast<__nv_bfloat16*>(out), B, I);
+  return ao_launch_status();
+}

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(kGemvWarps * 32) int4_gemv_strip_kernel(
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[mt][i] = 0.f;
 
-    const uint4* wp = packed + strip * k_tiles * 32 + lane;
+    const uint4* wp = packed + lane;
     const int64_t row_lo = strip * 16 + g;
 
     constexpr int U = 4;  // tiles in flight per warp
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kGemvWarps * 32) int4_gemv_strip_kernel(
       for (int u = 0; u < U; ++u) {
         const int64_t kt = kt0 + u;
         const bool ok = kt < k_tiles;
-        wv[u] = ok ? ldg128(wp + kt * 32) : make_uint4(0x88888888u, 0x88888888u, 0x88888888u, 0x88888888u);
+        wv[u] = ok ? ldg128(wp + tile_slot(strip, kt, k_tiles) * 32) : make_uint4(0x88888888u, 0x88888888u, 0x88888888u, 0x88888888u);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int64_t grp = (kt * 64 + 32 * h) / G;

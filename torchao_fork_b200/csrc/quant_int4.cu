@@ -30,7 +30,7 @@ __device__ __forceinline__ uint32_t tinygemm_quant1(float w, float min_val, floa
 }
 
 // ---------------------------------------------------------------------------------------
-// Fused quantize + pack.  One warp owns a unit = 16 rows x UK columns, UK = max(G, 64):
+// Fused quantize + pack into the super-tile layout (include/ao_b200.h).  One warp owns a unit = 16 rows x UK columns, UK = max(G, 64):
 // it loads the unit's tiles in the strip layout's own lane order (so the packed words fall
 // out of registers already in place), reduces min/max over the 4 lanes that share a row,
 // and writes 512-byte tiles with one coalesced 16-byte store per lane.
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(256) int4_quantize_pack_kernel(
         words[j] = word;
       }
       const int64_t kt = uk * T + t;
-      packed[(strip * (Kp / 64) + kt) * 32 + lane] = make_uint4(words[0], words[1], words[2], words[3]);
+      packed[tile_slot(strip, kt, Kp / 64) * 32 + lane] = make_uint4(words[0], words[1], words[2], words[3]);
     }
     if (c == 0) {
 #pragma unroll
@@ -182,8 +182,8 @@ __global__ void __launch_bounds__(256) int4_pack_kernel(const int32_t* __restric
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int lane = i & 31;
-    const int64_t tile = i >> 5;
-    const int64_t strip = tile / (Kp / 64), kt = tile % (Kp / 64);
+    int64_t strip, kt;
+    tile_of_slot(i >> 5, Kp / 64, strip, kt);
     const int g = lane >> 2, c = lane & 3;
     uint32_t words[4];
 #pragma unroll
@@ -210,8 +210,8 @@ __global__ void __launch_bounds__(256) int4_unpack_kernel(const uint4* __restric
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int lane = i & 31;
-    const int64_t tile = i >> 5;
-    const int64_t strip = tile / (Kp / 64), kt = tile % (Kp / 64);
+    int64_t strip, kt;
+    tile_of_slot(i >> 5, Kp / 64, strip, kt);
     const int g = lane >> 2, c = lane & 3;
     const uint4 v = packed[i];
     const uint32_t words[4] = {v.x, v.y, v.z, v.w};
@@ -311,7 +311,7 @@ extern "C" int ao_b200_int4_quantize_pack(const void* w, int64_t N, int64_t K, i
   AO_CHECK_ARG(N > 0 && K > 0 && Np >= N && Kp >= K);
   if (!valid_group(group_size)) return AO_B200_ERR_UNSUPPORTED;
   const int64_t uk = group_size > 64 ? group_size : 64;
-  AO_CHECK_ARG(K % group_size == 0 && Kp % uk == 0 && Np % 16 == 0);
+  AO_CHECK_ARG(K % group_size == 0 && Kp % uk == 0 && Np % 128 == 0);
   AO_CHECK_ARG(ldw % 8 == 0 && ao_aligned(w, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 4));
   AO_CHECK_ARG(div_mode == AO_B200_DIV_IEEE || div_mode == AO_B200_DIV_RECIP);
   const int64_t units = (Np / 16) * (Kp / uk);
@@ -351,7 +351,7 @@ extern "C" int ao_b200_int4_quantize(const void* w, int64_t N, int64_t K, int64_
 
 extern "C" int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp, int pad_value,
                                  void* packed, void* stream) {
-  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 16 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 128 == 0 && Kp % 64 == 0);
   AO_CHECK_ARG(ao_aligned(packed, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   int4_pack_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -360,7 +360,7 @@ extern "C" int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t
 }
 
 extern "C" int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, int32_t* q, void* stream) {
-  AO_CHECK_ARG(packed && q && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(packed && q && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0);
   AO_CHECK_ARG(ao_aligned(packed, 16) && ao_aligned(q, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   int4_unpack_kernel<false><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -370,7 +370,7 @@ extern "C" int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, i
 
 extern "C" int ao_b200_int4_dequant(const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                                     int group_size, void* out, void* stream) {
-  AO_CHECK_ARG(packed && scale_and_zero && out && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(packed && scale_and_zero && out && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0);
   if (!valid_group(group_size)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0 && ao_aligned(packed, 16) && ao_aligned(out, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;

@@ -2,7 +2,7 @@
 
 * TensorCoreTiledLayout / TensorCoreTiledAQTTensorImpl — int4, drop-in for
   torchao/dtypes/uintx/tensor_core_tiled_layout.py, but the packed weight lives in the B200
-  "strip" layout (include/ao_b200.h) instead of the mma.sync m16n8k16 tinygemm layout, and the
+  "super-tile" layout (include/ao_b200.h) instead of the mma.sync m16n8k16 tinygemm layout, and the
   linear calls torch.ops.torchao.b200_int4_weight_only_mm instead of aten._weight_int4pack_mm.
 * PlainAQTTensorImpl — int8, drop-in for torchao/dtypes/uintx/plain_layout.py (weight-only half).
 """
@@ -33,17 +33,17 @@ __all__ = ["TensorCoreTiledLayout", "TensorCoreTiledAQTTensorImpl", "PlainLayout
 class TensorCoreTiledLayout(Layout):
     """reference: tensor_core_tiled_layout.py:117-188.  `inner_k_tiles` is accepted for API
     compatibility (Int4WeightOnlyConfig's default is TensorCoreTiledLayout(inner_k_tiles=8)); the
-    strip layout has no such knob.  Padding: N -> x16, K -> x max(G, 64) (reference: x8 / x1024)."""
+    super-tile layout has no such knob.  Padding: N -> x128, K -> x max(G, 64) (reference: x8 / x1024)."""
 
     inner_k_tiles: int = 8
 
     def pre_process(self, input: torch.Tensor) -> torch.Tensor:
         n, k = input.shape[-2:]
-        return torch.nn.functional.pad(input, (0, find_multiple(k, 64) - k, 0, find_multiple(n, 16) - n))
+        return torch.nn.functional.pad(input, (0, find_multiple(k, 64) - k, 0, find_multiple(n, 128) - n))
 
     def post_process(self, input, scale, zero_point, block_size):
         n, k = input.shape[-2:]
-        np_, kp = find_multiple(n, 16), find_multiple(k, max(64, block_size[-1]))
+        np_, kp = find_multiple(n, 128), find_multiple(k, max(64, block_size[-1]))
         input = torch.nn.functional.pad(input, (0, kp - k, 0, np_ - n))
         pad_g = (kp - k) // block_size[-1]
         scale = torch.nn.functional.pad(scale, (0, pad_g, 0, np_ - n))
@@ -61,7 +61,7 @@ def _wrapper(cls, like: torch.Tensor, shape):
 
 @register_layout(TensorCoreTiledLayout)
 class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
-    """int4 storage: packed_weight int32 (Np/16, Kp/64, 32, 4) in strip layout + scale_and_zero bf16
+    """int4 storage: packed_weight int32 (Np/128, Kp/64, 8, 32, 4) in super-tile layout + scale_and_zero bf16
     (Kp/G, Np, 2) (same format as the reference's).  reference: tensor_core_tiled_layout.py:191-520."""
 
     def __new__(cls, packed_weight, scale_and_zero, transposed, _layout):
@@ -114,7 +114,7 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
     # -- views ----------------------------------------------------------------------------
     @property
     def padded_shape(self) -> Tuple[int, int]:
-        return self.packed_weight.shape[0] * 16, self.packed_weight.shape[1] * 64
+        return self.packed_weight.shape[0] * 128, self.packed_weight.shape[1] * 64
 
     @property
     def group_size(self) -> int:
@@ -168,19 +168,19 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
         if func is aten.slice.Tensor:
-            # logical (N, K) ranges -> strips / k-tiles / groups (reference: :386-440 does the same on its tiles)
+            # logical (N, K) ranges -> super-strips (128 rows) / k-tiles / groups (reference: :386-440 does the same on its tiles)
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])
             assert step == 1 and dim in (0, 1), f"slice: dim={dim}, step={step} not supported"
             np_, kp = self.padded_shape
             full = np_ if dim == 0 else kp
             start = 0 if start is None else start
             end = full if end is None or end > full else end
-            pw_unit = 16 if dim == 0 else 64
+            pw_unit = 128 if dim == 0 else 64
             sz_unit = 1 if dim == 0 else self.group_size
             if start % pw_unit or start % sz_unit:
                 raise NotImplementedError(f"int4 slice start must be a multiple of {max(pw_unit, sz_unit)} on dim {dim}")
             pw = aten.slice.Tensor(self.packed_weight, dim, start // pw_unit, -(-end // pw_unit), 1)
-            sz_end = pw.shape[0] * 16 + start if dim == 0 else -(-end // sz_unit)
+            sz_end = pw.shape[0] * 128 + start if dim == 0 else -(-end // sz_unit)
             sz = aten.slice.Tensor(self.scale_and_zero, 1 - dim, start // sz_unit, sz_end, 1)
             new = self.__class__(pw.contiguous(), sz.contiguous(), self.transposed, self._layout)
             return return_and_correct_aliasing(func, args, kwargs, new)

@@ -71,9 +71,9 @@ def _round_up(a, b):
 
 
 def padded_int4_shape(n: int, k: int, group_size: int) -> Tuple[int, int]:
-    """Strip layout needs N % 16 == 0 and K % max(G, 64) == 0 (the reference pads to N % 8, K % 1024,
-    tensor_core_tiled_layout.py:127-135; padding only ever adds whole all-zero groups)."""
-    return _round_up(n, 16), _round_up(k, max(group_size, 64))
+    """Super-tile layout needs N % 128 == 0 and K % max(G, 64) == 0 (the reference pads to N % 8, K % 1024,
+    tensor_core_tiled_layout.py:127-135; padding only ever adds whole all-zero groups / all-zero rows)."""
+    return _round_up(n, 128), _round_up(k, max(group_size, 64))
 
 
 def _check_cuda_bf16(t, what):
@@ -177,7 +177,7 @@ def _(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
     _check_group(group_size)
     torch._check(w.dim() == 2, lambda: "weight must be 2-D")
     np_, kp = padded_int4_shape(w.size(0), w.size(1), group_size)
-    return (torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device),
+    return (torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=w.device),
             torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device))
 
 
@@ -187,7 +187,7 @@ def _int4_quantize_pack_cuda(w: Tensor, group_size: int, eps: float, cuda_div_se
     n, k = w.shape
     np_, kp = padded_int4_shape(n, k, group_size)
     w, ldw = _rows(w)
-    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device)
+    packed = torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=w.device)
     sz = torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device)
     with torch.cuda.device(w.device):
         _lib.check(_lib.lib().ao_b200_int4_quantize_pack(
@@ -242,8 +242,8 @@ def _int4_quantize_cuda(w: Tensor, scale: Tensor, zero: Tensor, group_size: int)
 
 @register_custom_op("torchao::b200_int4_pack")
 def _(int_data: Tensor):
-    np_, kp = _round_up(int_data.size(0), 16), _round_up(int_data.size(1), 64)
-    return torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
+    np_, kp = _round_up(int_data.size(0), 128), _round_up(int_data.size(1), 64)
+    return torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=int_data.device)
 
 
 @_impl_cuda("b200_int4_pack")
@@ -251,8 +251,8 @@ def _int4_pack_cuda(int_data: Tensor):
     torch._check(int_data.dim() == 2 and int_data.dtype is torch.int32, lambda: "int_data must be 2-D int32")
     int_data = int_data.contiguous()
     n, k = int_data.shape
-    np_, kp = _round_up(n, 16), _round_up(k, 64)
-    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
+    np_, kp = _round_up(n, 128), _round_up(k, 64)
+    packed = torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=int_data.device)
     with torch.cuda.device(int_data.device):
         _lib.check(_lib.lib().ao_b200_int4_pack(int_data.data_ptr(), n, k, np_, kp, 0, packed.data_ptr(),
                                                 _stream(int_data)), "int4_pack")
@@ -260,10 +260,10 @@ def _int4_pack_cuda(int_data: Tensor):
 
 
 def _strip_shape_checks(packed_w):
-    torch._check(packed_w.dim() == 4 and packed_w.size(2) == 32 and packed_w.size(3) == 4,
-                 lambda: f"strip-layout weight must be (N/16, K/64, 32, 4), got {tuple(packed_w.shape)}")
+    torch._check(packed_w.dim() == 5 and tuple(packed_w.shape[2:]) == (8, 32, 4),
+                 lambda: f"super-tile weight must be (N/128, K/64, 8, 32, 4), got {tuple(packed_w.shape)}")
     torch._check(packed_w.dtype is torch.int32, lambda: f"weight must be INT32, got {packed_w.dtype}")
-    return packed_w.size(0) * 16, packed_w.size(1) * 64
+    return packed_w.size(0) * 128, packed_w.size(1) * 64
 
 
 @register_custom_op("torchao::b200_int4_unpack")
@@ -325,7 +325,7 @@ def _tinygemm_pack_cuda(int_data: Tensor, inner_k_tiles: int):
 
 
 def convert_tinygemm_to_b200(packed_w: Tensor, inner_k_tiles: int) -> Tensor:
-    """Re-tile a weight packed by aten._convert_weight_to_int4pack (reference checkpoints) into the strip layout."""
+    """Re-tile a weight packed by aten._convert_weight_to_int4pack (reference checkpoints) into the super-tile layout."""
     return torch.ops.torchao.b200_int4_pack(unpack_tensor_core_tiled_layout(packed_w, inner_k_tiles))
 
 
@@ -353,7 +353,7 @@ def _workspace(device, nbytes):
 @_impl_cuda("b200_int4_weight_only_mm")
 def _int4_mm_cuda(x: Tensor, packed_w: Tensor, group_size: int, scales_and_zeros: Tensor, out_features: int):
     """Same contract as aten._weight_int4pack_mm(x, packed, G, scale_and_zero)
-    (call site torchao/dtypes/uintx/tensor_core_tiled_layout.py:104) on the strip layout."""
+    (call site torchao/dtypes/uintx/tensor_core_tiled_layout.py:104) on the super-tile layout."""
     np_, kp = _strip_shape_checks(packed_w)
     _sz_checks(scales_and_zeros, np_, kp, group_size)
     _check_cuda_bf16(x, "activation")
