@@ -1,0 +1,399 @@
+"""bench.py — Llama-3-8B int4 (group_size=128) weight-only decode on B200: tok/s + roofline of the GEMV.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload ...]
+
+A "step" is one decoded token at batch size 1: one pass of the hot path (129 weight-only quantized GEMVs
++ the decode glue) over the whole random-init model.  Weights 3.99 GB >> the 126 MB L2, so every step
+streams them from HBM (no L2 flush needed).  Prints ONE JSON line (see the task contract):
+  value      decode tok/s with the token on the device (CUDA-graph replays, CUDA-event timed)
+  e2e        the same through the public Generator.decode_tokens(stream_to_host=True): each step copies the
+             token to feed from pinned host memory and reads the sampled token back to pinned host memory
+  roofline   the dominant kernel (int4 GEMV of the fused w1|w3 projection, 28672x4096) timed live with
+             CUDA events over a graph of that launch on the 32 layers' distinct weights
+  cpu_baseline  the unmodified reference (oracle/_ref) Int4CPULayout path on the host cores, bounded sample
+--impl reference times that CPU path alone (rank 0 only).  N > 1: tensor parallel (tp.py), strong scaling.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "llama3-8b-int4": dict(model="Llama-3-8B", quant="int4", group_size=128),
+    "llama3-8b-int8": dict(model="Llama-3-8B", quant="int8", group_size=None),
+    "llama3-8b-bf16": dict(model="Llama-3-8B", quant="bf16", group_size=None),
+    "llama3-70b-int4": dict(model="Llama-3-70B", quant="int4", group_size=128),
+    "tiny-int4": dict(model="tiny-llama3", quant="int4", group_size=128),
+}
+# reference: torchao/_models/llama/model.py:104-113 (Llama-3-8B); Llama-3-70B = Llama-3.1-70B without scaled rope
+MODEL_DIMS = {
+    "Llama-3-8B": dict(dim=4096, intermediate_size=14336, n_layer=32, n_head=32, n_local_heads=8, head_dim=128, vocab_size=128256),
+    "Llama-3-70B": dict(dim=8192, intermediate_size=28672, n_layer=80, n_head=64, n_local_heads=8, head_dim=128, vocab_size=128256),
+    "tiny-llama3": dict(dim=1024, intermediate_size=2048, n_layer=2, n_head=8, n_local_heads=2, head_dim=128, vocab_size=1024),
+}
+PROMPT_LEN = 8  # reference default prompt "Hello, my name is" ~ 6-8 tokens (generate.py:260)
+
+
+def int4_gemv_bytes(m, n, k, g):
+    """algorithmic bytes of one int4 weight-only GEMM launch"""
+    return n * k // 2 + (k // g) * n * 4 + m * k * 2 + m * n * 2
+
+
+# --------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples SM clock + throttle reasons during the timed region (pynvml; nvidia-smi fallback)."""
+
+    def __init__(self, index=0, period=0.05):
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {}
+        if nv is not None:
+            for nm in dir(nv):
+                if nm.startswith("nvmlClocksThrottleReason") or nm.startswith("nvmlClocksEventReason"):
+                    v = getattr(nv, nm)
+                    if isinstance(v, int) and v:
+                        names[v] = nm.replace("nvmlClocksThrottleReason", "").replace("nvmlClocksEventReason", "")
+        while not self._stop.is_set():
+            try:
+                if nv is not None:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                    for bit, nm in names.items():
+                        if mask & bit and bin(bit).count("1") == 1:
+                            self.reasons.add(nm)
+                else:
+                    out = subprocess.run(["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm,"
+                                          "clocks_event_reasons.active", "--format=csv,noheader,nounits"],
+                                         capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                    self.samples.append(int(out[0]))
+                    self.max_mhz = int(out[1])
+                    self.reasons.add(out[2].strip())
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._thread.join(timeout=5)
+
+    def summary(self):
+        s = [x for x in self.samples if x]
+        idle = {"GpuIdle", "None", "ApplicationsClocksSetting"}
+        return {"sm_mhz": statistics.median(s) if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(r for r in self.reasons if r not in idle), "samples": len(s)}
+
+
+# --------------------------------------------------------------------------------------- CPU reference arm
+def cpu_reference(workload, steps, warmup, budget_s=25.0):
+    """Times the UNMODIFIED reference (oracle/_ref = pip install --target of /root/reference) on the host
+    cores: quantize_(Int4WeightOnlyConfig(group_size, layout=Int4CPULayout())) -> aten._weight_int4pack_mm_for_cpu
+    (torchao/dtypes/uintx/int4_cpu_layout.py:281-316) for the five linears of ONE Llama transformer block at
+    M=1; a decode token = n_layer blocks + the output projection (scaled by weight count)."""
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    kind = "reference"
+    if not os.path.isdir(os.path.join(ref_dir, "torchao")):
+        raise RuntimeError("oracle/_ref (the reference install) is missing; run __graft_entry__.build() where /root/reference exists")
+    sys.path.insert(0, ref_dir)
+    import torch
+    import warnings
+    warnings.filterwarnings("ignore")
+    from torchao.dtypes import Int4CPULayout  # the reference, not this repo
+    from torchao.quantization import Int4WeightOnlyConfig, Int8WeightOnlyConfig, quantize_
+
+    from types import SimpleNamespace
+
+    spec = WORKLOADS[workload]
+    cfg = SimpleNamespace(**MODEL_DIMS[spec["model"]])  # no import of this repo's package in the reference arm
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    torch.set_num_threads(cores)
+    torch.manual_seed(1234)
+    D, I = cfg.dim, cfg.intermediate_size
+    qkv = (cfg.n_head + 2 * cfg.n_local_heads) * cfg.head_dim
+    shapes = [(qkv, D), (D, D), (I, D), (I, D), (D, I)]  # wqkv, wo, w1, w3, w2  (model.py:422-425,481-483)
+    block = torch.nn.ModuleList([torch.nn.Linear(k, n, bias=False, dtype=torch.bfloat16) for n, k in shapes])
+    t0 = time.perf_counter()
+    if spec["quant"] == "int4":
+        quantize_(block, Int4WeightOnlyConfig(group_size=spec["group_size"], layout=Int4CPULayout()))
+    elif spec["quant"] == "int8":
+        quantize_(block, Int8WeightOnlyConfig())
+    t_quant = time.perf_counter() - t0
+    xs = [torch.randn(1, k, dtype=torch.bfloat16) for n, k in shapes]
+
+    def one_block():
+        with torch.no_grad():
+            for lin, x in zip(block, xs):
+                lin(x)
+
+    for _ in range(max(warmup, 3)):
+        one_block()
+    times = []
+    t_start = time.perf_counter()
+    for _ in range(max(steps, 1)):
+        t0 = time.perf_counter()
+        one_block()
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_start > budget_s:
+            break
+    t_block = statistics.median(times)
+    block_w = sum(n * k for n, k in shapes)
+    t_token = t_block * (cfg.n_layer + cfg.vocab_size * D / block_w)
+    return {"value": 1.0 / t_token, "unit": "tok/s", "cores": cores, "kind": kind,
+            "sample": f"{len(times)} timed passes over the 5 quantized linears of 1 of {cfg.n_layer} transformer blocks "
+                      f"at M=1 through the reference's Int4CPULayout path (median {t_block * 1e3:.2f} ms/block); token time = "
+                      f"{cfg.n_layer} blocks + output projection scaled by weight count; attention/norms/sampling excluded; "
+                      f"reference quantize_ of the block took {t_quant:.1f} s",
+            "ms_per_token": t_token * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_reference(args.workload, args.steps, args.warmup)
+    spec = WORKLOADS[args.workload]
+    line = {"impl": "reference", "metric": "llama3_8b_int4_decode_tok_per_s" if args.workload == "llama3-8b-int4" else args.workload + "_decode_tok_per_s",
+            "value": cb["value"], "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": cb["ms_per_token"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16 activations x int4 weights, fp32 accumulate" if spec["quant"] == "int4" else spec["quant"],
+            "data": "synthetic (random-init weights, random activations)",
+            "config": {"workload": args.workload, "batch_size": 1, "group_size": spec["group_size"]},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------- GPU arm
+def build_model(spec, device, tp=None):
+    import torch
+    import torchao_fork_b200 as ao
+    from torchao_fork_b200._models.llama import ModelArgs, Transformer
+
+    cfg = ModelArgs.from_name(spec["model"])
+    torch.manual_seed(1234)  # reference: generate.py:325
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        if tp is not None and tp.world_size > 1:
+            from torchao_fork_b200._models.llama.tp import build_tp_transformer
+            model = build_tp_transformer(cfg, tp, device, spec)
+        else:
+            with torch.device(device):
+                model = Transformer(cfg)
+            model.eval()
+            if spec["quant"] == "int4":
+                ao.quantize_(model, ao.Int4WeightOnlyConfig(group_size=spec["group_size"]))
+            elif spec["quant"] == "int8":
+                ao.quantize_(model, ao.Int8WeightOnlyConfig())
+    finally:
+        torch.set_default_dtype(old)
+    return model, cfg
+
+
+def time_gemv_launch(engine, which, iters):
+    """Average duration of ONE launch of the `which` linear of every layer (distinct weights, > L2 in total),
+    replayed from a CUDA graph, CUDA events on the launching stream."""
+    import torch
+    lins = [l[which] for l in engine.layers if l[which] is not None]
+    lin0 = lins[0]
+    x = torch.randn(engine.B, lin0.k, dtype=torch.bfloat16, device=engine.device)
+    y = torch.empty(engine.B, lin0.n, dtype=torch.bfloat16, device=engine.device)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for lin in lins[:2]:
+            lin.launch(x, y, engine.ws, side.cuda_stream)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        st = torch.cuda.current_stream().cuda_stream
+        for lin in lins:
+            lin.launch(x, y, engine.ws, st)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / (iters * len(lins)), lin0, sum(l.weight_bytes for l in lins)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+    assert torch.cuda.is_available(), "bench.py needs a B200 (there is no CPU fallback path)"
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    tp = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+        from torchao_fork_b200._models.llama.tp import TPContext
+        tp = TPContext(rank, world, device)
+
+    from torchao_fork_b200 import _lib
+    from torchao_fork_b200._models.llama import Generator
+
+    _lib.lib()  # fail loudly now if libao_b200.so is missing
+    spec = WORKLOADS[args.workload]
+    model, cfg = build_model(spec, device, tp)
+    K, W = args.steps, max(args.warmup, 3)
+    max_seq = PROMPT_LEN + 2 * (K + W) + 16
+    gen = Generator(model, args.batch_size, max_seq, temperature=args.temperature, top_k=args.top_k, tp=tp)
+    eng = gen.engine
+    prompt = torch.randint(0, cfg.vocab_size, (PROMPT_LEN,), device=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: tokens stay on the device; K graph replays between CUDA events
+    eng.set_state(prompt[-1:].repeat(args.batch_size), PROMPT_LEN)
+    for _ in range(W):
+        eng.step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        e0.record()
+        for _ in range(K):
+            eng.step()
+        e1.record()
+        barrier()
+    t_dev = e0.elapsed_time(e1) * 1e-3
+    # ---- e2e: public API, token fed from pinned host memory and read back every step
+    for _ in range(W):
+        gen.decode_tokens(1, stream_to_host=True)
+    barrier()
+    t0 = time.perf_counter()
+    host_tokens = gen.decode_tokens(K, stream_to_host=True)
+    barrier()
+    t_e2e = time.perf_counter() - t0
+    assert host_tokens.shape == (args.batch_size, K) and int(host_tokens.min()) >= 0
+    if world > 1:
+        t = torch.tensor([t_dev, t_e2e], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_dev, t_e2e = t.tolist()
+
+    toks = K * args.batch_size
+    line = {"metric": "llama3_8b_int4_decode_tok_per_s" if args.workload == "llama3-8b-int4" else args.workload + "_decode_tok_per_s",
+            "value": toks / t_dev, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": t_dev / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": {"int4": "bf16 activations x int4 weights, fp32 accumulate", "int8": "bf16 x int8 weights, fp32 accumulate",
+                      "bf16": "bf16"}[spec["quant"]],
+            "data": "synthetic (random-init weights, random tokens)",
+            "config": {"workload": args.workload, "batch_size": args.batch_size, "group_size": spec["group_size"],
+                       "prompt_len": PROMPT_LEN, "sampling": f"temperature={args.temperature}, top_k={args.top_k}",
+                       "parallelism": f"tp{world}", "l2": "inputs larger than L2 (weights %.2f GB per step per rank)" % (eng.weight_bytes / 1e9)},
+            "e2e": {"value": toks / t_e2e, "unit": "tok/s", "h2d_bytes_per_step": 8 * args.batch_size,
+                    "d2h_bytes_per_step": 8 * args.batch_size},
+            "gpu_launches": eng.launches_per_step * K,
+            "model_bandwidth_gbs": eng.weight_bytes * world / (t_dev / K) / 1e9,
+            "clocks": clk.summary()}
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+        which = "w13" if eng.layers[0]["w13"] is not None else "w2"
+        t_launch, lin, _ = time_gemv_launch(eng, which, max(10, K // 10))
+        if lin.kind == "int4":
+            alg = int4_gemv_bytes(args.batch_size, lin.n, lin.k, lin.group_size)
+        else:
+            alg = lin.weight_bytes + args.batch_size * (lin.n + lin.k) * 2
+        traffic = None
+        tp_path = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp_path):
+            tr = json.load(open(tp_path))
+            if tr.get("n") == lin.n and tr.get("k") == lin.k and tr.get("kind") == lin.kind:
+                traffic = tr.get("dram_bytes_per_launch")
+        line["roofline"] = {"bound": "hbm", "achieved": alg / t_launch / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": alg / t_launch / 1e9 / peak, "traffic": traffic,
+                            "kernel": f"{lin.kind} weight-only GEMV {lin.n}x{lin.k} (fused w1|w3), M={args.batch_size}",
+                            "algorithmic_bytes_per_launch": alg, "us_per_launch": t_launch * 1e6, "peak_source": peak_src}
+        # all GEMV launches of one step, back to back (share of the step)
+        t_all, b_all = 0.0, 0
+        for nm in ("wqkv", "wo", "w13", "w1", "w3", "w2"):
+            if eng.layers[0][nm] is not None:
+                t1, l1, wb = time_gemv_launch(eng, nm, max(5, K // 20))
+                t_all += t1 * len(eng.layers)
+                b_all += wb
+        line["roofline"]["all_layer_gemvs"] = {"gbs": b_all / t_all / 1e9, "frac": b_all / t_all / 1e9 / peak,
+                                               "share_of_step": t_all / (t_dev / K)}
+        if world == 1 and not args.no_cpu_baseline:
+            # separate process: the reference's torchao and this repo's ops both own the `torchao::` op namespace
+            try:
+                out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload",
+                                      args.workload, "--steps", "40", "--warmup", "3"], capture_output=True, text=True,
+                                     timeout=600, env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
+                ref_line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+                line["cpu_baseline"] = ref_line["cpu_baseline"]
+            except Exception as e:  # the checker is optional at run time; the product path is not
+                line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "reference",
+                                        "sample": f"unavailable: {type(e).__name__}: {e}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)  # reference: 200 new tokens per sample (generate.py:264)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="llama3-8b-int4", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch-size", type=int, default=1)
+    ap.add_argument("--temperature", type=float, default=0.8)
+    ap.add_argument("--top-k", type=int, default=200)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

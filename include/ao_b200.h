@@ -139,6 +139,34 @@ AO_B200_API int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx
                     const int8_t* q, const void* scale, int64_t N,
                     void* y, int64_t ldy, void* stream);
 
+/* ---------------------------------------------------------------- decode-step glue ---- */
+/* The non-GEMM remainder of one Llama decode step (reference:
+ * torchao/_models/llama/model.py).  All of them read the token position from DEVICE memory
+ * (int32 *input_pos) so that one captured CUDA graph can be replayed for every token. */
+
+/* RMSNorm.forward (model.py:489-503) with an optional fused residual add:
+ *   h = bf16(x + residual) (written to h_out when non-NULL);  y = bf16( bf16(h * rsqrt(mean(h^2)+eps)) * weight ).
+ * x, residual, h_out, y: bf16 [rows][dim]; weight bf16 [dim]; dim % 8 == 0. */
+AO_B200_API int ao_b200_rmsnorm(const void* x, const void* residual, const void* weight, void* h_out, void* y,
+                    int64_t rows, int64_t dim, float eps, void* stream);
+
+/* apply_rotary_emb (model.py:547-559) on q and k + KVCache.update (model.py:175-192) for ONE new token.
+ * qkv bf16 [B][(H + 2 Hkv) * head_dim] (the wqkv output), freqs_cis bf16 [block_size][head_dim/2][2],
+ * q_out bf16 [B][H][head_dim], caches bf16 [B][Hkv][S][head_dim]. */
+AO_B200_API int ao_b200_rope_kv_append(const void* qkv, const void* freqs_cis, const int32_t* input_pos, void* q_out,
+                           void* k_cache, void* v_cache, int B, int H, int Hkv, int head_dim, int S, void* stream);
+
+/* scaled_dot_product_attention of one query token against cache positions 0..*input_pos, GQA without
+ * repeat_interleave (model.py:465-470).  head_dim must be 128.  n_split > 1 splits the sequence over CTAs
+ * (workspace: ao_b200_decode_attention_workspace_bytes).  out bf16 [B][H][head_dim]. */
+AO_B200_API int64_t ao_b200_decode_attention_workspace_bytes(int B, int H, int n_split);
+AO_B200_API int ao_b200_decode_attention(const void* q, const void* k_cache, const void* v_cache,
+                             const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim, int S,
+                             float scale, int n_split, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* FeedForward gate (model.py:486): out = bf16( bf16(silu(gate)) * up ), gate_up bf16 [B][2*I] = [w1 x | w3 x]. */
+AO_B200_API int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64_t I, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

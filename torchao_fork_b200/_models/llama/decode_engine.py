@@ -1,0 +1,238 @@
+"""Single-token decode of the gpt-fast Llama through the B200 kernels, captured in one CUDA graph.
+
+The reference gets its decode speed from `torch.compile(decode_one_token, mode="reduce-overhead")`
+(torchao/_models/llama/generate.py:865-875), i.e. inductor + CUDA graphs.  Here there is no tracing compiler:
+DecodeEngine walks the (already quantized) Transformer once, collects raw device pointers of every weight,
+and issues the whole step — embedding gather, per layer [RMSNorm(+residual) -> wqkv -> RoPE+KV append ->
+GQA attention -> wo -> RMSNorm(+residual) -> w1|w3 -> SiLU*mul -> w2], final norm, `output`, sampling —
+as C-ABI kernel launches on the current stream; `capture()` records them into a CUDA graph which
+`step()` replays.  The token position lives in device memory so the same graph serves every token.
+
+w1 and w3 are fused by concatenating their packed rows (row-wise quantization: the fused weight is
+exactly the two quantized weights stacked), which cuts one launch per layer.
+"""
+import math
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from ... import _lib
+from ...dtypes.affine_quantized_tensor import AffineQuantizedTensor
+from ...dtypes.layouts import PlainAQTTensorImpl, TensorCoreTiledAQTTensorImpl
+from .model import Transformer
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+class _Linear:
+    """One (possibly row-fused) weight-only linear: y[B][N] = x[B][K] @ W^T, launched through the C ABI."""
+
+    def __init__(self, weights: List[torch.Tensor]):
+        w0 = weights[0]
+        self.n = sum(int(w.shape[0]) for w in weights)
+        self.k = int(w0.shape[1])
+        if isinstance(w0, AffineQuantizedTensor) and isinstance(w0.tensor_impl, TensorCoreTiledAQTTensorImpl):
+            self.kind = "int4"
+            impls = [w.tensor_impl for w in weights]
+            assert all(not i.transposed for i in impls)
+            self.group_size = impls[0].group_size
+            if len(impls) > 1:
+                assert all(int(w.shape[0]) % 128 == 0 for w in weights[:-1]), "row fusion needs N % 128 == 0"
+                self.packed = torch.cat([i.packed_weight for i in impls], dim=0).contiguous()
+                self.sz = torch.cat([i.scale_and_zero for i in impls], dim=1).contiguous()
+            else:
+                self.packed, self.sz = impls[0].packed_weight, impls[0].scale_and_zero
+            self.np_, self.kp = self.packed.shape[0] * 128, self.packed.shape[1] * 64
+            self.weight_bytes = self.packed.numel() * 4 + self.sz.numel() * 2
+        elif isinstance(w0, AffineQuantizedTensor) and isinstance(w0.tensor_impl, PlainAQTTensorImpl):
+            self.kind = "int8"
+            impls = [w.tensor_impl for w in weights]
+            self.q = torch.cat([i.int_data for i in impls], dim=0).contiguous() if len(impls) > 1 else impls[0].int_data
+            self.scale = torch.cat([i.scale for i in impls], dim=0).contiguous() if len(impls) > 1 else impls[0].scale
+            self.weight_bytes = self.q.numel() + self.scale.numel() * 2
+        else:
+            self.kind = "bf16"  # unquantized line: library GEMM (cuBLAS), for comparison only
+            self.w = torch.cat([w.detach() for w in weights], dim=0).contiguous() if len(weights) > 1 else w0.detach()
+            assert self.w.dtype == torch.bfloat16
+            self.weight_bytes = self.w.numel() * 2
+
+    def workspace_bytes(self, m):
+        if self.kind != "int4":
+            return 0
+        return int(_lib.lib().ao_b200_int4_mm_workspace_bytes(m, self.np_, self.kp))
+
+    def launch(self, x: torch.Tensor, y: torch.Tensor, ws: Optional[torch.Tensor], stream: int):
+        m = x.shape[0]
+        L = _lib.lib()
+        if self.kind == "int4":
+            _lib.check(L.ao_b200_int4_mm(x.data_ptr(), m, self.k, x.stride(0), self.packed.data_ptr(),
+                                         self.sz.data_ptr(), self.np_, self.kp, self.group_size, y.data_ptr(),
+                                         self.n, y.stride(0), _ptr(ws), 0 if ws is None else ws.numel(), stream),
+                       "int4_mm")
+        elif self.kind == "int8":
+            _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, self.k, x.stride(0), self.q.data_ptr(),
+                                         self.scale.data_ptr(), self.n, y.data_ptr(), y.stride(0), stream), "int8_mm")
+        else:
+            torch.mm(x, self.w.t(), out=y)
+
+
+class DecodeEngine:
+    """decode_one_token (generate.py:111-117) + sample (generate.py:79-100) for a fixed batch size."""
+
+    def __init__(self, model: Transformer, batch_size: int = 1, temperature: float = 0.8,
+                 top_k: Optional[int] = 200, tp=None):
+        cfg = model.config
+        assert model.freqs_cis is not None and model.max_batch_size >= batch_size, "call model.setup_caches first"
+        assert cfg.head_dim == 128, "decode attention kernel is specialised for head_dim 128"
+        assert batch_size <= 16, "the decode path covers M <= 16"
+        self.model, self.cfg, self.B = model, cfg, batch_size
+        self.temperature, self.top_k = temperature, top_k
+        self.tp = tp  # tensor-parallel context (tp.py) or None
+        dev = model.tok_embeddings.weight.device
+        self.device = dev
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        B, D = batch_size, cfg.dim
+        first = model.layers[0].attention
+        self.H, self.Hkv, self.hd = first.n_head, first.n_local_heads, cfg.head_dim  # local (per-rank) head counts
+        self.S = model.max_seq_length
+        self.layers = []
+        for blk in model.layers:
+            ff = blk.feed_forward
+            fuse = int(ff.w1.weight.shape[0]) % 128 == 0 and type(ff.w1.weight) is type(ff.w3.weight)
+            self.layers.append(dict(
+                attn_norm=blk.attention_norm.weight.detach(), ffn_norm=blk.ffn_norm.weight.detach(),
+                wqkv=_Linear([blk.attention.wqkv.weight]), wo=_Linear([blk.attention.wo.weight]),
+                w13=_Linear([ff.w1.weight, ff.w3.weight]) if fuse else None,
+                w1=None if fuse else _Linear([ff.w1.weight]), w3=None if fuse else _Linear([ff.w3.weight]),
+                w2=_Linear([ff.w2.weight]),
+                k_cache=blk.attention.kv_cache.k_cache, v_cache=blk.attention.kv_cache.v_cache))
+        self.I = int(model.layers[0].feed_forward.w1.weight.shape[0])
+        self.out_norm = model.norm.weight.detach()
+        self.output = _Linear([model.output.weight])
+        self.emb = model.tok_embeddings.weight.detach()
+        self.eps = cfg.norm_eps
+        self.freqs = model.freqs_cis
+        for t in [self.out_norm, self.emb] + [l["attn_norm"] for l in self.layers]:
+            assert t.dtype == torch.bfloat16, "model must be bf16"
+        # activations (fixed addresses: the graph replays over them)
+        self.tok = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.pos = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.h = torch.zeros(B, D, **bf)
+        self.a = torch.zeros(B, D, **bf)
+        self.qkv = torch.zeros(B, (self.H + 2 * self.Hkv) * self.hd, **bf)
+        self.q = torch.zeros(B, self.H * self.hd, **bf)
+        self.o = torch.zeros(B, self.H * self.hd, **bf)
+        self.delta = torch.zeros(B, D, **bf)
+        self.gu = torch.zeros(B, 2 * self.I, **bf)
+        self.s = torch.zeros(B, self.I, **bf)
+        self.logits = torch.zeros(B, int(model.output.weight.shape[0]), **bf)
+        self.next_tok = torch.zeros(B, dtype=torch.int64, device=dev)
+        lins = [self.output] + [l[k] for l in self.layers for k in ("wqkv", "wo", "w13", "w1", "w3", "w2") if l[k]]
+        ws_bytes = max(l.workspace_bytes(B) for l in lins)
+        self.ws = torch.zeros(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
+        self.n_split = max(1, min(64, -(-self.S // 16)))
+        awb = int(_lib.lib().ao_b200_decode_attention_workspace_bytes(B, self.H, self.n_split))
+        self.attn_ws = torch.zeros(max(awb, 16), dtype=torch.uint8, device=dev)
+        self.weight_bytes = sum(l.weight_bytes for l in lins) + 2 * (
+            self.out_norm.numel() + sum(l["attn_norm"].numel() + l["ffn_norm"].numel() for l in self.layers))
+        self.graph = None
+        self.launches_per_step = 0
+
+    # ------------------------------------------------------------------ one step, eager launches
+    def _mm(self, lin, x, y, stream):
+        lin.launch(x, y, self.ws, stream)
+        self.launches_per_step += 1
+
+    def _launch_step(self):
+        L = _lib.lib()
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        B, D = self.B, self.cfg.dim
+        self.launches_per_step = 0
+        torch.index_select(self.emb, 0, self.tok, out=self.h)
+        residual = None
+        for l in self.layers:
+            _lib.check(L.ao_b200_rmsnorm(self.h.data_ptr(), _ptr(residual), l["attn_norm"].data_ptr(),
+                                         self.h.data_ptr() if residual is not None else None, self.a.data_ptr(),
+                                         B, D, self.eps, st), "rmsnorm")
+            self._mm(l["wqkv"], self.a, self.qkv, st)
+            _lib.check(L.ao_b200_rope_kv_append(self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(),
+                                                self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
+                                                B, self.H, self.Hkv, self.hd, self.S, st), "rope_kv_append")
+            _lib.check(L.ao_b200_decode_attention(self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
+                                                  self.pos.data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd,
+                                                  self.S, 1.0 / math.sqrt(self.hd), self.n_split,
+                                                  self.attn_ws.data_ptr(), self.attn_ws.numel(), st), "decode_attention")
+            self._mm(l["wo"], self.o, self.delta, st)
+            if self.tp is not None:
+                self.tp.all_reduce(self.delta)
+            _lib.check(L.ao_b200_rmsnorm(self.h.data_ptr(), self.delta.data_ptr(), l["ffn_norm"].data_ptr(),
+                                         self.h.data_ptr(), self.a.data_ptr(), B, D, self.eps, st), "rmsnorm")
+            if l["w13"] is not None:
+                self._mm(l["w13"], self.a, self.gu, st)
+            else:
+                self._mm(l["w1"], self.a, self.gu[:, : self.I], st)
+                self._mm(l["w3"], self.a, self.gu[:, self.I:], st)
+            _lib.check(L.ao_b200_silu_mul(self.gu.data_ptr(), self.s.data_ptr(), B, self.I, st), "silu_mul")
+            self._mm(l["w2"], self.s, self.delta, st)
+            if self.tp is not None:
+                self.tp.all_reduce(self.delta)
+            residual = self.delta
+            self.launches_per_step += 5 + (1 if self.n_split > 1 else 0)
+        _lib.check(L.ao_b200_rmsnorm(self.h.data_ptr(), _ptr(residual), self.out_norm.data_ptr(), None,
+                                     self.a.data_ptr(), B, D, self.eps, st), "rmsnorm")
+        self._mm(self.output, self.a, self.logits, st)
+        self.launches_per_step += 1
+        logits = self.logits
+        if self.tp is not None:
+            logits = self.tp.gather_logits(self.logits)
+        self._sample(logits)
+        self.tok.copy_(self.next_tok)
+        self.pos.add_(1)
+
+    def _sample(self, logits):
+        """reference: generate.py:79-100 (temperature, top-k, gumbel-max multinomial)."""
+        if self.temperature == 0.0:
+            torch.argmax(logits, dim=-1, out=self.next_tok)
+            return
+        lg = logits.float() / max(self.temperature, 1e-5)
+        if self.top_k is not None:
+            v, _ = torch.topk(lg, min(self.top_k, lg.size(-1)))
+            lg = torch.where(lg < v[..., -1:], -float("inf"), lg)
+        probs = torch.softmax(lg, dim=-1)
+        q = torch.empty_like(probs).exponential_(1)
+        torch.argmax(probs / q, dim=-1, out=self.next_tok)
+
+    # ------------------------------------------------------------------ graph
+    def capture(self):
+        tok0, pos0 = self.tok.clone(), self.pos.clone()
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(2):  # warm-up (lazy module loads, workspace growth) outside capture
+                self._launch_step()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._launch_step()
+        self.tok.copy_(tok0)
+        self.pos.copy_(pos0)
+        torch.cuda.synchronize(self.device)
+        return self
+
+    def set_state(self, tokens: torch.Tensor, pos: int):
+        """tokens int [B] = the token to feed next; pos = its position in the sequence."""
+        self.tok.copy_(tokens.reshape(-1).to(torch.int64))
+        self.pos.fill_(pos)
+
+    def step(self) -> torch.Tensor:
+        """Runs one decode step; returns the device buffer holding the sampled tokens [B] (overwritten by
+        the next step).  The sampled token is already fed back for the following step."""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._launch_step()
+        return self.next_tok
