@@ -59,6 +59,7 @@ def main():
     ap.add_argument("--group", type=int, default=128)
     ap.add_argument("--shapes", default="8b")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--only", default=None, help="n,k")
     args = ap.parse_args()
     dev = "cuda"
     peak = 6550.7
@@ -66,6 +67,8 @@ def main():
     if os.path.exists(pk):
         peak = json.load(open(pk))["hbm_gbs"]
     shapes = SHAPES_8B if args.shapes == "8b" else SHAPES_70B
+    if args.only:
+        shapes = [tuple(int(v) for v in args.only.split(","))]
     rows = []
     for (n, k) in shapes:
         wbytes = n * k // 2 if not args.int8 else n * k
@@ -84,7 +87,9 @@ def main():
                 kp = (k + 1023) // 1024 * 1024
                 assert kp == k
                 pa = torch.ops.aten._convert_weight_to_int4pack(u8, 8)
-                was = [(pa.clone(), sz.clone()) for _ in range(copies)]
+                from torchao_fork_b200.ops import sz_b200_to_tinygemm
+                szr = sz_b200_to_tinygemm(sz)
+                was = [(pa.clone(), szr.clone()) for _ in range(copies)]
         del w
         for m in args.m:
             x = torch.randn(m, k, dtype=torch.bfloat16, device=dev)

@@ -16,19 +16,21 @@
  * bf16 tensors are passed as `const void*` to 2-byte elements, row-major.
  *
  * HBM layouts
- *   "super-tile" layout (this library's int4 weight format), uint32 [Np/128][Kp/64][8][32][4]:
- *       super-tile (S, kt) = 128 rows x 64 k = 4096 contiguous bytes (one TMA bulk copy), made of
- *       8 sub-tiles r of 16 rows x 64 k = 512 bytes; inside a sub-tile lane l = (g = l>>2, c = l&3)
- *       owns 16 bytes; word j of the lane: row = 128 S + 16 r + g + 8 (j&1),
- *       k0 = 64 kt + 32 (j>>1) + 8 c, and holds k0..k0+7 in nibble slots
- *       [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7] (slot i = bits 4i..4i+3) so that
- *       "(w >> 4i) & 0x000f000f" yields the pair (k0+2i, k0+2i+1).  Np % 128 == 0, Kp % 64 == 0.
- *       A lane's 4 words are exactly the A-operand rows (g, g+8) of two m16n8k16 MMAs per k-half,
- *       and each word is one 16-byte chunk of a K-major UMMA shared-memory operand row.
- *   scale_and_zero: bf16 [Kp/G][Np][2] = (scale, zero) — identical to the reference's
- *       pack_tinygemm_scales_and_zeros (torchao/quantization/utils.py:395-409).
- *   "tinygemm" layout: int32 [N/8][K/(ikt*16)][32][ikt/2], the output format of
- *       aten._convert_weight_to_int4pack (tensor_core_tiled_layout.cu:128-215).
+ *   strip-major int4 weight (this library's format), uint32 [Np/16][Kp/64][32][4]:
+ *       strip s (16 rows) x k-tile kt (64 k) = one 512-byte sub-tile; ALL sub-tiles of a strip are contiguous
+ *       (Kp * 8 bytes), so a CTA that owns a range of strips streams one contiguous byte range with large TMA bulk
+ *       copies.  Inside a sub-tile lane l = (g = l>>2, c = l&3) owns 16 bytes; word j of the lane:
+ *       row = 16 s + g + 8 (j&1), k0 = 64 kt + 32 (j>>1) + 8 c, and holds k0..k0+7 in nibble slots
+ *       [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7] (slot i = bits 4i..4i+3) so that "(w >> 4i) & 0x000f000f" yields
+ *       the pair (k0+2i, k0+2i+1).  A lane's 4 words are exactly the A-operand rows (g, g+8) of two m16n8k16 MMAs
+ *       per k-half, and each word is one 16-byte chunk of a K-major UMMA shared-memory operand row.
+ *       Np % 16 == 0 (the host pads to 128), Kp % 64 == 0.
+ *   scale_and_zero, strip-major: bf16 [Np/16][Kp/G][16][2] = (scale, zero) — the numbers of the reference's
+ *       pack_tinygemm_scales_and_zeros (torchao/quantization/utils.py:395-409, [Kp/G][Np][2]) with the 16 rows of a
+ *       strip made contiguous, so a strip's qparams for a K range are one contiguous copy.
+ *   "tinygemm" layout: int32 [N/8][K/(ikt*16)][32][ikt/2] + scale_and_zero bf16 [K/G][N][2], the formats of
+ *       aten._convert_weight_to_int4pack / pack_tinygemm_scales_and_zeros (tensor_core_tiled_layout.cu:128-215);
+ *       only the ao_b200_tinygemm_* functions take them.
  */
 #ifndef AO_B200_H_
 #define AO_B200_H_
@@ -70,8 +72,8 @@ AO_B200_API int ao_b200_abi_version(void);
  * TensorCoreTiledAQTTensorImpl.from_plain (tensor_core_tiled_layout.py:262-307):
  * one pass over W.  w: bf16 [N][K] with row stride ldw (elements, % 8 == 0).
  * Rows >= N / columns >= K of the padded [Np][Kp] problem read as zero.
- * Outputs: packed (super-tile layout, Np x Kp), scale_and_zero bf16 [Kp/G][Np][2].
- * G in {32,64,128,256}; K % G == 0; Kp % max(G,64) == 0; Np % 128 == 0. */
+ * Outputs: packed (strip-major, Np x Kp), scale_and_zero bf16 strip-major [Np/16][Kp/G][16][2].
+ * G in {32,64,128,256}; K % G == 0; Kp % max(G,64) == 0; Np % 16 == 0. */
 AO_B200_API int ao_b200_int4_quantize_pack(const void* w, int64_t N, int64_t K, int64_t ldw,
                                int64_t Np, int64_t Kp, int group_size, float eps, int div_mode,
                                void* packed, void* scale_and_zero, void* stream);
@@ -86,12 +88,12 @@ AO_B200_API int ao_b200_int4_quantize(const void* w, int64_t N, int64_t K, int64
 
 /* ---------------------------------------------------------------- int4: layouts ----- */
 
-/* from_plain: q int32 [N][K] (values 0..15; rows>=N / cols>=K pad with `pad_value`) -> super-tile layout. */
+/* from_plain: q int32 [N][K] (values 0..15; rows>=N / cols>=K pad with `pad_value`) -> strip-major layout. */
 AO_B200_API int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp,
                       int pad_value, void* packed, void* stream);
-/* super-tile layout -> int32 [Np][Kp]. */
+/* strip-major layout -> int32 [Np][Kp]. */
 AO_B200_API int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, int32_t* q, void* stream);
-/* super-tile layout + scale_and_zero -> bf16 [Np][Kp], W' = bf16_rn((q-8)*s + z) (single rounding,
+/* strip-major layout + strip-major scale_and_zero -> bf16 [Np][Kp], W' = bf16_rn((q-8)*s + z) (single rounding,
  * the dequant of aten._weight_int4pack_mm; tensor_core_tiled_layout.cu:41-117,194). */
 AO_B200_API int ao_b200_int4_dequant(const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                          int group_size, void* out, void* stream);
@@ -123,6 +125,23 @@ AO_B200_API int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ld
                     const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                     int group_size, void* y, int64_t N_out, int64_t ldy,
                     void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Decode-path GEMV (M <= 16) with the neighbouring element-wise ops of the Llama block fused in
+ * (reference: torchao/_models/llama/model.py:405-408,486,489-503):
+ *   norm_weight != NULL : the activation is RMSNorm(x) * norm_weight (RMSNorm.forward), computed in the prologue
+ *                         (x * norm_weight rounded to bf16; rsqrt(mean(x^2)+eps) applied to the fp32 result);
+ *   epilogue 0 (plain)  : y[m][n] = bf16(acc)
+ *   epilogue 1 (residual): y[m][n] = bf16(residual[m][n] + bf16(acc))          (h = x + attention(...), y may alias residual)
+ *   epilogue 2 (silu*mul): the packed weight holds w1 and w3 interleaved 8 rows / 8 rows per 16-row strip
+ *                         (ops.interleave_gate_up); y[m][i] = bf16(bf16(silu(bf16(gate_i))) * bf16(up_i)), i < N_out/2.
+ * Arithmetic: the affine dequant is applied per group in fp32 to the tensor-core partial sums (the fp32 dequant of
+ * the reference's _weight_int4pack_mm_for_cpu) — see csrc/gemv_int4_fused.cu.  Returns AO_B200_ERR_WORKSPACE when
+ * M * K does not fit the kernel's shared-memory staging (use ao_b200_int4_mm then). */
+AO_B200_API int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx,
+                            const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
+                            int group_size, void* y, int64_t N_out, int64_t ldy,
+                            const void* norm_weight, float norm_eps, const void* residual, int64_t ld_res,
+                            int epilogue, void* stream);
 
 /* ---------------------------------------------------------------- int8 -------------- */
 

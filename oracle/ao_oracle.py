@@ -281,38 +281,53 @@ def unpack_tinygemm(packed, inner_k_tiles=8):
     return q
 
 
-# ---- the B200 "super-tile" layout (this build's own; see DESIGN.md "HBM layout") ----
-# packed uint32 [N/128][K/64][8][32][4]: super-tile (S, kt) = 128 rows x 64 k = 4096 contiguous bytes,
-# made of 8 sub-tiles r (16 rows each, 512 bytes); in a sub-tile lane l=(g=l>>2, c=l&3) owns 16 bytes,
-# word j:  row = 128*S + 16*r + g + 8*(j&1);  k0 = 64*kt + 32*(j>>1) + 8*c;  word holds k0..k0+7.
+# ---- the B200 strip-major layout (this build's own; see DESIGN.md "Data layout in HBM") ----
+# packed uint32 [N/16][K/64][32][4]: strip s (16 rows) x k-tile kt (64 k) = one 512-byte sub-tile; all sub-tiles of a
+# strip are contiguous.  In a sub-tile lane l=(g=l>>2, c=l&3) owns 16 bytes; word j:
+#   row = 16*s + g + 8*(j&1);  k0 = 64*kt + 32*(j>>1) + 8*c;  the word holds k0..k0+7 (nibble order of _pack_words).
 def pack_b200(q):
     n, k = q.shape
-    assert n % 128 == 0 and k % 64 == 0
+    assert n % 16 == 0 and k % 64 == 0
     lane = np.arange(32)
     g, c = lane >> 2, lane & 3
-    out = np.zeros((n // 128, k // 64, 8, 32, 4), dtype=np.uint32)
-    q6 = q.reshape(n // 128, 8, 16, k // 64, 8, 8)   # [S][r][row][kt][chunk][8]
+    out = np.zeros((n // 16, k // 64, 32, 4), dtype=np.uint32)
+    q5 = q.reshape(n // 16, 16, k // 64, 8, 8)        # [s][row][kt][chunk][8]
     for j in range(4):
         rows = g + 8 * (j & 1)
         chunks = c + 4 * (j >> 1)
-        vals = q6[:, :, rows, :, chunks, :]           # -> [32][S][r][kt][8]
-        out[:, :, :, :, j] = _pack_words(vals).transpose(1, 3, 2, 0)
+        vals = q5[:, rows, :, chunks, :]               # -> [32][s][kt][8]
+        out[:, :, :, j] = _pack_words(vals).transpose(1, 2, 0)
     return out.view(np.int32)
 
 
 def unpack_b200(packed):
     p = packed.view(np.uint32)
     s_, kt_ = p.shape[0], p.shape[1]
-    n, k = s_ * 128, kt_ * 64
+    n, k = s_ * 16, kt_ * 64
     lane = np.arange(32)
     g, c = lane >> 2, lane & 3
-    q6 = np.zeros((s_, 8, 16, kt_, 8, 8), dtype=np.int32)
+    q5 = np.zeros((s_, 16, kt_, 8, 8), dtype=np.int32)
     for j in range(4):
         rows = g + 8 * (j & 1)
         chunks = c + 4 * (j >> 1)
-        vals = _unpack_words(p[:, :, :, :, j])        # [S][kt][r][32][8]
-        q6[:, :, rows, :, chunks, :] = vals.transpose(3, 0, 2, 1, 4)
-    return q6.reshape(n, k)
+        vals = _unpack_words(p[:, :, :, j])            # [s][kt][32][8]
+        q5[:, rows, :, chunks, :] = vals.transpose(2, 0, 1, 3)
+    return q5.reshape(n, k)
+
+
+def pack_scales_and_zeros_b200(scale, zero):
+    """scale, zero [N][K/G] -> strip-major [N/16][K/G][16][2]: the numbers of the reference's
+    pack_tinygemm_scales_and_zeros (torchao/quantization/utils.py:395-409, [K/G][N][2]) with the 16 rows of a
+    strip contiguous."""
+    n, ng = scale.shape
+    sz = np.stack([scale, zero], axis=-1)              # [N][NG][2]
+    return np.ascontiguousarray(sz.reshape(n // 16, 16, ng, 2).transpose(0, 2, 1, 3))
+
+
+def unpack_scales_and_zeros_b200(sz):
+    s16, ng = sz.shape[0], sz.shape[1]
+    t = sz.transpose(0, 2, 1, 3).reshape(s16 * 16, ng, 2)
+    return np.ascontiguousarray(t[..., 0]), np.ascontiguousarray(t[..., 1])
 
 
 # --------------------------------------------------------------------------

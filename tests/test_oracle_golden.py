@@ -108,15 +108,24 @@ def test_layout_round_trips(shape):
     rng = np.random.default_rng(shape[1])
     q = rng.integers(0, 16, shape).astype(np.int32)
     p = o.pack_b200(q)
-    assert p.shape == (shape[0] // 128, shape[1] // 64, 8, 32, 4)
+    assert p.shape == (shape[0] // 16, shape[1] // 64, 32, 4)
     assert np.array_equal(o.unpack_b200(p), q)
     # the layout definition of include/ao_b200.h, spelled out element by element
     pu = p.view(np.uint32)
-    for (S, kt, r, lane, j) in [(0, 0, 0, 0, 0), (shape[0] // 128 - 1, shape[1] // 64 - 1, 7, 31, 3), (0, 0, 5, 13, 2)]:
+    for (st, kt, lane, j) in [(0, 0, 0, 0), (shape[0] // 16 - 1, shape[1] // 64 - 1, 31, 3), (5, 0, 13, 2)]:
         g, c = lane >> 2, lane & 3
-        row, k0 = 128 * S + 16 * r + g + 8 * (j & 1), 64 * kt + 32 * (j >> 1) + 8 * c
-        w = int(pu[S, kt, r, lane, j])
+        row, k0 = 16 * st + g + 8 * (j & 1), 64 * kt + 32 * (j >> 1) + 8 * c
+        w = int(pu[st, kt, lane, j])
         assert [(w >> (4 * s)) & 15 for s in (0, 4, 1, 5, 2, 6, 3, 7)] == list(q[row, k0:k0 + 8])
+    # strip-major qparams are a pure permutation of the reference's (K/G, N, 2) tensor
+    sc = rng.standard_normal((shape[0], shape[1] // 32)).astype(np.float32)
+    zr = rng.standard_normal((shape[0], shape[1] // 32)).astype(np.float32)
+    szb = o.pack_scales_and_zeros_b200(sc, zr)
+    assert szb.shape == (shape[0] // 16, shape[1] // 32, 16, 2)
+    s2, z2 = o.unpack_scales_and_zeros_b200(szb)
+    assert np.array_equal(s2, sc) and np.array_equal(z2, zr)
+    ref = o.pack_scales_and_zeros(sc, zr)
+    assert np.array_equal(szb[3, 1, 7], ref[1, 3 * 16 + 7])
     if shape[1] % 128 == 0:
         for ikt in (2, 4, 8):
             assert np.array_equal(o.unpack_tinygemm(o.pack_tinygemm(q, ikt), ikt), q)

@@ -30,8 +30,9 @@ def _ptr(t: Optional[torch.Tensor]):
 class _Linear:
     """One (possibly row-fused) weight-only linear: y[B][N] = x[B][K] @ W^T, launched through the C ABI."""
 
-    def __init__(self, weights: List[torch.Tensor]):
+    def __init__(self, weights: List[torch.Tensor], interleave_gate_up: bool = False):
         w0 = weights[0]
+        self.interleaved = False
         self.n = sum(int(w.shape[0]) for w in weights)
         self.k = int(w0.shape[1])
         if isinstance(w0, AffineQuantizedTensor) and isinstance(w0.tensor_impl, TensorCoreTiledAQTTensorImpl):
@@ -39,13 +40,19 @@ class _Linear:
             impls = [w.tensor_impl for w in weights]
             assert all(not i.transposed for i in impls)
             self.group_size = impls[0].group_size
-            if len(impls) > 1:
+            if interleave_gate_up:
+                from ...ops import interleave_gate_up as _ilv
+                assert len(impls) == 2 and int(weights[0].shape[0]) % 128 == 0
+                self.packed, self.sz = _ilv(impls[0].packed_weight, impls[0].scale_and_zero,
+                                            impls[1].packed_weight, impls[1].scale_and_zero)
+                self.interleaved = True
+            elif len(impls) > 1:
                 assert all(int(w.shape[0]) % 128 == 0 for w in weights[:-1]), "row fusion needs N % 128 == 0"
                 self.packed = torch.cat([i.packed_weight for i in impls], dim=0).contiguous()
-                self.sz = torch.cat([i.scale_and_zero for i in impls], dim=1).contiguous()
+                self.sz = torch.cat([i.scale_and_zero for i in impls], dim=0).contiguous()
             else:
                 self.packed, self.sz = impls[0].packed_weight, impls[0].scale_and_zero
-            self.np_, self.kp = self.packed.shape[0] * 128, self.packed.shape[1] * 64
+            self.np_, self.kp = self.packed.shape[0] * 16, self.packed.shape[1] * 64
             self.weight_bytes = self.packed.numel() * 4 + self.sz.numel() * 2
         elif isinstance(w0, AffineQuantizedTensor) and isinstance(w0.tensor_impl, PlainAQTTensorImpl):
             self.kind = "int8"
@@ -63,6 +70,17 @@ class _Linear:
         if self.kind != "int4":
             return 0
         return int(_lib.lib().ao_b200_int4_mm_workspace_bytes(m, self.np_, self.kp))
+
+    def launch_fused(self, x, y, stream, norm_w=None, eps=0.0, residual=None, epilogue=0):
+        """ao_b200_int4_gemv_fused: RMSNorm prologue (norm_w), epilogue 0 plain / 1 residual add / 2 SiLU*mul."""
+        assert self.kind == "int4"
+        _lib.check(_lib.lib().ao_b200_int4_gemv_fused(
+            x.data_ptr(), x.shape[0], self.k, x.stride(0), self.packed.data_ptr(), self.sz.data_ptr(), self.np_,
+            self.kp, self.group_size, y.data_ptr(), self.n, y.stride(0), _ptr(norm_w), eps, _ptr(residual),
+            0 if residual is None else residual.stride(0), epilogue, stream), "int4_gemv_fused")
+
+    def fused_fits(self, m):
+        return self.kind == "int4" and m * (2 * self.kp + 16) <= 150 * 1024
 
     def launch(self, x: torch.Tensor, y: torch.Tensor, ws: Optional[torch.Tensor], stream: int):
         m = x.shape[0]
@@ -83,7 +101,7 @@ class DecodeEngine:
     """decode_one_token (generate.py:111-117) + sample (generate.py:79-100) for a fixed batch size."""
 
     def __init__(self, model: Transformer, batch_size: int = 1, temperature: float = 0.8,
-                 top_k: Optional[int] = 200, tp=None):
+                 top_k: Optional[int] = 200, tp=None, fused: bool = True):
         cfg = model.config
         assert model.freqs_cis is not None and model.max_batch_size >= batch_size, "call model.setup_caches first"
         assert cfg.head_dim == 128, "decode attention kernel is specialised for head_dim 128"
@@ -99,13 +117,16 @@ class DecodeEngine:
         self.H, self.Hkv, self.hd = first.n_head, first.n_local_heads, cfg.head_dim  # local (per-rank) head counts
         self.S = model.max_seq_length
         self.layers = []
+        probe = [_Linear([model.layers[0].attention.wqkv.weight]), _Linear([model.layers[0].feed_forward.w2.weight])]
+        self.fused = (fused and all(l.fused_fits(batch_size) for l in probe)
+                      and int(model.layers[0].feed_forward.w1.weight.shape[0]) % 128 == 0)
         for blk in model.layers:
             ff = blk.feed_forward
             fuse = int(ff.w1.weight.shape[0]) % 128 == 0 and type(ff.w1.weight) is type(ff.w3.weight)
             self.layers.append(dict(
                 attn_norm=blk.attention_norm.weight.detach(), ffn_norm=blk.ffn_norm.weight.detach(),
                 wqkv=_Linear([blk.attention.wqkv.weight]), wo=_Linear([blk.attention.wo.weight]),
-                w13=_Linear([ff.w1.weight, ff.w3.weight]) if fuse else None,
+                w13=_Linear([ff.w1.weight, ff.w3.weight], interleave_gate_up=self.fused) if fuse else None,
                 w1=None if fuse else _Linear([ff.w1.weight]), w3=None if fuse else _Linear([ff.w3.weight]),
                 w2=_Linear([ff.w2.weight]),
                 k_cache=blk.attention.kv_cache.k_cache, v_cache=blk.attention.kv_cache.v_cache))
@@ -146,7 +167,47 @@ class DecodeEngine:
         lin.launch(x, y, self.ws, stream)
         self.launches_per_step += 1
 
+    def _launch_step_fused(self):
+        """5 GEMVs + RoPE/KV-append + attention per layer: the two RMSNorms, both residual adds and SiLU*mul live in
+        the GEMV prologues / epilogues (include/ao_b200.h, ao_b200_int4_gemv_fused)."""
+        L = _lib.lib()
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        B = self.B
+        n = 0
+        torch.index_select(self.emb, 0, self.tok, out=self.h)
+        for l in self.layers:
+            l["wqkv"].launch_fused(self.h, self.qkv, st, norm_w=l["attn_norm"], eps=self.eps)
+            _lib.check(L.ao_b200_rope_kv_append(self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(),
+                                                self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
+                                                B, self.H, self.Hkv, self.hd, self.S, st), "rope_kv_append")
+            _lib.check(L.ao_b200_decode_attention(self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
+                                                  self.pos.data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd,
+                                                  self.S, 1.0 / math.sqrt(self.hd), self.n_split,
+                                                  self.attn_ws.data_ptr(), self.attn_ws.numel(), st), "decode_attention")
+            if self.tp is None:
+                l["wo"].launch_fused(self.o, self.h, st, residual=self.h, epilogue=1)
+            else:
+                l["wo"].launch_fused(self.o, self.delta, st)
+                self.tp.all_reduce_add(self.delta, self.h)
+            l["w13"].launch_fused(self.h, self.s, st, norm_w=l["ffn_norm"], eps=self.eps, epilogue=2)
+            if self.tp is None:
+                l["w2"].launch_fused(self.s, self.h, st, residual=self.h, epilogue=1)
+            else:
+                l["w2"].launch_fused(self.s, self.delta, st)
+                self.tp.all_reduce_add(self.delta, self.h)
+            n += 6 + (1 if self.n_split > 1 else 0)
+        self.output.launch_fused(self.h, self.logits, st, norm_w=self.out_norm, eps=self.eps)
+        self.launches_per_step = n + 1
+        logits = self.logits
+        if self.tp is not None:
+            logits = self.tp.gather_logits(self.logits)
+        self._sample(logits)
+        self.tok.copy_(self.next_tok)
+        self.pos.add_(1)
+
     def _launch_step(self):
+        if self.fused:
+            return self._launch_step_fused()
         L = _lib.lib()
         st = torch.cuda.current_stream(self.device).cuda_stream
         B, D = self.B, self.cfg.dim

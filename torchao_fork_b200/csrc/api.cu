@@ -4,10 +4,9 @@
 namespace ao {
 int int4_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
               int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, cudaStream_t s);
-int int4_gemv_stream(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz,
-                     int64_t Np, int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, void* workspace,
-                     int64_t workspace_bytes, int stages, bool pdl, cudaStream_t s);
-int64_t int4_gemv_stream_workspace_bytes(int64_t Np);
+int int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+                    int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
+                    const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
 int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
               void* y, int64_t ldy, cudaStream_t s);
 }  // namespace ao
@@ -31,11 +30,11 @@ struct Tunables {
   int gemv_version, stages, pdl;
   Tunables() {
     const char* v = std::getenv("AO_B200_GEMV");
-    gemv_version = v ? std::atoi(v) : 2;
+    gemv_version = v ? std::atoi(v) : 3;
     const char* st = std::getenv("AO_B200_STAGES");
     stages = st ? std::atoi(st) : 8;
     if (stages < 2) stages = 2;
-    if (stages > 9) stages = 9;
+    if (stages > 16) stages = 16;
     const char* pd = std::getenv("AO_B200_PDL");
     pdl = pd ? std::atoi(pd) : 1;
   }
@@ -47,17 +46,18 @@ const Tunables& tunables() {
 }  // namespace
 
 extern "C" int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
-  (void)M; (void)Kp;
-  return ao::int4_gemv_stream_workspace_bytes(Np);
+  (void)M; (void)Np; (void)Kp;
+  return 0;  // the strip-parallel GEMVs reduce inside the CTA: no cross-CTA workspace (kept in the ABI for split-K kernels)
 }
 
 extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
                                const void* scale_and_zero, int64_t Np, int64_t Kp, int group_size, void* y,
                                int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, void* stream) {
   AO_CHECK_ARG(x && packed && scale_and_zero && y);
-  AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
+  AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
   AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx && ldy >= N_out);
-  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 4) && ao_aligned(y, 2));
+  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 64) && ao_aligned(y, 2));
+  (void)workspace; (void)workspace_bytes;
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0);
   auto s = static_cast<cudaStream_t>(stream);
@@ -65,17 +65,38 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   auto yb = static_cast<__nv_bfloat16*>(y);
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
-    int e;
-    if (tunables().gemv_version == 1)
-      e = ao::int4_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out,
-                        ldy, s);
-    else
-      e = ao::int4_gemv_stream(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size,
-                               yb + m0 * ldy, N_out, ldy, workspace, workspace_bytes, tunables().stages,
-                               tunables().pdl != 0, s);
+    int e = AO_B200_ERR_WORKSPACE;
+    if (tunables().gemv_version == 3) {
+      e = ao::int4_gemv_fused(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
+                              N_out, ldy, nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
+      if (e == AO_B200_OK) continue;
+      if (e != AO_B200_ERR_WORKSPACE) return e;
+    }
+    e = ao::int4_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out,
+                      ldy, s);
     if (e) return e;
   }
   return AO_B200_OK;
+}
+
+extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
+                                       const void* scale_and_zero, int64_t Np, int64_t Kp, int group_size, void* y,
+                                       int64_t N_out, int64_t ldy, const void* norm_weight, float norm_eps,
+                                       const void* residual, int64_t ld_res, int epilogue, void* stream) {
+  AO_CHECK_ARG(x && packed && scale_and_zero && y);
+  AO_CHECK_ARG(M > 0 && M <= 16 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
+  AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx);
+  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 64));
+  AO_CHECK_ARG(epilogue >= 0 && epilogue <= 2);
+  AO_CHECK_ARG(epilogue != 1 || residual != nullptr);
+  AO_CHECK_ARG(epilogue != 2 || (N_out % 16 == 0 && ldy >= N_out / 2));
+  AO_CHECK_ARG(epilogue == 2 || ldy >= N_out);
+  AO_CHECK_ARG(!norm_weight || ao_aligned(norm_weight, 16));
+  if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
+  AO_CHECK_ARG(Kp % group_size == 0);
+  return ao::int4_gemv_fused(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
+                             norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,
+                             static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale,

@@ -127,14 +127,18 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
-// super-tile layout addressing: 16-row strip s16 = 8*S + r, k-tile kt -> index of the 512-byte sub-tile
+// strip-major layout addressing: 16-row strip s16, k-tile kt -> index of the 512-byte sub-tile.  All of a strip's
+// sub-tiles are contiguous (K * 8 bytes), so a CTA that owns a range of strips streams one contiguous byte range.
 __host__ __device__ __forceinline__ int64_t tile_slot(int64_t s16, int64_t kt, int64_t k_tiles) {
-  return ((s16 >> 3) * k_tiles + kt) * 8 + (s16 & 7);
+  return s16 * k_tiles + kt;
 }
 __host__ __device__ __forceinline__ void tile_of_slot(int64_t slot, int64_t k_tiles, int64_t& s16, int64_t& kt) {
-  const int64_t r = slot & 7, st = slot >> 3;
-  kt = st % k_tiles;
-  s16 = (st / k_tiles) * 8 + r;
+  s16 = slot / k_tiles;
+  kt = slot - s16 * k_tiles;
+}
+// scale_and_zero, strip-major: uint32 (scale | zero << 16) [Np/16][n_groups][16 rows]
+__host__ __device__ __forceinline__ int64_t sz_index(int64_t grp, int64_t row, int64_t n_groups) {
+  return ((row >> 4) * n_groups + grp) * 16 + (row & 15);
 }
 
 // nibble slot of value i (0..7) inside a word

@@ -48,8 +48,8 @@ __global__ void __launch_bounds__(kGemvWarps * 32) int4_gemv_strip_kernel(
         for (int h = 0; h < 2; ++h) {
           const int64_t grp = (kt * 64 + 32 * h) / G;
           const bool need = ok && (h == 0 || G == 32);
-          szv[u][h][0] = need ? __ldg(sz + grp * Np + row_lo) : 0u;
-          szv[u][h][1] = need ? __ldg(sz + grp * Np + row_lo + 8) : 0u;
+          szv[u][h][0] = need ? __ldg(sz + sz_index(grp, row_lo, Kp / G)) : 0u;
+          szv[u][h][1] = need ? __ldg(sz + sz_index(grp, row_lo + 8, Kp / G)) : 0u;
         }
         if (G != 32) {
           szv[u][1][0] = szv[u][0][0];

@@ -1,0 +1,548 @@
+// int4 weight-only linear, decode path (M <= 16) — v3: strip-parallel, TMA-bulk ring, deferred-affine dequant,
+// fused RMSNorm prologue and residual / SiLU*mul epilogues, PDL-chained.
+//
+//   y[m][n] = sum_g [ s[g][n] * sum_{k in g} x[m][k] * (q[n][k] - 8)  +  z[g][n] * sum_{k in g} x[m][k] ]
+//
+// i.e. the affine dequant (q-8)*s+z is applied ONCE PER GROUP in fp32 to the tensor-core partial sum instead of
+// once per weight in bf16 (that is the arithmetic of the reference's CPU op _weight_int4pack_mm_for_cpu, which
+// dequantises in fp32 without rounding W' to bf16 — SURVEY.md §8 a15; the CUDA op rounds W' to bf16 first, a10;
+// the two differ by the bf16 rounding of each W', well inside the stated GEMM tolerance).  What is left per packed
+// word is 3 shifts + 4 lop3 (nibble -> bf16 value 128+q with the 0x4300 magic) + one mma.sync: half the issue
+// slots of the exact per-weight bf16 fma, which is what made v2 ALU-bound at ~54 % of HBM peak.
+//     sum x*(q-8) = sum x*(128+q) - 136 * X_g,   X_g = sum_{k in g} x[k]  (computed once per CTA from the staged x)
+//
+// Decomposition: a work item is one 16-row strip over the whole K; CTA b owns strips [b*S/B, (b+1)*S/B).  No
+// cross-CTA reduction, no workspace, deterministic.  The layout is strip-major, so the CTA's share is ONE contiguous
+// byte range of the weight (and of the scale/zero tensor): the producer issues one 16 KB cp.async.bulk plus one
+// <= 4 KB scale/zero copy per stage into a shared-memory ring (many small bulk copies measured ~40 ns each and
+// lost DRAM page locality: 20 % of HBM peak); 8 consumer warps split every 32-k-tile stage 4 k-tiles each, and one (rotating) warp sums the 8 partials of
+// a finished strip and runs the epilogue while the others go on.  The ring is sized so two CTAs of consecutive
+// kernels fit on one SM: with programmatic dependent launch the next GEMV's weights are already in shared memory
+// when the previous kernel retires (weights never depend on the previous kernel; x, y do -> griddepcontrol.wait).
+#include <cuda_fp16.h>
+
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace ao {
+
+constexpr int kFConsumers = 16;
+constexpr int kFThreads = (kFConsumers + 1) * 32;
+constexpr int kStageTiles = 32;            // k-tiles (of 64 k) per stage: 16 KB of weights
+constexpr int kTilesPerWarp = kStageTiles / kFConsumers;  // 2 k-tiles = 128 k per warp per stage
+
+enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSiluMul = 2 };
+
+struct GemvFusedParams {
+  const uint8_t* packed;      // strip-major [Np/16][Kp/64][512 B]
+  const uint32_t* sz;         // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
+  const __nv_bfloat16* x;     // [M][ldx]
+  const __nv_bfloat16* norm_w;  // [Kx] or null: x_eff = bf16(x * norm_w), result scaled by rsqrt(mean(x^2)+eps)
+  const __nv_bfloat16* residual;  // [M][ld_res] or null (kEpiResidual)
+  __nv_bfloat16* y;
+  int M, stages, epilogue, copy_split;
+  int KT;                     // Kp / 64
+  int64_t Kx, ldx, Np, N_out, ldy, ld_res;
+  int n_strips;               // Np / 16
+  float eps;
+  uint32_t x_row_bytes;       // 2 * Kp + 16
+  uint32_t off_x, off_X, off_red, off_misc;  // shared-memory carve-up (bytes)
+};
+
+template <int G>
+__host__ __device__ constexpr int stage_sz_bytes() { return (kStageTiles * 64 / G) * 64; }
+template <int G>
+__host__ __device__ constexpr int stage_bytes() { return kStageTiles * 512 + stage_sz_bytes<G>(); }
+
+__device__ __forceinline__ float warp_sum_f(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// D(16x8, f32) += A(16x16, f16, row) * B(16x8, f16, col)
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// (w & mask) | 0x64006400: a nibble pair OR-ed into the mantissa of fp16 1024.0 (ulp 1, 10 mantissa bits):
+// mask 0x000f000f -> 1024 + q, mask 0x00f000f0 -> 1024 + 16 q.  Two of the four nibble alignments of a word need no
+// shift at all and the other two share one (w >> 8): 5 ALU-pipe ops per 8 weights (bf16's 7-bit mantissa needs 7).
+__device__ __forceinline__ uint32_t nib_f16_lo(uint32_t w) {
+  uint32_t h;
+  asm("lop3.b32 %0, %1, 0x000f000f, 0x64006400, 0xea;" : "=r"(h) : "r"(w));
+  return h;
+}
+__device__ __forceinline__ uint32_t nib_f16_hi(uint32_t w) {
+  uint32_t h;
+  asm("lop3.b32 %0, %1, 0x00f000f0, 0x64006400, 0xea;" : "=r"(h) : "r"(w));
+  return h;
+}
+__device__ __forceinline__ float warp_max_f(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <int G, int MT>
+__global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_kernel(const GemvFusedParams p) {
+  constexpr int kStageB = stage_bytes<G>();
+  constexpr int SEG = G < 128 ? G : 128;  // the correction sums are kept per min(G, 128) k: a warp owns 128 k of a stage
+  constexpr int U32 = SEG / 32;           // 32-k halves per accumulation segment
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* ring = smem;
+  uint8_t* x_s = smem + p.off_x;                                // [M][x_row_bytes]: bf16 while staging, then scaled fp16
+  float* X_s = reinterpret_cast<float*>(smem + p.off_X);        // [Kp/SEG][2 = {X, C}][8*MT]
+  float* red = reinterpret_cast<float*>(smem + p.off_red);      // [2][16 warps][MT][32][4]
+  float* part = reinterpret_cast<float*>(smem + p.off_misc);    // [16 rows][16 warps][2 = {sum sq, amax}]
+  float* row_scale = part + 16 * kFConsumers * 2;               // [16]: 2^e (* rsqrt(mean sq + eps))
+  float* row_dn = row_scale + 16;                               // [16]: 2^-e
+  uint64_t* full = reinterpret_cast<uint64_t*>(row_dn + 16);
+  uint64_t* empty = full + p.stages;
+  uint64_t* red_full = empty + p.stages;                        // [2]
+  uint64_t* red_free = red_full + 2;                            // [2]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = p.stages;
+  const int B = gridDim.x, b = blockIdx.x;
+  const int s0 = (int)(((int64_t)b * p.n_strips) / B), s1 = (int)(((int64_t)(b + 1) * p.n_strips) / B);
+  const int KT = p.KT;
+  const int n_chunks = (KT + kStageTiles - 1) / kStageTiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kFConsumers);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&red_full[s], kFConsumers);
+      mbar_init(&red_free[s], 1);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  grid_launch_dependents();
+
+  if (warp == kFConsumers) {
+    // ===================== producer: lane 0 owns the barriers; `copy_split` lanes share the weight copy ===============
+    {
+      int slot = 0;
+      uint32_t par = 1;
+      const int n_groups = KT * 64 / G;
+      const int split = p.copy_split;
+      for (int strip = s0; strip < s1; ++strip) {
+        const uint8_t* wrow = p.packed + (int64_t)strip * KT * 512;
+        const uint32_t* srow = p.sz + (int64_t)strip * n_groups * 16;
+        for (int ch = 0; ch < n_chunks; ++ch) {
+          const int kt0 = ch * kStageTiles;
+          const int cnt = min(kStageTiles, KT - kt0);
+          const int n_grp = cnt * 64 / G;
+          uint8_t* wdst = ring + (size_t)slot * kStageB;
+          if (lane == 0) {
+            mbar_wait(&empty[slot], par);
+            mbar_arrive_expect_tx(&full[slot], (uint32_t)(cnt * 512 + n_grp * 64));
+            bulk_g2s(wdst + kStageTiles * 512, srow + (int64_t)(kt0 * 64 / G) * 16, (uint32_t)(n_grp * 64), &full[slot]);
+          }
+          __syncwarp();
+          if (lane < split) {
+            const int per = (cnt + split - 1) / split;           // k-tiles per piece
+            const int t0 = lane * per, t1 = min(cnt, t0 + per);
+            if (t1 > t0)
+              bulk_g2s(wdst + t0 * 512, wrow + (int64_t)(kt0 + t0) * 512, (uint32_t)((t1 - t0) * 512), &full[slot]);
+          }
+          if (++slot == stages) {
+            slot = 0;
+            par ^= 1u;
+          }
+        }
+      }
+    }
+    __syncwarp();
+    grid_dependency_wait();  // every kernel of a PDL chain must wait before it exits (transitive ordering)
+    return;
+  }
+
+  // ===================== consumers =====================
+  const int g = lane >> 2, c = lane & 3;
+  const int tid = threadIdx.x;  // 0 .. 511
+  constexpr int kCT = kFConsumers * 32;
+  grid_dependency_wait();
+
+  // ---- stage the activations: x (* norm_w) -> per-row power-of-two scaling -> fp16, the entries that meet a
+  //      "1024 + 16 q" weight pre-divided by 16; then the per-segment correction sums ----
+  {
+    const int chunks_per_row = KT * 8;  // 16-byte chunks of 8 elements over Kp
+    for (int m = 0; m < p.M; ++m) {
+      float ss = 0.f, amax = 0.f;
+      for (int ci = tid; ci < chunks_per_row; ci += kCT) {
+        const int64_t k0 = (int64_t)ci * 8;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (k0 < p.Kx) v = *reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0);
+        float f[8];
+        unpack8(v, f);
+        if (p.norm_w != nullptr && k0 < p.Kx) {
+          float wn[8];
+          unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            ss = fmaf(f[e], f[e], ss);
+            f[e] = bf16r(f[e] * wn[e]);
+          }
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
+          v = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
+        *reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16) = v;
+      }
+      ss = warp_sum_f(ss);
+      amax = warp_max_f(amax);
+      if (lane == 0) {
+        part[(m * kFConsumers + warp) * 2] = ss;
+        part[(m * kFConsumers + warp) * 2 + 1] = amax;
+      }
+    }
+    named_bar_sync(1, kCT);
+    if (tid < p.M) {
+      float t = 0.f, amax = 0.f;
+#pragma unroll
+      for (int w = 0; w < kFConsumers; ++w) {
+        t += part[(tid * kFConsumers + w) * 2];
+        amax = fmaxf(amax, part[(tid * kFConsumers + w) * 2 + 1]);
+      }
+      // 2^e: brings the row's largest magnitude to [2^13, 2^14): every bf16 value within 2^-27 of it is exact in fp16
+      int e = 0;
+      if (amax > 0.f) e = (int)((__float_as_uint(amax) >> 23) & 0xFF) - 127 - 13;
+      e = max(-100, min(100, e));
+      const float up = __uint_as_float((uint32_t)(e + 127) << 23), dn = __uint_as_float((uint32_t)(127 - e) << 23);
+      row_dn[tid] = dn;
+      row_scale[tid] = (p.norm_w != nullptr) ? up * rsqrtf(t / (float)p.Kx + p.eps) : up;
+    }
+    named_bar_sync(1, kCT);
+    for (int m = 0; m < p.M; ++m) {
+      const float dn = row_dn[m], dn16 = dn * 0.0625f;
+      for (int ci = tid; ci < chunks_per_row; ci += kCT) {
+        uint4* ptr = reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16);
+        float f[8];
+        unpack8(*ptr, f);
+        // element pairs (0,1),(4,5) meet "1024 + q" weights, pairs (2,3),(6,7) meet "1024 + 16 q" weights
+        const __half2 h0 = __floats2half2_rn(f[0] * dn, f[1] * dn), h1 = __floats2half2_rn(f[2] * dn16, f[3] * dn16);
+        const __half2 h2 = __floats2half2_rn(f[4] * dn, f[5] * dn), h3 = __floats2half2_rn(f[6] * dn16, f[7] * dn16);
+        *ptr = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                          *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+      }
+    }
+    named_bar_sync(1, kCT);
+    // X[seg][m] = sum of the scaled activations, C[seg][m] = 1024 * (sum of the STORED values) + 8 * X:
+    //   sum_k x_k (q_k - 8) = (MMA result) - C
+    const int n_segs = KT * 64 / SEG;
+    constexpr int EPL = SEG / 32;  // elements per lane (1, 2 or 4: never straddles a pair)
+    for (int pi = warp; pi < n_segs * 8 * MT; pi += kFConsumers) {
+      const int sg = pi / (8 * MT), m = pi % (8 * MT);
+      float xs = 0.f, xt = 0.f;
+      if (m < p.M) {
+        const int k_in = lane * EPL;  // offset inside the segment (multiple of EPL)
+        const __half* src = reinterpret_cast<const __half*>(x_s + (size_t)m * p.x_row_bytes) + (size_t)sg * SEG + k_in;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const float v = __half2float(src[e]);
+          const bool x16 = ((k_in + e) & 2) != 0;  // positions 2,3,6,7 of every 8
+          xs += v;
+          xt += x16 ? v * 16.f : v;
+        }
+        xs = warp_sum_f(xs);
+        xt = warp_sum_f(xt);
+      }
+      if (lane == 0) {
+        X_s[(sg * 2 + 0) * 8 * MT + m] = xt;
+        X_s[(sg * 2 + 1) * 8 * MT + m] = fmaf(1024.f, xs, 8.f * xt);
+      }
+    }
+    named_bar_sync(1, kCT);
+  }
+
+  // activation rows of the two MMA column blocks: columns m >= M are never stored, so their lanes may read any valid
+  // row (MMA columns are independent) -> no predicate in the loop
+  const uint8_t* xrow[MT];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) xrow[mt] = x_s + (size_t)min(g + 8 * mt, p.M - 1) * p.x_row_bytes + c * 16;
+  const int tl0 = warp * kTilesPerWarp;  // this warp's first k-tile inside a stage
+  int slot = 0;
+  uint32_t par = 0;
+  for (int strip = s0; strip < s1; ++strip) {
+    float yacc[MT][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) yacc[mt][e] = 0.f;
+
+    for (int ch = 0; ch < n_chunks; ++ch) {
+      const int kt0 = ch * kStageTiles;
+      const int cnt = min(kStageTiles, KT - kt0);
+      const uint8_t* stage = ring + (size_t)slot * kStageB;
+      const uint32_t* ssrc = reinterpret_cast<const uint32_t*>(stage + kStageTiles * 512);
+      const int kbase = (kt0 + tl0) * 64;  // first k of this warp's share of the stage
+      mbar_wait(&full[slot], par);
+      if (tl0 < cnt) {
+        uint4 wv[kTilesPerWarp];
+#pragma unroll
+        for (int t = 0; t < kTilesPerWarp; ++t)
+          wv[t] = (tl0 + t < cnt) ? *reinterpret_cast<const uint4*>(stage + (tl0 + t) * 512 + lane * 16)
+                                  : make_uint4(0, 0, 0, 0);
+        // kChains independent accumulators per segment: consecutive mma.sync on ONE accumulator serialise on the
+        // (long) HMMA latency; the partial sums are added when the segment is complete
+        constexpr int kChains = (2 * U32 >= 4) ? 4 : 2 * U32;  // MMAs per segment = 2 * U32
+        float accg[kChains][MT][4];
+#pragma unroll
+        for (int t = 0; t < kTilesPerWarp; ++t) {
+          const uint32_t words[4] = {wv[t].x, wv[t].y, wv[t].z, wv[t].w};
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int q32 = 2 * t + h;  // 32-k half inside the warp's 128 k
+            const int j0 = (2 * (q32 % U32)) % kChains, j1 = (2 * (q32 % U32) + 1) % kChains;
+            const bool first0 = 2 * (q32 % U32) < kChains, first1 = 2 * (q32 % U32) + 1 < kChains;
+            const uint32_t wl = words[2 * h], wh = words[2 * h + 1];  // rows g and g + 8
+            const uint32_t wl8 = wl >> 8, wh8 = wh >> 8;
+            const uint32_t a0l = nib_f16_lo(wl), a1l = nib_f16_hi(wl), a2l = nib_f16_lo(wl8), a3l = nib_f16_hi(wl8);
+            const uint32_t a0h = nib_f16_lo(wh), a1h = nib_f16_hi(wh), a2h = nib_f16_lo(wh8), a3h = nib_f16_hi(wh8);
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+              const uint4 xx = *reinterpret_cast<const uint4*>(xrow[mt] + (size_t)(kbase + 32 * q32) * 2);
+              if (first0) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) accg[j0][mt][e] = 0.f;
+              }
+              mma_f16_16816(accg[j0][mt], a0l, a0h, a1l, a1h, xx.x, xx.y);
+              if (first1) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) accg[j1][mt][e] = 0.f;
+              }
+              mma_f16_16816(accg[j1][mt], a2l, a2h, a3l, a3h, xx.z, xx.w);
+            }
+            if (q32 % U32 == U32 - 1 && (tl0 + t < cnt)) {
+              // segment complete: y += s * (acc - C) + z * X   (fp32)
+              const int k_seg = kbase + 32 * (q32 - (U32 - 1));  // first k of the segment
+              const int gl = (k_seg - kt0 * 64) / G;               // group inside the stage
+              const uint32_t p0 = ssrc[gl * 16 + g], p1 = ssrc[gl * 16 + g + 8];
+              const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
+              const float z0 = __uint_as_float(p0 & 0xFFFF0000u), z1 = __uint_as_float(p1 & 0xFFFF0000u);
+              const float* Xp = X_s + (k_seg / SEG) * 2 * 8 * MT + 2 * c;
+#pragma unroll
+              for (int mt = 0; mt < MT; ++mt) {
+                float a[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  a[e] = accg[0][mt][e];
+#pragma unroll
+                  for (int j = 1; j < kChains; ++j) a[e] += accg[j][mt][e];
+                }
+                const float2 X = *reinterpret_cast<const float2*>(Xp + 8 * mt);
+                const float2 C = *reinterpret_cast<const float2*>(Xp + 8 * MT + 8 * mt);
+                yacc[mt][0] = fmaf(sc0, a[0] - C.x, fmaf(z0, X.x, yacc[mt][0]));
+                yacc[mt][1] = fmaf(sc0, a[1] - C.y, fmaf(z0, X.y, yacc[mt][1]));
+                yacc[mt][2] = fmaf(sc1, a[2] - C.x, fmaf(z1, X.x, yacc[mt][2]));
+                yacc[mt][3] = fmaf(sc1, a[3] - C.y, fmaf(z1, X.y, yacc[mt][3]));
+              }
+            }
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (++slot == stages) {
+        slot = 0;
+        par ^= 1u;
+      }
+    }
+
+    // ---- strip done: the 16 partials go to shared memory; ONE (rotating) warp sums them and runs the epilogue while
+    //      the others go straight on to the next strip (mbarrier hand-off, no rendezvous) ----
+    const int li = strip - s0;
+    const int rbuf = li & 1;
+    const uint32_t use = (uint32_t)(li >> 1);  // n-th use of this buffer
+    float* rb = red + (size_t)rbuf * (kFConsumers * MT * 128);
+    if (use > 0) mbar_wait(&red_free[rbuf], (use - 1) & 1u);  // the reducer of two strips ago has read it
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+      *reinterpret_cast<float4*>(rb + ((warp * MT + mt) * 32 + lane) * 4) =
+          make_float4(yacc[mt][0], yacc[mt][1], yacc[mt][2], yacc[mt][3]);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&red_full[rbuf]);
+    if (warp == (li % kFConsumers)) {
+      mbar_wait(&red_full[rbuf], use & 1u);
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int w = 0; w < kFConsumers; ++w) {
+          const float4 v = *reinterpret_cast<const float4*>(rb + ((w * MT + mt) * 32 + lane) * 4);
+          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        if (mt == MT - 1) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&red_free[rbuf]);
+        }
+        const float vals[2][2] = {{s.x, s.z}, {s.y, s.w}};  // [col j][row half]: rows g, g+8
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int m = 8 * mt + 2 * c + j;
+          if (m >= p.M) continue;
+          const float rsc = row_scale[m];
+          const float v0 = vals[j][0] * rsc, v1 = vals[j][1] * rsc;
+          if (p.epilogue == kEpiSiluMul) {
+            // rows g = gate (w1), rows g+8 = up (w3) of output index 8*strip + g  (model.py:486)
+            const int64_t n = 8 * (int64_t)strip + g;
+            if (2 * n < p.N_out) {
+              const float gate = bf16r(v0), up = bf16r(v1);
+              const float sg = bf16r(gate / (1.f + __expf(-gate)));
+              p.y[m * p.ldy + n] = __float2bfloat16_rn(sg * up);
+            }
+          } else {
+            const int64_t n0 = 16 * (int64_t)strip + g;
+            if (p.epilogue == kEpiResidual) {
+              if (n0 < p.N_out)
+                p.y[m * p.ldy + n0] = __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0]) + bf16r(v0));
+              if (n0 + 8 < p.N_out)
+                p.y[m * p.ldy + n0 + 8] =
+                    __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0 + 8]) + bf16r(v1));
+            } else {
+              if (n0 < p.N_out) p.y[m * p.ldy + n0] = __float2bfloat16_rn(v0);
+              if (n0 + 8 < p.N_out) p.y[m * p.ldy + n0 + 8] = __float2bfloat16_rn(v1);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+static int fused_sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n = v > 0 ? v : kNumSMs;
+  }
+  return n;
+}
+
+struct FusedPlan {
+  int stages;
+  size_t smem;
+  uint32_t off_x, off_X, off_red, off_misc, x_row_bytes;
+};
+
+// shared-memory plan; returns false when the activations do not fit (caller falls back to the strip kernel)
+template <int G>
+static bool plan_fused(int M, int MT, int64_t Kp, int max_stages, FusedPlan& pl) {
+  const size_t stage_b = stage_bytes<G>();
+  pl.x_row_bytes = (uint32_t)(2 * Kp + 16);
+  const size_t x_bytes = ((size_t)M * pl.x_row_bytes + 127) / 128 * 128;
+  const size_t X_bytes = ((size_t)(Kp / (G < 128 ? G : 128)) * 2 * 8 * MT * 4 + 127) / 128 * 128;
+  const size_t red_bytes = (size_t)2 * kFConsumers * MT * 128 * 4;
+  const size_t misc = (16 * kFConsumers * 2 + 32) * 4 + (2 * 16 + 4) * 8 + 64;
+  const size_t fixed = x_bytes + X_bytes + red_bytes + misc;
+  static const size_t two_per_sm = []() {  // AO_B200_SMEM_KB: shared-memory budget per CTA (default: two CTAs per SM)
+    const char* e = std::getenv("AO_B200_SMEM_KB");
+    return (size_t)(e ? std::atoi(e) : 113) * 1024;
+  }();
+  const size_t one_per_sm = 226 * 1024;
+  int st = 0;
+  if (fixed + 4 * stage_b <= two_per_sm) {
+    st = (int)((two_per_sm - fixed) / stage_b);
+  } else if (fixed + 3 * stage_b <= one_per_sm) {
+    st = (int)((one_per_sm - fixed) / stage_b);
+  } else {
+    return false;
+  }
+  if (st > max_stages) st = max_stages;
+  if (st > 16) st = 16;
+  pl.stages = st;
+  size_t off = (size_t)st * stage_b;
+  pl.off_x = (uint32_t)off; off += x_bytes;
+  pl.off_X = (uint32_t)off; off += X_bytes;
+  pl.off_red = (uint32_t)off; off += red_bytes;
+  pl.off_misc = (uint32_t)off; off += misc;
+  pl.smem = off;
+  return true;
+}
+
+template <int G, int MT>
+static int launch_fused(GemvFusedParams& p, const FusedPlan& pl, bool pdl, cudaStream_t s) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(int4_gemv_fused_kernel<G, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+        cudaSuccess)
+      return AO_B200_ERR_CUDA;
+    attr_done = true;
+  }
+  const int grid = p.n_strips < fused_sm_count() ? p.n_strips : fused_sm_count();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kFThreads);
+  cfg.dynamicSmemBytes = pl.smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  if (cudaLaunchKernelEx(&cfg, int4_gemv_fused_kernel<G, MT>, p) != cudaSuccess) return AO_B200_ERR_CUDA;
+  return ao_launch_status();
+}
+
+// returns AO_B200_ERR_WORKSPACE when the shape does not fit this kernel (caller may fall back)
+int int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+                    int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
+                    const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s) {
+  GemvFusedParams p;
+  p.packed = static_cast<const uint8_t*>(packed);
+  p.sz = static_cast<const uint32_t*>(sz);
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.norm_w = static_cast<const __nv_bfloat16*>(norm_w);
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.y = static_cast<__nv_bfloat16*>(y);
+  p.M = (int)M;
+  p.epilogue = epilogue;
+  p.KT = (int)(Kp / 64);
+  p.Kx = Kx; p.ldx = ldx; p.Np = Np; p.N_out = N_out; p.ldy = ldy; p.ld_res = ld_res;
+  p.n_strips = (int)(Np / 16);
+  p.eps = eps;
+  const int MT = M <= 8 ? 1 : 2;
+  FusedPlan pl;
+  bool ok = false;
+  switch (G) {
+    case 32: ok = plan_fused<32>((int)M, MT, Kp, max_stages, pl); break;
+    case 64: ok = plan_fused<64>((int)M, MT, Kp, max_stages, pl); break;
+    case 128: ok = plan_fused<128>((int)M, MT, Kp, max_stages, pl); break;
+    case 256: ok = plan_fused<256>((int)M, MT, Kp, max_stages, pl); break;
+    default: return AO_B200_ERR_UNSUPPORTED;
+  }
+  if (!ok) return AO_B200_ERR_WORKSPACE;
+  p.stages = pl.stages;
+  {
+    static const int cs = []() { const char* e = std::getenv("AO_B200_COPY_SPLIT"); int v = e ? std::atoi(e) : 1; return v < 1 ? 1 : (v > 32 ? 32 : v); }();
+    p.copy_split = cs;
+  }
+  p.x_row_bytes = pl.x_row_bytes;
+  p.off_x = pl.off_x; p.off_X = pl.off_X; p.off_red = pl.off_red; p.off_misc = pl.off_misc;
+#define AO_LF(GG) return MT == 1 ? launch_fused<GG, 1>(p, pl, pdl, s) : launch_fused<GG, 2>(p, pl, pdl, s)
+  switch (G) {
+    case 32: AO_LF(32);
+    case 64: AO_LF(64);
+    case 128: AO_LF(128);
+    case 256: AO_LF(256);
+  }
+#undef AO_LF
+  return AO_B200_ERR_UNSUPPORTED;
+}
+
+}  // namespace ao

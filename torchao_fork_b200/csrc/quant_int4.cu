@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) int4_quantize_pack_kernel(
         for (int gi = 0; gi < NG; ++gi) {
           const int64_t row = strip * 16 + g + 8 * r;
           const int64_t grp = uk * NG + gi;
-          sz[grp * Np + row] = float_to_bf16_bits(qp[r][gi].scale) | (float_to_bf16_bits(qp[r][gi].zero) << 16);
+          sz[sz_index(grp, row, Kp / G)] = float_to_bf16_bits(qp[r][gi].scale) | (float_to_bf16_bits(qp[r][gi].zero) << 16);
         }
     }
   }
@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(256) int4_unpack_kernel(const uint4* __restric
       const int64_t row = strip * 16 + g + 8 * (j & 1);
       const int64_t k0 = kt * 64 + 32 * (j >> 1) + 8 * c;
       if constexpr (kDequant) {
-        const uint32_t p = sz[(k0 / G) * Np + row];
+        const uint32_t p = sz[sz_index(k0 / G, row, Kp / G)];
         const uint32_t s2 = __byte_perm(p, p, 0x1010), z2 = __byte_perm(p, p, 0x3232);
         uint32_t d[4];
         dequant_word(words[j], s2, z2, d);
@@ -311,7 +311,7 @@ extern "C" int ao_b200_int4_quantize_pack(const void* w, int64_t N, int64_t K, i
   AO_CHECK_ARG(N > 0 && K > 0 && Np >= N && Kp >= K);
   if (!valid_group(group_size)) return AO_B200_ERR_UNSUPPORTED;
   const int64_t uk = group_size > 64 ? group_size : 64;
-  AO_CHECK_ARG(K % group_size == 0 && Kp % uk == 0 && Np % 128 == 0);
+  AO_CHECK_ARG(K % group_size == 0 && Kp % uk == 0 && Np % 16 == 0);
   AO_CHECK_ARG(ldw % 8 == 0 && ao_aligned(w, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 4));
   AO_CHECK_ARG(div_mode == AO_B200_DIV_IEEE || div_mode == AO_B200_DIV_RECIP);
   const int64_t units = (Np / 16) * (Kp / uk);
@@ -351,7 +351,7 @@ extern "C" int ao_b200_int4_quantize(const void* w, int64_t N, int64_t K, int64_
 
 extern "C" int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp, int pad_value,
                                  void* packed, void* stream) {
-  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 128 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 16 == 0 && Kp % 64 == 0);
   AO_CHECK_ARG(ao_aligned(packed, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   int4_pack_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -360,7 +360,7 @@ extern "C" int ao_b200_int4_pack(const int32_t* q, int64_t N, int64_t K, int64_t
 }
 
 extern "C" int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, int32_t* q, void* stream) {
-  AO_CHECK_ARG(packed && q && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(packed && q && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0);
   AO_CHECK_ARG(ao_aligned(packed, 16) && ao_aligned(q, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;
   int4_unpack_kernel<false><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -370,7 +370,7 @@ extern "C" int ao_b200_int4_unpack(const void* packed, int64_t Np, int64_t Kp, i
 
 extern "C" int ao_b200_int4_dequant(const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                                     int group_size, void* out, void* stream) {
-  AO_CHECK_ARG(packed && scale_and_zero && out && Np > 0 && Kp > 0 && Np % 128 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(packed && scale_and_zero && out && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0);
   if (!valid_group(group_size)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0 && ao_aligned(packed, 16) && ao_aligned(out, 16));
   const int64_t total = (Np / 16) * (Kp / 64) * 32;

@@ -2,7 +2,7 @@
 
 * TensorCoreTiledLayout / TensorCoreTiledAQTTensorImpl — int4, drop-in for
   torchao/dtypes/uintx/tensor_core_tiled_layout.py, but the packed weight lives in the B200
-  "super-tile" layout (include/ao_b200.h) instead of the mma.sync m16n8k16 tinygemm layout, and the
+  strip-major layout (include/ao_b200.h) instead of the mma.sync m16n8k16 tinygemm layout, and the
   linear calls torch.ops.torchao.b200_int4_weight_only_mm instead of aten._weight_int4pack_mm.
 * PlainAQTTensorImpl — int8, drop-in for torchao/dtypes/uintx/plain_layout.py (weight-only half).
 """
@@ -33,7 +33,7 @@ __all__ = ["TensorCoreTiledLayout", "TensorCoreTiledAQTTensorImpl", "PlainLayout
 class TensorCoreTiledLayout(Layout):
     """reference: tensor_core_tiled_layout.py:117-188.  `inner_k_tiles` is accepted for API
     compatibility (Int4WeightOnlyConfig's default is TensorCoreTiledLayout(inner_k_tiles=8)); the
-    super-tile layout has no such knob.  Padding: N -> x128, K -> x max(G, 64) (reference: x8 / x1024)."""
+    strip-major layout has no such knob.  Padding: N -> x128, K -> x max(G, 64) (reference: x8 / x1024)."""
 
     inner_k_tiles: int = 8
 
@@ -61,8 +61,9 @@ def _wrapper(cls, like: torch.Tensor, shape):
 
 @register_layout(TensorCoreTiledLayout)
 class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
-    """int4 storage: packed_weight int32 (Np/128, Kp/64, 8, 32, 4) in super-tile layout + scale_and_zero bf16
-    (Kp/G, Np, 2) (same format as the reference's).  reference: tensor_core_tiled_layout.py:191-520."""
+    """int4 storage, both strip-major (include/ao_b200.h): packed_weight int32 (Np/16, Kp/64, 32, 4) and
+    scale_and_zero bf16 (Np/16, Kp/G, 16, 2) — the numbers of the reference's (Kp/G, Np, 2) tensor with the 16
+    rows of a strip made contiguous (ops.sz_b200_to_tinygemm converts).  reference: tensor_core_tiled_layout.py:191-520."""
 
     def __new__(cls, packed_weight, scale_and_zero, transposed, _layout):
         return _wrapper(cls, packed_weight, packed_weight.shape)
@@ -100,7 +101,7 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         group_size = k // scale.shape[1]
         int_data, scale, zero_point = _layout.post_process(int_data, scale, zero_point, (1, group_size))
         packed = torch.ops.torchao.b200_int4_pack(int_data)
-        sz = pack_tinygemm_scales_and_zeros(scale.to(torch.bfloat16), zero_point.to(torch.bfloat16), torch.bfloat16)
+        sz = _ops.pack_scales_and_zeros_b200(scale, zero_point)
         return cls(packed, sz, False, _layout)
 
     @classmethod
@@ -108,17 +109,18 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         """Adopt a weight packed by the reference (aten._convert_weight_to_int4pack) — checkpoint interchange."""
         q = _ops.unpack_tensor_core_tiled_layout(packed_weight, inner_k_tiles)
         s, z = unpack_tinygemm_scales_and_zeros(scale_and_zero)
-        return cls.from_plain(q, s.squeeze(-1).contiguous(), z.squeeze(-1).contiguous(),
+        n = q.shape[0]
+        return cls.from_plain(q, s.reshape(n, -1).contiguous(), z.reshape(n, -1).contiguous(),
                               _layout or TensorCoreTiledLayout(inner_k_tiles))
 
     # -- views ----------------------------------------------------------------------------
     @property
     def padded_shape(self) -> Tuple[int, int]:
-        return self.packed_weight.shape[0] * 128, self.packed_weight.shape[1] * 64
+        return self.packed_weight.shape[0] * 16, self.packed_weight.shape[1] * 64
 
     @property
     def group_size(self) -> int:
-        return self.padded_shape[1] // self.scale_and_zero.shape[0]
+        return self.padded_shape[1] // self.scale_and_zero.shape[1]
 
     @property
     def block_size(self):
@@ -129,8 +131,8 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         int_data with an identity matmul + re-quantize (tensor_core_tiled_layout.py:465-517); here it
         is a plain unpack kernel (exact by construction)."""
         int_data = torch.ops.torchao.b200_int4_unpack(self.packed_weight)
-        s, z = unpack_tinygemm_scales_and_zeros(self.scale_and_zero)
-        return int_data, s.squeeze(-1).contiguous(), z.squeeze(-1).contiguous()
+        s, z = _ops.unpack_scales_and_zeros_b200(self.scale_and_zero)
+        return int_data, s, z
 
     def get_layout(self):
         return self._layout
@@ -168,20 +170,23 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
         if func is aten.slice.Tensor:
-            # logical (N, K) ranges -> super-strips (128 rows) / k-tiles / groups (reference: :386-440 does the same on its tiles)
+            # logical (N, K) ranges -> 16-row strips / 64-wide k-tiles / groups (reference: :386-440 does the same on
+            # its tiles).  Both tensors are strip-major: dim 0 = strip, dim 1 = k-tile (weight) or group (qparams).
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])
             assert step == 1 and dim in (0, 1), f"slice: dim={dim}, step={step} not supported"
             np_, kp = self.padded_shape
             full = np_ if dim == 0 else kp
             start = 0 if start is None else start
             end = full if end is None or end > full else end
-            pw_unit = 128 if dim == 0 else 64
-            sz_unit = 1 if dim == 0 else self.group_size
+            pw_unit = 16 if dim == 0 else 64
+            sz_unit = 16 if dim == 0 else self.group_size
             if start % pw_unit or start % sz_unit:
                 raise NotImplementedError(f"int4 slice start must be a multiple of {max(pw_unit, sz_unit)} on dim {dim}")
+            if dim == 1 and (-(-end // 64) * 64) % self.group_size:
+                raise NotImplementedError(f"int4 slice end on dim 1 must cover whole groups of {self.group_size}")
             pw = aten.slice.Tensor(self.packed_weight, dim, start // pw_unit, -(-end // pw_unit), 1)
-            sz_end = pw.shape[0] * 128 + start if dim == 0 else -(-end // sz_unit)
-            sz = aten.slice.Tensor(self.scale_and_zero, 1 - dim, start // sz_unit, sz_end, 1)
+            sz_end = -(-end // 16) if dim == 0 else (-(-end // 64) * 64) // self.group_size
+            sz = aten.slice.Tensor(self.scale_and_zero, dim, start // sz_unit, sz_end, 1)
             new = self.__class__(pw.contiguous(), sz.contiguous(), self.transposed, self._layout)
             return return_and_correct_aliasing(func, args, kwargs, new)
         raise NotImplementedError(f"TensorCoreTiledAQTTensorImpl dispatch: attempting to run {func}, this is not supported")

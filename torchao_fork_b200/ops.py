@@ -177,8 +177,8 @@ def _(w: Tensor, group_size: int, eps: float, cuda_div_semantics: bool):
     _check_group(group_size)
     torch._check(w.dim() == 2, lambda: "weight must be 2-D")
     np_, kp = padded_int4_shape(w.size(0), w.size(1), group_size)
-    return (torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=w.device),
-            torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device))
+    return (torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device),
+            torch.empty((np_ // 16, kp // group_size, 16, 2), dtype=torch.bfloat16, device=w.device))
 
 
 @_impl_cuda("b200_int4_quantize_pack")
@@ -187,8 +187,8 @@ def _int4_quantize_pack_cuda(w: Tensor, group_size: int, eps: float, cuda_div_se
     n, k = w.shape
     np_, kp = padded_int4_shape(n, k, group_size)
     w, ldw = _rows(w)
-    packed = torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=w.device)
-    sz = torch.empty((kp // group_size, np_, 2), dtype=torch.bfloat16, device=w.device)
+    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=w.device)
+    sz = torch.empty((np_ // 16, kp // group_size, 16, 2), dtype=torch.bfloat16, device=w.device)
     with torch.cuda.device(w.device):
         _lib.check(_lib.lib().ao_b200_int4_quantize_pack(
             w.data_ptr(), n, k, ldw, np_, kp, group_size, eps,
@@ -243,7 +243,7 @@ def _int4_quantize_cuda(w: Tensor, scale: Tensor, zero: Tensor, group_size: int)
 @register_custom_op("torchao::b200_int4_pack")
 def _(int_data: Tensor):
     np_, kp = _round_up(int_data.size(0), 128), _round_up(int_data.size(1), 64)
-    return torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=int_data.device)
+    return torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
 
 
 @_impl_cuda("b200_int4_pack")
@@ -252,7 +252,7 @@ def _int4_pack_cuda(int_data: Tensor):
     int_data = int_data.contiguous()
     n, k = int_data.shape
     np_, kp = _round_up(n, 128), _round_up(k, 64)
-    packed = torch.empty((np_ // 128, kp // 64, 8, 32, 4), dtype=torch.int32, device=int_data.device)
+    packed = torch.empty((np_ // 16, kp // 64, 32, 4), dtype=torch.int32, device=int_data.device)
     with torch.cuda.device(int_data.device):
         _lib.check(_lib.lib().ao_b200_int4_pack(int_data.data_ptr(), n, k, np_, kp, 0, packed.data_ptr(),
                                                 _stream(int_data)), "int4_pack")
@@ -260,10 +260,47 @@ def _int4_pack_cuda(int_data: Tensor):
 
 
 def _strip_shape_checks(packed_w):
-    torch._check(packed_w.dim() == 5 and tuple(packed_w.shape[2:]) == (8, 32, 4),
-                 lambda: f"super-tile weight must be (N/128, K/64, 8, 32, 4), got {tuple(packed_w.shape)}")
+    torch._check(packed_w.dim() == 4 and tuple(packed_w.shape[2:]) == (32, 4),
+                 lambda: f"strip-major weight must be (N/16, K/64, 32, 4), got {tuple(packed_w.shape)}")
     torch._check(packed_w.dtype is torch.int32, lambda: f"weight must be INT32, got {packed_w.dtype}")
-    return packed_w.size(0) * 128, packed_w.size(1) * 64
+    return packed_w.size(0) * 16, packed_w.size(1) * 64
+
+
+def _sz_checks_b200(scales_and_zeros, n, k, group_size):
+    """strip-major scale/zero: bf16 (N/16, K/G, 16, 2)"""
+    torch._check(scales_and_zeros.dtype is torch.bfloat16, lambda: "scales_and_zeros must be bfloat16")
+    _check_group(group_size)
+    torch._check(tuple(scales_and_zeros.shape) == (n // 16, k // group_size, 16, 2),
+                 lambda: f"scales_and_zeros must be (N/16, K/G, 16, 2) = {(n // 16, k // group_size, 16, 2)}, "
+                         f"got {tuple(scales_and_zeros.shape)}")
+
+
+def pack_scales_and_zeros_b200(scale: Tensor, zero: Tensor) -> Tensor:
+    """scale, zero (N, K/G) -> strip-major bf16 (N/16, K/G, 16, 2); N % 16 == 0.  (The reference's
+    pack_tinygemm_scales_and_zeros, torchao/quantization/utils.py:395-409, gives (K/G, N, 2): same numbers, the rows
+    of one 16-row strip made contiguous so that a strip's qparams are one bulk copy.)"""
+    n, ng = scale.shape
+    sz = torch.stack([scale.to(torch.bfloat16), zero.to(torch.bfloat16)], dim=-1)  # (N, NG, 2)
+    return sz.reshape(n // 16, 16, ng, 2).permute(0, 2, 1, 3).contiguous()
+
+
+def unpack_scales_and_zeros_b200(sz: Tensor) -> Tuple[Tensor, Tensor]:
+    """strip-major (N/16, K/G, 16, 2) -> scale, zero (N, K/G)"""
+    s16, ng = sz.shape[0], sz.shape[1]
+    t = sz.permute(0, 2, 1, 3).reshape(s16 * 16, ng, 2)
+    return t[..., 0].contiguous(), t[..., 1].contiguous()
+
+
+def sz_b200_to_tinygemm(sz: Tensor) -> Tensor:
+    """strip-major (N/16, K/G, 16, 2) -> the reference's (K/G, N, 2)"""
+    s16, ng = sz.shape[0], sz.shape[1]
+    return sz.permute(1, 0, 2, 3).reshape(ng, s16 * 16, 2).contiguous()
+
+
+def sz_tinygemm_to_b200(sz: Tensor) -> Tensor:
+    """the reference's (K/G, N, 2) -> strip-major (N/16, K/G, 16, 2)"""
+    ng, n = sz.shape[0], sz.shape[1]
+    return sz.reshape(ng, n // 16, 16, 2).permute(1, 0, 2, 3).contiguous()
 
 
 @register_custom_op("torchao::b200_int4_unpack")
@@ -286,14 +323,14 @@ def _int4_unpack_cuda(packed_w: Tensor):
 @register_custom_op("torchao::b200_int4_dequantize")
 def _(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int):
     n, k = _strip_shape_checks(packed_w)
-    _sz_checks(scales_and_zeros, n, k, group_size)
+    _sz_checks_b200(scales_and_zeros, n, k, group_size)
     return torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
 
 
 @_impl_cuda("b200_int4_dequantize")
 def _int4_dequant_cuda(packed_w: Tensor, scales_and_zeros: Tensor, group_size: int):
     n, k = _strip_shape_checks(packed_w)
-    _sz_checks(scales_and_zeros, n, k, group_size)
+    _sz_checks_b200(scales_and_zeros, n, k, group_size)
     packed_w, scales_and_zeros = packed_w.contiguous(), scales_and_zeros.contiguous()
     out = torch.empty((n, k), dtype=torch.bfloat16, device=packed_w.device)
     with torch.cuda.device(packed_w.device):
@@ -355,7 +392,7 @@ def _int4_mm_cuda(x: Tensor, packed_w: Tensor, group_size: int, scales_and_zeros
     """Same contract as aten._weight_int4pack_mm(x, packed, G, scale_and_zero)
     (call site torchao/dtypes/uintx/tensor_core_tiled_layout.py:104) on the super-tile layout."""
     np_, kp = _strip_shape_checks(packed_w)
-    _sz_checks(scales_and_zeros, np_, kp, group_size)
+    _sz_checks_b200(scales_and_zeros, np_, kp, group_size)
     _check_cuda_bf16(x, "activation")
     torch._check(x.dim() == 2 and x.size(1) <= kp, lambda: f"x must be (M, K<= {kp}), got {tuple(x.shape)}")
     torch._check(0 < out_features <= np_, lambda: "out_features out of range")
@@ -423,3 +460,68 @@ def _int8_mm_cuda(x: Tensor, int_data: Tensor, scale: Tensor):
         _lib.check(_lib.lib().ao_b200_int8_mm(x.data_ptr(), m, x.size(1), ldx, int_data.data_ptr(), scale.data_ptr(),
                                               n, y.data_ptr(), n, _stream(x)), "int8_mm")
     return y
+
+
+# ------------------------------------------------------------------ fused decode GEMV (M <= 16)
+EPILOGUE_PLAIN, EPILOGUE_RESIDUAL, EPILOGUE_SILU_MUL = 0, 1, 2
+
+if not _defined("b200_int4_gemv_fused"):
+    lib.define("b200_int4_gemv_fused(Tensor x, Tensor packed_w, int group_size, Tensor scales_and_zeros, "
+               "int out_features, Tensor? norm_weight, float norm_eps, Tensor? residual, int epilogue) -> Tensor")
+
+
+@register_custom_op("torchao::b200_int4_gemv_fused")
+def _(x, packed_w, group_size, scales_and_zeros, out_features, norm_weight, norm_eps, residual, epilogue):
+    n = out_features // 2 if epilogue == EPILOGUE_SILU_MUL else out_features
+    return torch.empty((x.size(0), n), dtype=torch.bfloat16, device=x.device)
+
+
+@_impl_cuda("b200_int4_gemv_fused")
+def _int4_gemv_fused_cuda(x, packed_w, group_size, scales_and_zeros, out_features, norm_weight, norm_eps, residual,
+                          epilogue):
+    """Llama-block GEMV with RMSNorm prologue / residual or SiLU*mul epilogue (include/ao_b200.h)."""
+    np_, kp = _strip_shape_checks(packed_w)
+    _sz_checks_b200(scales_and_zeros, np_, kp, group_size)
+    _check_cuda_bf16(x, "activation")
+    torch._check(x.dim() == 2 and 0 < x.size(0) <= 16 and x.size(1) <= kp and x.size(1) % 8 == 0,
+                 lambda: f"x must be (M<=16, K<={kp}, K%8==0), got {tuple(x.shape)}")
+    torch._check(0 < out_features <= np_, lambda: "out_features out of range")
+    torch._check(epilogue in (0, 1, 2), lambda: "epilogue must be 0 (plain), 1 (residual) or 2 (silu*mul)")
+    x, ldx = _rows(x)
+    m = x.size(0)
+    n = out_features // 2 if epilogue == EPILOGUE_SILU_MUL else out_features
+    y = torch.empty((m, n), dtype=torch.bfloat16, device=x.device)
+    ld_res = 0
+    if epilogue == EPILOGUE_RESIDUAL:
+        torch._check(residual is not None and tuple(residual.shape) == (m, n), lambda: "residual must be (M, N)")
+        _check_cuda_bf16(residual, "residual")
+        residual = residual.contiguous()
+        ld_res = residual.stride(0)
+    if norm_weight is not None:
+        _check_cuda_bf16(norm_weight, "norm_weight")
+        torch._check(norm_weight.numel() == x.size(1), lambda: "norm_weight must have K elements")
+        norm_weight = norm_weight.contiguous()
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ao_b200_int4_gemv_fused(
+            x.data_ptr(), m, x.size(1), ldx, packed_w.data_ptr(), scales_and_zeros.data_ptr(), np_, kp, group_size,
+            y.data_ptr(), out_features, n, None if norm_weight is None else norm_weight.data_ptr(), norm_eps,
+            None if residual is None else residual.data_ptr(), ld_res, epilogue, _stream(x)), "int4_gemv_fused")
+    return y
+
+
+def interleave_gate_up(packed1: Tensor, sz1: Tensor, packed3: Tensor, sz3: Tensor) -> Tuple[Tensor, Tensor]:
+    """Fuse w1 (gate) and w3 (up) for the SiLU*mul epilogue: fused 16-row strip t holds rows 8t..8t+7 of w1 as its rows
+    0..7 and rows 8t..8t+7 of w3 as its rows 8..15, so one MMA lane owns gate_i and up_i of the same i.  Pure
+    permutation of packed words / scale rows: each row keeps its own quantization (rows are quantized independently)."""
+    torch._check(packed1.shape == packed3.shape and sz1.shape == sz3.shape, lambda: "w1 / w3 shape mismatch")
+    S16, KT = packed1.shape[0], packed1.shape[1]
+    NG = sz1.shape[1]
+    # word j = 2h + b of a lane holds row g + 8b of the strip
+    p1 = packed1.reshape(S16, KT, 32, 2, 2)
+    p3 = packed3.reshape(S16, KT, 32, 2, 2)
+    f = torch.stack([p1, p3], dim=-1)                       # [s][kt][lane][h][b][b']; b' = 0 gate rows, 1 up rows
+    f = f.permute(0, 4, 1, 2, 3, 5).reshape(2 * S16, KT, 32, 4).contiguous()   # new strip = 2 s + b, word j' = 2h + b'
+    z1 = sz1.reshape(S16, NG, 2, 8, 2)                      # [s][grp][b][g][2]
+    z3 = sz3.reshape(S16, NG, 2, 8, 2)
+    z = torch.stack([z1, z3], dim=3)                        # [s][grp][b][b'][g][2]
+    return f, z.permute(0, 2, 1, 3, 4, 5).reshape(2 * S16, NG, 16, 2).contiguous()
