@@ -22,6 +22,7 @@
 #include <cuda_fp16.h>
 
 #include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -239,8 +240,8 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
       }
     }
     named_bar_sync(1, kCT);
-    // X[seg][m] = sum of the scaled activations, C[seg][m] = 1024 * (sum of the STORED values) + 8 * X:
-    //   sum_k x_k (q_k - 8) = (MMA result) - C
+    // X[seg][m] = sum of the scaled activations, C[seg][m] = 1024 * (sum of the STORED values) + 8 * X, stored
+    // negated:  sum_k x_k (q_k - 8) = (MMA result) - C  ->  the MMA accumulator is initialised with -C
     const int n_segs = KT * 64 / SEG;
     constexpr int EPL = SEG / 32;  // elements per lane (1, 2 or 4: never straddles a pair)
     for (int pi = warp; pi < n_segs * 8 * MT; pi += kFConsumers) {
@@ -261,20 +262,96 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
       }
       if (lane == 0) {
         X_s[(sg * 2 + 0) * 8 * MT + m] = xt;
-        X_s[(sg * 2 + 1) * 8 * MT + m] = fmaf(1024.f, xs, 8.f * xt);
+        X_s[(sg * 2 + 1) * 8 * MT + m] = -fmaf(1024.f, xs, 8.f * xt);
       }
     }
     named_bar_sync(1, kCT);
   }
 
-  // activation rows of the two MMA column blocks: columns m >= M are never stored, so their lanes may read any valid
-  // row (MMA columns are independent) -> no predicate in the loop
-  const uint8_t* xrow[MT];
+  // ---- main loop.  Everything a warp touches in a stage sits at a FIXED offset from the stage base (its two
+  //      k-tiles, its scale/zero group(s)) or from a per-chunk base (its 128 activations, its correction sums): all
+  //      addresses are 32-bit shared-window addresses + immediates, so the loop body is loads, 5 ALU ops per packed
+  //      word, one mma.sync per word and the per-segment fix-up — nothing else. ----
+  constexpr uint32_t XS = 2 * 8 * MT * 4;                          // bytes of one segment's {X, -C} record
+  constexpr uint32_t kXChunk = (kStageTiles * 64 / SEG) * XS;      // correction records per stage
+  const int tl0 = warp * kTilesPerWarp;                            // this warp's first k-tile inside a stage
+  const uint32_t ring_u = smem_u32(ring);
+  const uint32_t w_off = (uint32_t)tl0 * 512u + (uint32_t)lane * 16u;
+  const uint32_t sz_off = kStageTiles * 512u + (uint32_t)(((tl0 * 64) / G) * 16 + g) * 4u;
+  const uint32_t X_u0 = smem_u32(X_s) + (uint32_t)((tl0 * 64) / SEG) * XS + (uint32_t)c * 8u;
+  // activation fragments: only the lanes whose MMA column is a real row (g + 8 mt < M) load; the others keep zeros
+  // (their columns are never stored) — for M = 1 that is one shared-memory wavefront per load instead of four
+  uint32_t x_u0[MT];
+  bool x_on[MT];
+  uint4 xx[MT];
 #pragma unroll
-  for (int mt = 0; mt < MT; ++mt) xrow[mt] = x_s + (size_t)min(g + 8 * mt, p.M - 1) * p.x_row_bytes + c * 16;
-  const int tl0 = warp * kTilesPerWarp;  // this warp's first k-tile inside a stage
+  for (int mt = 0; mt < MT; ++mt) {
+    x_on[mt] = g + 8 * mt < p.M;
+    x_u0[mt] = smem_u32(x_s) + (uint32_t)min(g + 8 * mt, p.M - 1) * p.x_row_bytes + (uint32_t)c * 16u + (uint32_t)tl0 * 128u;
+    xx[mt] = make_uint4(0, 0, 0, 0);
+  }
+  // keep the per-lane offsets in registers (opaque to the compiler, which otherwise re-derives them from %tid in
+  // every stage: ~12 extra ALU-pipe instructions per stage on the pipe that already carries the dequant)
+  uint32_t w_off_r = w_off, sz_off_r = sz_off, X_u0_r = X_u0;
+  asm volatile("" : "+r"(w_off_r), "+r"(sz_off_r), "+r"(X_u0_r));
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) asm volatile("" : "+r"(x_u0[mt]));
+  const int n_full = KT / kStageTiles;  // chunks [0, n_full) are complete stages
   int slot = 0;
   uint32_t par = 0;
+  uint32_t stage_u = ring_u;
+
+  // one stage of one warp: two k-tiles = four 32-k halves; FULL = every tile of the stage is valid
+  auto consume = [&](auto full_tag, const int cnt, const uint32_t xo, const uint32_t X_u, float (&yacc)[MT][4]) {
+    constexpr bool FULL = decltype(full_tag)::value;
+    const uint4 w0 = lds128(stage_u + w_off_r), w1 = lds128(stage_u + w_off_r + 512u);
+    float acc[MT][4];
+#pragma unroll
+    for (int t = 0; t < kTilesPerWarp; ++t) {
+      if (!FULL && tl0 + t >= cnt) continue;
+      const uint4 wv = t == 0 ? w0 : w1;
+      const uint32_t words[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int q32 = 2 * t + h;       // 32-k half inside the warp's 128 k
+        const int si = q32 / U32;        // segment inside the warp's 128 k
+        if (q32 % U32 == 0) {
+          // the accumulator starts at -C, so the MMA chain ends at  sum_k x_k (q_k - 8)
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            const float2 nc = lds64f(X_u + si * XS + 8 * MT * 4 + mt * 32);
+            acc[mt][0] = nc.x; acc[mt][1] = nc.y; acc[mt][2] = nc.x; acc[mt][3] = nc.y;
+          }
+        }
+        const uint32_t wl = words[2 * h], wh = words[2 * h + 1];  // rows g and g + 8
+        const uint32_t wl8 = wl >> 8, wh8 = wh >> 8;
+        const uint32_t a0l = nib_f16_lo(wl), a1l = nib_f16_hi(wl), a2l = nib_f16_lo(wl8), a3l = nib_f16_hi(wl8);
+        const uint32_t a0h = nib_f16_lo(wh), a1h = nib_f16_hi(wh), a2h = nib_f16_lo(wh8), a3h = nib_f16_hi(wh8);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          if (x_on[mt]) xx[mt] = lds128(x_u0[mt] + xo + q32 * 64);
+          mma_f16_16816(acc[mt], a0l, a0h, a1l, a1h, xx[mt].x, xx[mt].y);
+          mma_f16_16816(acc[mt], a2l, a2h, a3l, a3h, xx[mt].z, xx[mt].w);
+        }
+        if (q32 % U32 == U32 - 1) {
+          // segment complete: y += s * acc + z * X   (fp32)
+          constexpr uint32_t kGrpStep = G < 128 ? 64u : 0u;  // bytes between the groups of consecutive segments
+          const uint32_t p0 = lds32(stage_u + sz_off_r + si * kGrpStep), p1 = lds32(stage_u + sz_off_r + si * kGrpStep + 32u);
+          const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
+          const float z0 = __uint_as_float(p0 & 0xFFFF0000u), z1 = __uint_as_float(p1 & 0xFFFF0000u);
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            const float2 X = lds64f(X_u + si * XS + mt * 32);
+            yacc[mt][0] = fmaf(sc0, acc[mt][0], fmaf(z0, X.x, yacc[mt][0]));
+            yacc[mt][1] = fmaf(sc0, acc[mt][1], fmaf(z0, X.y, yacc[mt][1]));
+            yacc[mt][2] = fmaf(sc1, acc[mt][2], fmaf(z1, X.x, yacc[mt][2]));
+            yacc[mt][3] = fmaf(sc1, acc[mt][3], fmaf(z1, X.y, yacc[mt][3]));
+          }
+        }
+      }
+    }
+  };
+
   for (int strip = s0; strip < s1; ++strip) {
     float yacc[MT][4];
 #pragma unroll
@@ -282,82 +359,23 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
 #pragma unroll
       for (int e = 0; e < 4; ++e) yacc[mt][e] = 0.f;
 
+    uint32_t xo = 0, X_u = X_u0_r;
     for (int ch = 0; ch < n_chunks; ++ch) {
-      const int kt0 = ch * kStageTiles;
-      const int cnt = min(kStageTiles, KT - kt0);
-      const uint8_t* stage = ring + (size_t)slot * kStageB;
-      const uint32_t* ssrc = reinterpret_cast<const uint32_t*>(stage + kStageTiles * 512);
-      const int kbase = (kt0 + tl0) * 64;  // first k of this warp's share of the stage
       mbar_wait(&full[slot], par);
-      if (tl0 < cnt) {
-        uint4 wv[kTilesPerWarp];
-#pragma unroll
-        for (int t = 0; t < kTilesPerWarp; ++t)
-          wv[t] = (tl0 + t < cnt) ? *reinterpret_cast<const uint4*>(stage + (tl0 + t) * 512 + lane * 16)
-                                  : make_uint4(0, 0, 0, 0);
-        // kChains independent accumulators per segment: consecutive mma.sync on ONE accumulator serialise on the
-        // (long) HMMA latency; the partial sums are added when the segment is complete
-        constexpr int kChains = (2 * U32 >= 4) ? 4 : 2 * U32;  // MMAs per segment = 2 * U32
-        float accg[kChains][MT][4];
-#pragma unroll
-        for (int t = 0; t < kTilesPerWarp; ++t) {
-          const uint32_t words[4] = {wv[t].x, wv[t].y, wv[t].z, wv[t].w};
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int q32 = 2 * t + h;  // 32-k half inside the warp's 128 k
-            const int j0 = (2 * (q32 % U32)) % kChains, j1 = (2 * (q32 % U32) + 1) % kChains;
-            const bool first0 = 2 * (q32 % U32) < kChains, first1 = 2 * (q32 % U32) + 1 < kChains;
-            const uint32_t wl = words[2 * h], wh = words[2 * h + 1];  // rows g and g + 8
-            const uint32_t wl8 = wl >> 8, wh8 = wh >> 8;
-            const uint32_t a0l = nib_f16_lo(wl), a1l = nib_f16_hi(wl), a2l = nib_f16_lo(wl8), a3l = nib_f16_hi(wl8);
-            const uint32_t a0h = nib_f16_lo(wh), a1h = nib_f16_hi(wh), a2h = nib_f16_lo(wh8), a3h = nib_f16_hi(wh8);
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-              const uint4 xx = *reinterpret_cast<const uint4*>(xrow[mt] + (size_t)(kbase + 32 * q32) * 2);
-              if (first0) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) accg[j0][mt][e] = 0.f;
-              }
-              mma_f16_16816(accg[j0][mt], a0l, a0h, a1l, a1h, xx.x, xx.y);
-              if (first1) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) accg[j1][mt][e] = 0.f;
-              }
-              mma_f16_16816(accg[j1][mt], a2l, a2h, a3l, a3h, xx.z, xx.w);
-            }
-            if (q32 % U32 == U32 - 1 && (tl0 + t < cnt)) {
-              // segment complete: y += s * (acc - C) + z * X   (fp32)
-              const int k_seg = kbase + 32 * (q32 - (U32 - 1));  // first k of the segment
-              const int gl = (k_seg - kt0 * 64) / G;               // group inside the stage
-              const uint32_t p0 = ssrc[gl * 16 + g], p1 = ssrc[gl * 16 + g + 8];
-              const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
-              const float z0 = __uint_as_float(p0 & 0xFFFF0000u), z1 = __uint_as_float(p1 & 0xFFFF0000u);
-              const float* Xp = X_s + (k_seg / SEG) * 2 * 8 * MT + 2 * c;
-#pragma unroll
-              for (int mt = 0; mt < MT; ++mt) {
-                float a[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  a[e] = accg[0][mt][e];
-#pragma unroll
-                  for (int j = 1; j < kChains; ++j) a[e] += accg[j][mt][e];
-                }
-                const float2 X = *reinterpret_cast<const float2*>(Xp + 8 * mt);
-                const float2 C = *reinterpret_cast<const float2*>(Xp + 8 * MT + 8 * mt);
-                yacc[mt][0] = fmaf(sc0, a[0] - C.x, fmaf(z0, X.x, yacc[mt][0]));
-                yacc[mt][1] = fmaf(sc0, a[1] - C.y, fmaf(z0, X.y, yacc[mt][1]));
-                yacc[mt][2] = fmaf(sc1, a[2] - C.x, fmaf(z1, X.x, yacc[mt][2]));
-                yacc[mt][3] = fmaf(sc1, a[3] - C.y, fmaf(z1, X.y, yacc[mt][3]));
-              }
-            }
-          }
-        }
+      if (ch < n_full) {
+        consume(std::true_type{}, kStageTiles, xo, X_u, yacc);
+      } else if (tl0 < KT - ch * kStageTiles) {
+        consume(std::false_type{}, KT - ch * kStageTiles, xo, X_u, yacc);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
+      xo += kStageTiles * 128u;
+      X_u += kXChunk;
+      stage_u += kStageB;
       if (++slot == stages) {
         slot = 0;
         par ^= 1u;
+        stage_u = ring_u;
       }
     }
 
