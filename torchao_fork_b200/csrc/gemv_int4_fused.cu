@@ -26,14 +26,39 @@
 
 #include "common.cuh"
 
+#ifndef AO_CHAINS
+#define AO_CHAINS 2
+#endif
+#ifndef AO_STAGE_TILES
+#define AO_STAGE_TILES 32
+#endif
+#ifndef AO_EXP
+#define AO_EXP 0  // benchmarks/gemv_trace.cu ablations only
+#endif
+
 namespace ao {
 
 constexpr int kFConsumers = 16;
-constexpr int kFThreads = (kFConsumers + 1) * 32;
-constexpr int kStageTiles = 32;            // k-tiles (of 64 k) per stage: 16 KB of weights
+constexpr int kFThreads = (kFConsumers + 2) * 32;  // + TMA producer warp + epilogue warp
+constexpr int kRedBufs = 2;                       // partial-sum buffers between the consumers and the epilogue warp
+constexpr int kStageTiles = AO_STAGE_TILES;  // k-tiles (of 64 k) per stage: 16 KB of weights per 32
 constexpr int kTilesPerWarp = kStageTiles / kFConsumers;  // 2 k-tiles = 128 k per warp per stage
 
 enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSiluMul = 2 };
+
+// AO_GEMV_TRACE (benchmarks/gemv_trace.cu only): per-warp, per-stage SM clock stamps of one CTA
+#ifdef AO_GEMV_TRACE
+constexpr int kTraceIts = 256, kTraceKinds = 6;
+__device__ long long ao_trace[kTraceKinds][kFConsumers + 2][kTraceIts];
+__device__ int ao_trace_cta = 0;
+#define AO_TRACE(kind, it)                                                                  \
+  do {                                                                                      \
+    if ((int)blockIdx.x == ao_trace_cta && (threadIdx.x & 31) == 0 && (it) < kTraceIts)     \
+      ao_trace[kind][threadIdx.x >> 5][it] = clock64();                                     \
+  } while (0)
+#else
+#define AO_TRACE(kind, it) do { } while (0)
+#endif
 
 struct GemvFusedParams {
   const uint8_t* packed;      // strip-major [Np/16][Kp/64][512 B]
@@ -46,6 +71,7 @@ struct GemvFusedParams {
   int KT;                     // Kp / 64
   int64_t Kx, ldx, Np, N_out, ldy, ld_res;
   int n_strips;               // Np / 16
+  int strips_base, strips_rem;  // n_strips / grid, n_strips % grid
   float eps;
   uint32_t x_row_bytes;       // 2 * Kp + 16
   uint32_t off_x, off_X, off_red, off_misc;  // shared-memory carve-up (bytes)
@@ -105,31 +131,38 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
   uint64_t* full = reinterpret_cast<uint64_t*>(row_dn + 16);
   uint64_t* empty = full + p.stages;
   uint64_t* red_full = empty + p.stages;                        // [2]
-  uint64_t* red_free = red_full + 2;                            // [2]
+  uint64_t* red_free = red_full + kRedBufs;                            // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  AO_TRACE(5, 0);
   const int stages = p.stages;
-  const int B = gridDim.x, b = blockIdx.x;
-  const int s0 = (int)(((int64_t)b * p.n_strips) / B), s1 = (int)(((int64_t)(b + 1) * p.n_strips) / B);
+  const int b = blockIdx.x;
+  // strips [s0, s1) of this CTA: base = n_strips / grid each, the first `rem` CTAs one more (host-computed: no division)
+  const int s0 = b * p.strips_base + min(b, p.strips_rem), s1 = s0 + p.strips_base + (b < p.strips_rem ? 1 : 0);
   const int KT = p.KT;
   const int n_chunks = (KT + kStageTiles - 1) / kStageTiles;
 
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < stages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], kFConsumers);
-    }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&red_full[s], kFConsumers);
-      mbar_init(&red_free[s], 1);
-    }
-    fence_barrier_init();
-  }
-  __syncthreads();
+  // The producer warp initialises the mbarriers and starts streaming at once; everybody else meets it on named
+  // barrier 2 only when they first need an mbarrier (after the activation staging), so the first stages are in
+  // flight while the kernel is still waiting for its predecessor (PDL) and staging x.
   grid_launch_dependents();
+  AO_TRACE(5, 1);
 
   if (warp == kFConsumers) {
     // ===================== producer: lane 0 owns the barriers; `copy_split` lanes share the weight copy ===============
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], kFConsumers);
+      }
+      for (int s = 0; s < kRedBufs; ++s) {
+        mbar_init(&red_full[s], kFConsumers);
+        mbar_init(&red_free[s], 1);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    named_bar_arrive(2, kFThreads);
     {
       int slot = 0;
       uint32_t par = 1;
@@ -144,7 +177,9 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
           const int n_grp = cnt * 64 / G;
           uint8_t* wdst = ring + (size_t)slot * kStageB;
           if (lane == 0) {
+            AO_TRACE(0, (strip - s0) * n_chunks + ch);
             mbar_wait(&empty[slot], par);
+            AO_TRACE(1, (strip - s0) * n_chunks + ch);
             mbar_arrive_expect_tx(&full[slot], (uint32_t)(cnt * 512 + n_grp * 64));
             bulk_g2s(wdst + kStageTiles * 512, srow + (int64_t)(kt0 * 64 / G) * 16, (uint32_t)(n_grp * 64), &full[slot]);
           }
@@ -167,11 +202,75 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
     return;
   }
 
+  if (warp == kFConsumers + 1) {
+    // ===================== epilogue warp: sums the 16 partials of every finished strip, applies the row scale and
+    //                       the residual / SiLU*mul epilogue, stores =====================
+    const int g = lane >> 2, c = lane & 3;
+    grid_dependency_wait();
+    named_bar_sync(2, kFThreads);  // mbarriers initialised
+    for (int strip = s0; strip < s1; ++strip) {
+      const int li = strip - s0;
+      const int rbuf = li % kRedBufs;
+      const uint32_t use = (uint32_t)(li / kRedBufs);
+      const float* rb = red + (size_t)rbuf * (kFConsumers * MT * 128);
+      mbar_wait(&red_full[rbuf], use & 1u);
+      AO_TRACE(4, li);
+      float4 sum[MT];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int w = 0; w < kFConsumers; ++w) {
+          const float4 v = *reinterpret_cast<const float4*>(rb + ((w * MT + mt) * 32 + lane) * 4);
+          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        sum[mt] = s;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&red_free[rbuf]);
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        const float vals[2][2] = {{sum[mt].x, sum[mt].z}, {sum[mt].y, sum[mt].w}};  // [col j][row half]: rows g, g+8
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int m = 8 * mt + 2 * c + j;
+          if (m >= p.M) continue;
+          const float rsc = row_scale[m];
+          const float v0 = vals[j][0] * rsc, v1 = vals[j][1] * rsc;
+          if (p.epilogue == kEpiSiluMul) {
+            // rows g = gate (w1), rows g+8 = up (w3) of output index 8*strip + g  (model.py:486)
+            const int64_t n = 8 * (int64_t)strip + g;
+            if (2 * n < p.N_out) {
+              const float gate = bf16r(v0), up = bf16r(v1);
+              const float sg = bf16r(gate / (1.f + __expf(-gate)));
+              p.y[m * p.ldy + n] = __float2bfloat16_rn(sg * up);
+            }
+          } else {
+            const int64_t n0 = 16 * (int64_t)strip + g;
+            if (p.epilogue == kEpiResidual) {
+              if (n0 < p.N_out)
+                p.y[m * p.ldy + n0] = __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0]) + bf16r(v0));
+              if (n0 + 8 < p.N_out)
+                p.y[m * p.ldy + n0 + 8] =
+                    __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0 + 8]) + bf16r(v1));
+            } else {
+              if (n0 < p.N_out) p.y[m * p.ldy + n0] = __float2bfloat16_rn(v0);
+              if (n0 + 8 < p.N_out) p.y[m * p.ldy + n0 + 8] = __float2bfloat16_rn(v1);
+            }
+          }
+        }
+      }
+      AO_TRACE(5, li);
+    }
+    return;
+  }
+
   // ===================== consumers =====================
   const int g = lane >> 2, c = lane & 3;
   const int tid = threadIdx.x;  // 0 .. 511
   constexpr int kCT = kFConsumers * 32;
   grid_dependency_wait();
+  AO_TRACE(5, 2);
 
   // ---- stage the activations: x (* norm_w) -> per-row power-of-two scaling -> fp16, the entries that meet a
   //      "1024 + 16 q" weight pre-divided by 16; then the per-segment correction sums ----
@@ -210,63 +309,69 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
       }
     }
     named_bar_sync(1, kCT);
-    if (tid < p.M) {
+    AO_TRACE(5, 3);
+    if (warp < p.M) {
+      // warp w finishes row w: 16 (sum sq, amax) partials -> 2^e and the epilogue scale
       float t = 0.f, amax = 0.f;
-#pragma unroll
-      for (int w = 0; w < kFConsumers; ++w) {
-        t += part[(tid * kFConsumers + w) * 2];
-        amax = fmaxf(amax, part[(tid * kFConsumers + w) * 2 + 1]);
+      if (lane < kFConsumers) {
+        t = part[(warp * kFConsumers + lane) * 2];
+        amax = part[(warp * kFConsumers + lane) * 2 + 1];
       }
-      // 2^e: brings the row's largest magnitude to [2^13, 2^14): every bf16 value within 2^-27 of it is exact in fp16
-      int e = 0;
-      if (amax > 0.f) e = (int)((__float_as_uint(amax) >> 23) & 0xFF) - 127 - 13;
-      e = max(-100, min(100, e));
-      const float up = __uint_as_float((uint32_t)(e + 127) << 23), dn = __uint_as_float((uint32_t)(127 - e) << 23);
-      row_dn[tid] = dn;
-      row_scale[tid] = (p.norm_w != nullptr) ? up * rsqrtf(t / (float)p.Kx + p.eps) : up;
+      t = warp_sum_f(t);
+      amax = warp_max_f(amax);
+      if (lane == 0) {
+        // 2^e: brings the row's largest magnitude to [2^13, 2^14): every bf16 value within 2^-27 of it is exact in fp16
+        int e = 0;
+        if (amax > 0.f) e = (int)((__float_as_uint(amax) >> 23) & 0xFF) - 127 - 13;
+        e = max(-100, min(100, e));
+        const float up = __uint_as_float((uint32_t)(e + 127) << 23), dn = __uint_as_float((uint32_t)(127 - e) << 23);
+        row_dn[warp] = dn;
+        row_scale[warp] = (p.norm_w != nullptr) ? up * rsqrtf(t / (float)p.Kx + p.eps) : up;
+      }
     }
     named_bar_sync(1, kCT);
+    AO_TRACE(5, 4);
+    // rescale to fp16 and, in the same pass, the per-segment correction sums: a segment is SEG / 8 consecutive chunks
+    // = SEG / 8 consecutive lanes.  X[seg][m] = sum of the scaled activations, C[seg][m] = 1024 * (sum of the STORED
+    // values) + 8 * X, stored negated:  sum_k x_k (q_k - 8) = (MMA result) - C  ->  the accumulator starts at -C.
+    // (Columns m >= M of X_s stay unwritten: they only feed MMA columns that are never stored.)
+    constexpr int CPS = SEG / 8;  // chunks per segment: 4, 8 or 16
     for (int m = 0; m < p.M; ++m) {
       const float dn = row_dn[m], dn16 = dn * 0.0625f;
-      for (int ci = tid; ci < chunks_per_row; ci += kCT) {
-        uint4* ptr = reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16);
-        float f[8];
-        unpack8(*ptr, f);
-        // element pairs (0,1),(4,5) meet "1024 + q" weights, pairs (2,3),(6,7) meet "1024 + 16 q" weights
-        const __half2 h0 = __floats2half2_rn(f[0] * dn, f[1] * dn), h1 = __floats2half2_rn(f[2] * dn16, f[3] * dn16);
-        const __half2 h2 = __floats2half2_rn(f[4] * dn, f[5] * dn), h3 = __floats2half2_rn(f[6] * dn16, f[7] * dn16);
-        *ptr = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
-                          *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
-      }
-    }
-    named_bar_sync(1, kCT);
-    // X[seg][m] = sum of the scaled activations, C[seg][m] = 1024 * (sum of the STORED values) + 8 * X, stored
-    // negated:  sum_k x_k (q_k - 8) = (MMA result) - C  ->  the MMA accumulator is initialised with -C
-    const int n_segs = KT * 64 / SEG;
-    constexpr int EPL = SEG / 32;  // elements per lane (1, 2 or 4: never straddles a pair)
-    for (int pi = warp; pi < n_segs * 8 * MT; pi += kFConsumers) {
-      const int sg = pi / (8 * MT), m = pi % (8 * MT);
-      float xs = 0.f, xt = 0.f;
-      if (m < p.M) {
-        const int k_in = lane * EPL;  // offset inside the segment (multiple of EPL)
-        const __half* src = reinterpret_cast<const __half*>(x_s + (size_t)m * p.x_row_bytes) + (size_t)sg * SEG + k_in;
-#pragma unroll
-        for (int e = 0; e < EPL; ++e) {
-          const float v = __half2float(src[e]);
-          const bool x16 = ((k_in + e) & 2) != 0;  // positions 2,3,6,7 of every 8
-          xs += v;
-          xt += x16 ? v * 16.f : v;
+      for (int base = 0; base < chunks_per_row; base += kCT) {
+        const int ci = base + tid;
+        float xs = 0.f, xt = 0.f;
+        if (ci < chunks_per_row) {
+          uint4* ptr = reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16);
+          float f[8];
+          unpack8(*ptr, f);
+          // element pairs (0,1),(4,5) meet "1024 + q" weights, pairs (2,3),(6,7) meet "1024 + 16 q" weights
+          const __half2 h0 = __floats2half2_rn(f[0] * dn, f[1] * dn), h1 = __floats2half2_rn(f[2] * dn16, f[3] * dn16);
+          const __half2 h2 = __floats2half2_rn(f[4] * dn, f[5] * dn), h3 = __floats2half2_rn(f[6] * dn16, f[7] * dn16);
+          *ptr = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                            *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+          const float2 a0 = __half22float2(h0), a1 = __half22float2(h1), a2 = __half22float2(h2), a3 = __half22float2(h3);
+          const float plain = (a0.x + a0.y) + (a2.x + a2.y), div16 = (a1.x + a1.y) + (a3.x + a3.y);
+          xs = plain + div16;
+          xt = fmaf(16.f, div16, plain);
         }
-        xs = warp_sum_f(xs);
-        xt = warp_sum_f(xt);
-      }
-      if (lane == 0) {
-        X_s[(sg * 2 + 0) * 8 * MT + m] = xt;
-        X_s[(sg * 2 + 1) * 8 * MT + m] = -fmaf(1024.f, xs, 8.f * xt);
+#pragma unroll
+        for (int o = CPS / 2; o; o >>= 1) {
+          xs += __shfl_xor_sync(0xffffffffu, xs, o);
+          xt += __shfl_xor_sync(0xffffffffu, xt, o);
+        }
+        if (ci < chunks_per_row && (ci % CPS) == 0) {
+          const int sg = ci / CPS;
+          X_s[(sg * 2 + 0) * 8 * MT + m] = xt;
+          X_s[(sg * 2 + 1) * 8 * MT + m] = -fmaf(1024.f, xs, 8.f * xt);
+        }
       }
     }
     named_bar_sync(1, kCT);
+    AO_TRACE(5, 5);
+    AO_TRACE(5, 6);
   }
+  named_bar_sync(2, kFThreads);  // the producer has initialised the mbarriers (long ago)
 
   // ---- main loop.  Everything a warp touches in a stage sits at a FIXED offset from the stage base (its two
   //      k-tiles, its scale/zero group(s)) or from a per-chunk base (its 128 activations, its correction sums): all
@@ -304,48 +409,74 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
   // one stage of one warp: two k-tiles = four 32-k halves; FULL = every tile of the stage is valid
   auto consume = [&](auto full_tag, const int cnt, const uint32_t xo, const uint32_t X_u, float (&yacc)[MT][4]) {
     constexpr bool FULL = decltype(full_tag)::value;
-    const uint4 w0 = lds128(stage_u + w_off_r), w1 = lds128(stage_u + w_off_r + 512u);
-    float acc[MT][4];
+    uint4 wv[kTilesPerWarp];
+#pragma unroll
+    for (int t = 0; t < kTilesPerWarp; ++t) wv[t] = lds128(stage_u + w_off_r + t * 512u);
+    // kChains independent accumulators per segment: back-to-back mma.sync on ONE accumulator serialise on the HMMA
+    // latency (~50 clk under load: removing the MMAs altogether took the kernel from 82 to 56 us)
+    constexpr int kChains = (2 * U32 < AO_CHAINS) ? 2 * U32 : AO_CHAINS;
+    float acc[kChains][MT][4];
 #pragma unroll
     for (int t = 0; t < kTilesPerWarp; ++t) {
       if (!FULL && tl0 + t >= cnt) continue;
-      const uint4 wv = t == 0 ? w0 : w1;
-      const uint32_t words[4] = {wv.x, wv.y, wv.z, wv.w};
+      const uint32_t words[4] = {wv[t].x, wv[t].y, wv[t].z, wv[t].w};
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const int q32 = 2 * t + h;       // 32-k half inside the warp's 128 k
-        const int si = q32 / U32;        // segment inside the warp's 128 k
-        if (q32 % U32 == 0) {
-          // the accumulator starts at -C, so the MMA chain ends at  sum_k x_k (q_k - 8)
-#pragma unroll
-          for (int mt = 0; mt < MT; ++mt) {
-            const float2 nc = lds64f(X_u + si * XS + 8 * MT * 4 + mt * 32);
-            acc[mt][0] = nc.x; acc[mt][1] = nc.y; acc[mt][2] = nc.x; acc[mt][3] = nc.y;
-          }
-        }
+        const int q32 = 2 * t + h;       // 32-k half inside the warp's share of the stage
+        const int si = q32 / U32;        // segment inside the warp's share
+        const int j0 = (2 * (q32 % U32)) % kChains, j1 = (2 * (q32 % U32) + 1) % kChains;
         const uint32_t wl = words[2 * h], wh = words[2 * h + 1];  // rows g and g + 8
         const uint32_t wl8 = wl >> 8, wh8 = wh >> 8;
+#if AO_EXP == 2
+        const uint32_t a0l = wl, a1l = wl, a2l = wl8, a3l = wl8, a0h = wh, a1h = wh, a2h = wh8, a3h = wh8;
+#else
         const uint32_t a0l = nib_f16_lo(wl), a1l = nib_f16_hi(wl), a2l = nib_f16_lo(wl8), a3l = nib_f16_hi(wl8);
         const uint32_t a0h = nib_f16_lo(wh), a1h = nib_f16_hi(wh), a2h = nib_f16_lo(wh8), a3h = nib_f16_hi(wh8);
+#endif
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
           if (x_on[mt]) xx[mt] = lds128(x_u0[mt] + xo + q32 * 64);
-          mma_f16_16816(acc[mt], a0l, a0h, a1l, a1h, xx[mt].x, xx[mt].y);
-          mma_f16_16816(acc[mt], a2l, a2h, a3l, a3h, xx[mt].z, xx[mt].w);
+          if (2 * (q32 % U32) < kChains) {
+            if (j0 == 0) {  // chain 0 starts at -C, so the chains sum to  sum_k x_k (q_k - 8)
+              const float2 nc = lds64f(X_u + si * XS + 8 * MT * 4 + mt * 32);
+              acc[0][mt][0] = nc.x; acc[0][mt][1] = nc.y; acc[0][mt][2] = nc.x; acc[0][mt][3] = nc.y;
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) acc[j0][mt][e] = 0.f;
+            }
+          }
+          if (2 * (q32 % U32) + 1 < kChains) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[j1][mt][e] = 0.f;
+          }
+#if AO_EXP == 1
+          asm volatile("" ::"r"(a0l), "r"(a0h), "r"(a1l), "r"(a1h), "r"(a2l), "r"(a2h), "r"(a3l), "r"(a3h), "r"(xx[mt].x),
+                       "r"(xx[mt].y), "r"(xx[mt].z), "r"(xx[mt].w));
+#else
+          mma_f16_16816(acc[j0][mt], a0l, a0h, a1l, a1h, xx[mt].x, xx[mt].y);
+          mma_f16_16816(acc[j1][mt], a2l, a2h, a3l, a3h, xx[mt].z, xx[mt].w);
+#endif
         }
         if (q32 % U32 == U32 - 1) {
           // segment complete: y += s * acc + z * X   (fp32)
-          constexpr uint32_t kGrpStep = G < 128 ? 64u : 0u;  // bytes between the groups of consecutive segments
-          const uint32_t p0 = lds32(stage_u + sz_off_r + si * kGrpStep), p1 = lds32(stage_u + sz_off_r + si * kGrpStep + 32u);
+          const uint32_t ga = stage_u + sz_off_r + (uint32_t)((si * SEG) / G) * 64u;
+          const uint32_t p0 = lds32(ga), p1 = lds32(ga + 32u);
           const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
           const float z0 = __uint_as_float(p0 & 0xFFFF0000u), z1 = __uint_as_float(p1 & 0xFFFF0000u);
 #pragma unroll
           for (int mt = 0; mt < MT; ++mt) {
+            float a[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              a[e] = acc[0][mt][e];
+#pragma unroll
+              for (int j = 1; j < kChains; ++j) a[e] += acc[j][mt][e];
+            }
             const float2 X = lds64f(X_u + si * XS + mt * 32);
-            yacc[mt][0] = fmaf(sc0, acc[mt][0], fmaf(z0, X.x, yacc[mt][0]));
-            yacc[mt][1] = fmaf(sc0, acc[mt][1], fmaf(z0, X.y, yacc[mt][1]));
-            yacc[mt][2] = fmaf(sc1, acc[mt][2], fmaf(z1, X.x, yacc[mt][2]));
-            yacc[mt][3] = fmaf(sc1, acc[mt][3], fmaf(z1, X.y, yacc[mt][3]));
+            yacc[mt][0] = fmaf(sc0, a[0], fmaf(z0, X.x, yacc[mt][0]));
+            yacc[mt][1] = fmaf(sc0, a[1], fmaf(z0, X.y, yacc[mt][1]));
+            yacc[mt][2] = fmaf(sc1, a[2], fmaf(z1, X.x, yacc[mt][2]));
+            yacc[mt][3] = fmaf(sc1, a[3], fmaf(z1, X.y, yacc[mt][3]));
           }
         }
       }
@@ -361,7 +492,11 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
 
     uint32_t xo = 0, X_u = X_u0_r;
     for (int ch = 0; ch < n_chunks; ++ch) {
+      AO_TRACE(0, (strip - s0) * n_chunks + ch);
+#if AO_EXP != 3 && AO_EXP != 5
       mbar_wait(&full[slot], par);
+#endif
+      AO_TRACE(1, (strip - s0) * n_chunks + ch);
       if (ch < n_full) {
         consume(std::true_type{}, kStageTiles, xo, X_u, yacc);
       } else if (tl0 < KT - ch * kStageTiles) {
@@ -369,6 +504,7 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
+      AO_TRACE(2, (strip - s0) * n_chunks + ch);
       xo += kStageTiles * 128u;
       X_u += kXChunk;
       stage_u += kStageB;
@@ -379,64 +515,25 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
       }
     }
 
-    // ---- strip done: the 16 partials go to shared memory; ONE (rotating) warp sums them and runs the epilogue while
-    //      the others go straight on to the next strip (mbarrier hand-off, no rendezvous) ----
+    // ---- strip done: the 16 partials go to shared memory and the warp goes straight on to the next strip; the
+    //      epilogue warp sums them.  (A consumer doubling as the reducer falls behind by the reduction, the next
+    //      reducer has to wait for it, and the lag chains: strip time became compute + reduce, 2700 clk.) ----
+#if AO_EXP == 4 || AO_EXP == 5
+    if (yacc[0][0] == 123.456f) p.y[strip] = __float2bfloat16_rn(yacc[0][1] + yacc[0][2] + yacc[0][3]);
+    continue;
+#endif
     const int li = strip - s0;
-    const int rbuf = li & 1;
-    const uint32_t use = (uint32_t)(li >> 1);  // n-th use of this buffer
+    const int rbuf = li % kRedBufs;
+    const uint32_t use = (uint32_t)(li / kRedBufs);  // n-th use of this buffer
     float* rb = red + (size_t)rbuf * (kFConsumers * MT * 128);
-    if (use > 0) mbar_wait(&red_free[rbuf], (use - 1) & 1u);  // the reducer of two strips ago has read it
+    if (use > 0) mbar_wait(&red_free[rbuf], (use - 1) & 1u);  // the epilogue of kRedBufs strips ago has read it
+    AO_TRACE(3, li);
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt)
       *reinterpret_cast<float4*>(rb + ((warp * MT + mt) * 32 + lane) * 4) =
           make_float4(yacc[mt][0], yacc[mt][1], yacc[mt][2], yacc[mt][3]);
     __syncwarp();
     if (lane == 0) mbar_arrive(&red_full[rbuf]);
-    if (warp == (li % kFConsumers)) {
-      mbar_wait(&red_full[rbuf], use & 1u);
-#pragma unroll
-      for (int mt = 0; mt < MT; ++mt) {
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int w = 0; w < kFConsumers; ++w) {
-          const float4 v = *reinterpret_cast<const float4*>(rb + ((w * MT + mt) * 32 + lane) * 4);
-          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-        }
-        if (mt == MT - 1) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&red_free[rbuf]);
-        }
-        const float vals[2][2] = {{s.x, s.z}, {s.y, s.w}};  // [col j][row half]: rows g, g+8
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const int m = 8 * mt + 2 * c + j;
-          if (m >= p.M) continue;
-          const float rsc = row_scale[m];
-          const float v0 = vals[j][0] * rsc, v1 = vals[j][1] * rsc;
-          if (p.epilogue == kEpiSiluMul) {
-            // rows g = gate (w1), rows g+8 = up (w3) of output index 8*strip + g  (model.py:486)
-            const int64_t n = 8 * (int64_t)strip + g;
-            if (2 * n < p.N_out) {
-              const float gate = bf16r(v0), up = bf16r(v1);
-              const float sg = bf16r(gate / (1.f + __expf(-gate)));
-              p.y[m * p.ldy + n] = __float2bfloat16_rn(sg * up);
-            }
-          } else {
-            const int64_t n0 = 16 * (int64_t)strip + g;
-            if (p.epilogue == kEpiResidual) {
-              if (n0 < p.N_out)
-                p.y[m * p.ldy + n0] = __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0]) + bf16r(v0));
-              if (n0 + 8 < p.N_out)
-                p.y[m * p.ldy + n0 + 8] =
-                    __float2bfloat16_rn(__bfloat162float(p.residual[m * p.ld_res + n0 + 8]) + bf16r(v1));
-            } else {
-              if (n0 < p.N_out) p.y[m * p.ldy + n0] = __float2bfloat16_rn(v0);
-              if (n0 + 8 < p.N_out) p.y[m * p.ldy + n0 + 8] = __float2bfloat16_rn(v1);
-            }
-          }
-        }
-      }
-    }
   }
 }
 
@@ -465,8 +562,8 @@ static bool plan_fused(int M, int MT, int64_t Kp, int max_stages, FusedPlan& pl)
   pl.x_row_bytes = (uint32_t)(2 * Kp + 16);
   const size_t x_bytes = ((size_t)M * pl.x_row_bytes + 127) / 128 * 128;
   const size_t X_bytes = ((size_t)(Kp / (G < 128 ? G : 128)) * 2 * 8 * MT * 4 + 127) / 128 * 128;
-  const size_t red_bytes = (size_t)2 * kFConsumers * MT * 128 * 4;
-  const size_t misc = (16 * kFConsumers * 2 + 32) * 4 + (2 * 16 + 4) * 8 + 64;
+  const size_t red_bytes = (size_t)kRedBufs * kFConsumers * MT * 128 * 4;
+  const size_t misc = (16 * kFConsumers * 2 + 32) * 4 + (2 * 16 + 2 * kRedBufs) * 8 + 64;
   const size_t fixed = x_bytes + X_bytes + red_bytes + misc;
   static const size_t two_per_sm = []() {  // AO_B200_SMEM_KB: shared-memory budget per CTA (default: two CTAs per SM)
     const char* e = std::getenv("AO_B200_SMEM_KB");
@@ -502,7 +599,12 @@ static int launch_fused(GemvFusedParams& p, const FusedPlan& pl, bool pdl, cudaS
       return AO_B200_ERR_CUDA;
     attr_done = true;
   }
-  const int grid = p.n_strips < fused_sm_count() ? p.n_strips : fused_sm_count();
+  // AO_B200_CTAS: co-resident CTAs per SM of ONE launch (the 113 KB plan leaves room for two)
+  static const int ctas_per_sm = []() { const char* e = std::getenv("AO_B200_CTAS"); int v = e ? std::atoi(e) : 2; return v < 1 ? 1 : v; }();
+  const int max_grid = fused_sm_count() * (pl.smem <= 113 * 1024 && MT == 1 ? ctas_per_sm : 1);
+  const int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
+  p.strips_base = p.n_strips / grid;
+  p.strips_rem = p.n_strips % grid;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kFThreads);
