@@ -186,6 +186,15 @@ AO_B200_API int ao_b200_decode_attention(const void* q, const void* k_cache, con
 /* FeedForward gate (model.py:486): out = bf16( bf16(silu(gate)) * up ), gate_up bf16 [B][2*I] = [w1 x | w3 x]. */
 AO_B200_API int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64_t I, void* stream);
 
+/* sample (generate.py:79-100: logits_to_probs + multinomial_sample_one_no_sync) in one launch:
+ *   lg = float(logits) / max(temperature, 1e-5); entries below the top_k-th largest -> -inf (ties kept, top_k <= 0 or
+ *   >= V: keep all); probs = softmax(lg); next_tok[b] = argmax_i probs[i] / noise[b][i]  (first index on ties).
+ * noise fp32 [B][ldq] holds Exp(1) samples drawn by the CALLER (torch's exponential_ on the reference side), so the
+ * random stream stays the framework generator's.  temperature == 0: greedy argmax, noise may be null.
+ * logits bf16 [B][ldl], next_tok int64 [B]. */
+AO_B200_API int ao_b200_sample(const void* logits, int64_t ldl, int64_t B, int64_t V, float temperature, int top_k,
+                               const void* noise, int64_t ldq, void* next_tok, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -159,6 +159,7 @@ class DecodeEngine:
         self.attn_ws = torch.zeros(max(awb, 16), dtype=torch.uint8, device=dev)
         self.weight_bytes = sum(l.weight_bytes for l in lins) + 2 * (
             self.out_norm.numel() + sum(l["attn_norm"].numel() + l["ffn_norm"].numel() for l in self.layers))
+        self._noise = None
         self.graph = None
         self.launches_per_step = 0
 
@@ -254,17 +255,28 @@ class DecodeEngine:
         self.pos.add_(1)
 
     def _sample(self, logits):
-        """reference: generate.py:79-100 (temperature, top-k, gumbel-max multinomial)."""
+        """reference: generate.py:79-100 (temperature, top-k, exponential-noise argmax).  The Exp(1) noise is drawn by
+        torch's generator exactly as the reference draws it; everything else is one ao_b200_sample launch."""
+        noise = None
+        if self.temperature != 0.0:
+            if self._noise is None or self._noise.shape != logits.shape:
+                self._noise = torch.empty(logits.shape, dtype=torch.float32, device=logits.device)
+            noise = self._noise.exponential_(1)
+        _lib.check(_lib.lib().ao_b200_sample(
+            logits.data_ptr(), logits.stride(0), logits.shape[0], logits.shape[1], float(self.temperature),
+            0 if self.top_k is None else int(self.top_k), _ptr(noise), 0 if noise is None else noise.stride(0),
+            self.next_tok.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream), "sample")
+
+    def _sample_torch(self, logits):
+        """The reference's own op sequence (tests compare the kernel with it on the same noise)."""
         if self.temperature == 0.0:
-            torch.argmax(logits, dim=-1, out=self.next_tok)
-            return
+            return torch.argmax(logits, dim=-1)
         lg = logits.float() / max(self.temperature, 1e-5)
         if self.top_k is not None:
             v, _ = torch.topk(lg, min(self.top_k, lg.size(-1)))
             lg = torch.where(lg < v[..., -1:], -float("inf"), lg)
         probs = torch.softmax(lg, dim=-1)
-        q = torch.empty_like(probs).exponential_(1)
-        torch.argmax(probs / q, dim=-1, out=self.next_tok)
+        return torch.argmax(probs / self._noise, dim=-1)
 
     # ------------------------------------------------------------------ graph
     def capture(self):
