@@ -70,6 +70,10 @@ def main():
             e.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(), e.pos.data_ptr(), e.o.data_ptr(), B, e.H,
             e.Hkv, e.hd, e.S, 1.0 / math.sqrt(e.hd), e.n_split, e.attn_ws.data_ptr(), e.attn_ws.numel(), st()), "attn")
             for l in e.layers],
+        "attention_fused": lambda: [_lib.check(L.ao_b200_decode_attention_fused(
+            e.qkv.data_ptr(), e.freqs.data_ptr(), e.pos.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
+            e.o.data_ptr(), B, e.H, e.Hkv, e.hd, e.S, 1.0 / math.sqrt(e.hd), e.n_split, e.attn_fused_ws.data_ptr(),
+            e.attn_fused_ws.numel(), st()), "attn_fused") for l in e.layers],
         "wo": lambda: [l["wo"].launch_fused(e.o, e.h, st(), residual=e.h, epilogue=1) for l in e.layers],
         "w13": lambda: [l["w13"].launch_fused(e.h, e.s, st(), norm_w=l["ffn_norm"], eps=e.eps, epilogue=2) for l in e.layers],
         "w2": lambda: [l["w2"].launch_fused(e.s, e.h, st(), residual=e.h, epilogue=1) for l in e.layers],

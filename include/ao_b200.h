@@ -183,6 +183,17 @@ AO_B200_API int ao_b200_decode_attention(const void* q, const void* k_cache, con
                              const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim, int S,
                              float scale, int n_split, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Attention.forward for ONE new token in one launch (model.py:405-440): RoPE on q and the new k (model.py:547-559),
+ * KV append at *input_pos (KVCache.update, model.py:175-192), GQA softmax(q K^T * scale) V over positions 0..pos split
+ * n_split ways, partials merged by the last CTA to finish.  qkv bf16 [B][(H + 2 Hkv) * 128] (the wqkv output), caches
+ * bf16 [B][Hkv][S][128], out bf16 [B][H * 128].  workspace: ao_b200_decode_attention_fused_workspace_bytes, ZEROED
+ * once by the caller (the kernel leaves its tickets zeroed).  Programmatic-dependent-launch aware. */
+AO_B200_API int64_t ao_b200_decode_attention_fused_workspace_bytes(int B, int H, int Hkv, int n_split);
+AO_B200_API int ao_b200_decode_attention_fused(const void* qkv, const void* freqs_cis, const int32_t* input_pos,
+                                               void* k_cache, void* v_cache, void* out, int B, int H, int Hkv,
+                                               int head_dim, int S, float scale, int n_split, void* workspace,
+                                               int64_t workspace_bytes, void* stream);
+
 /* FeedForward gate (model.py:486): out = bf16( bf16(silu(gate)) * up ), gate_up bf16 [B][2*I] = [w1 x | w3 x]. */
 AO_B200_API int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64_t I, void* stream);
 

@@ -33,11 +33,15 @@ SIGNATURES = {
     "ao_b200_rope_kv_append": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "ao_b200_decode_attention_workspace_bytes": [_i32, _i32, _i32],
     "ao_b200_decode_attention": [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp, _i64, _vp],
+    "ao_b200_decode_attention_fused_workspace_bytes": [_i32, _i32, _i32, _i32],
+    "ao_b200_decode_attention_fused": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp, _i64,
+                                       _vp],
     "ao_b200_silu_mul": [_vp, _vp, _i64, _i64, _vp],
     "ao_b200_sample": [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _i64, _vp, _vp],
 }
 _RESTYPES = {"ao_b200_error_string": ctypes.c_char_p, "ao_b200_int4_mm_workspace_bytes": _i64,
-             "ao_b200_decode_attention_workspace_bytes": _i64}
+             "ao_b200_decode_attention_workspace_bytes": _i64,
+             "ao_b200_decode_attention_fused_workspace_bytes": _i64}
 
 DIV_IEEE, DIV_RECIP = 0, 1
 

@@ -157,6 +157,8 @@ class DecodeEngine:
         self.n_split = max(1, min(64, -(-self.S // 16)))
         awb = int(_lib.lib().ao_b200_decode_attention_workspace_bytes(B, self.H, self.n_split))
         self.attn_ws = torch.zeros(max(awb, 16), dtype=torch.uint8, device=dev)
+        fwb = int(_lib.lib().ao_b200_decode_attention_fused_workspace_bytes(B, self.H, self.Hkv, self.n_split))
+        self.attn_fused_ws = torch.zeros(fwb, dtype=torch.uint8, device=dev)  # zeroed once: the kernel keeps its tickets 0
         self.weight_bytes = sum(l.weight_bytes for l in lins) + 2 * (
             self.out_norm.numel() + sum(l["attn_norm"].numel() + l["ffn_norm"].numel() for l in self.layers))
         self._noise = None
@@ -169,7 +171,7 @@ class DecodeEngine:
         self.launches_per_step += 1
 
     def _launch_step_fused(self):
-        """5 GEMVs + RoPE/KV-append + attention per layer: the two RMSNorms, both residual adds and SiLU*mul live in
+        """4 GEMVs + one RoPE/KV-append/attention launch per layer: the two RMSNorms, both residual adds and SiLU*mul live in
         the GEMV prologues / epilogues (include/ao_b200.h, ao_b200_int4_gemv_fused)."""
         L = _lib.lib()
         st = torch.cuda.current_stream(self.device).cuda_stream
@@ -178,13 +180,11 @@ class DecodeEngine:
         torch.index_select(self.emb, 0, self.tok, out=self.h)
         for l in self.layers:
             l["wqkv"].launch_fused(self.h, self.qkv, st, norm_w=l["attn_norm"], eps=self.eps)
-            _lib.check(L.ao_b200_rope_kv_append(self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(),
-                                                self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
-                                                B, self.H, self.Hkv, self.hd, self.S, st), "rope_kv_append")
-            _lib.check(L.ao_b200_decode_attention(self.q.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
-                                                  self.pos.data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd,
-                                                  self.S, 1.0 / math.sqrt(self.hd), self.n_split,
-                                                  self.attn_ws.data_ptr(), self.attn_ws.numel(), st), "decode_attention")
+            _lib.check(L.ao_b200_decode_attention_fused(
+                self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(), l["k_cache"].data_ptr(),
+                l["v_cache"].data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd, self.S,
+                1.0 / math.sqrt(self.hd), self.n_split, self.attn_fused_ws.data_ptr(), self.attn_fused_ws.numel(), st),
+                "decode_attention_fused")
             if self.tp is None:
                 l["wo"].launch_fused(self.o, self.h, st, residual=self.h, epilogue=1)
             else:
@@ -196,7 +196,7 @@ class DecodeEngine:
             else:
                 l["w2"].launch_fused(self.s, self.delta, st)
                 self.tp.all_reduce_add(self.delta, self.h)
-            n += 6 + (1 if self.n_split > 1 else 0)
+            n += 5
         self.output.launch_fused(self.h, self.logits, st, norm_w=self.out_norm, eps=self.eps)
         self.launches_per_step = n + 1
         logits = self.logits

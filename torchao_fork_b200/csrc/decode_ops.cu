@@ -189,6 +189,142 @@ __global__ void decode_attn_merge_kernel(const float* __restrict__ part_o, const
   out[bh * hd + d] = __float2bfloat16_rn(acc / l);
 }
 
+// ---------------------------------------------------------------------------------------
+// RoPE + KV append + GQA decode attention + split merge in ONE launch (PDL-aware): what Attention.forward does for
+// one new token (model.py:405-440).  Grid (Hkv, B, n_split), one warp per q head of the group.
+//   * every CTA ropes its own q heads from qkv (fp32 math on bf16 cos/sin, rounded to bf16 like the reference);
+//   * the CTA whose split contains position `pos` ropes the new k, appends k and v to the caches, then walks it;
+//   * splits leave (m, l, acc) partials in the workspace; the LAST CTA of a (b, kv head) to finish (atomic ticket, no
+//     spinning) merges them and writes the bf16 output, and resets the ticket for the next launch.
+// ---------------------------------------------------------------------------------------
+template <int kGroup>
+__global__ void __launch_bounds__(kGroup * 32) decode_attn_fused_kernel(
+    const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ freqs,
+    const int32_t* __restrict__ input_pos, __nv_bfloat16* __restrict__ k_cache, __nv_bfloat16* __restrict__ v_cache,
+    __nv_bfloat16* __restrict__ out, float* __restrict__ part_o, float* __restrict__ part_ml,
+    unsigned int* __restrict__ tickets, int H, int Hkv, int S, float scale, int n_split) {
+  constexpr int hd = 128;
+  __shared__ int s_last;
+  grid_launch_dependents();
+  const int kvh = blockIdx.x, b = blockIdx.y, split = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = kvh * kGroup + warp;
+  const int heads = H + 2 * Hkv;
+  grid_dependency_wait();
+  const int pos = *input_pos;
+  const int len = pos + 1;
+  const int chunk = (len + n_split - 1) / n_split;
+  const int j0 = split * chunk, j1 = min(len, j0 + chunk);
+
+  // cos/sin of this lane's two pairs (dims 4 lane .. 4 lane + 3)
+  const uint2 cs = *reinterpret_cast<const uint2*>(freqs + ((int64_t)pos * (hd / 2) + 2 * lane) * 2);
+  const float c0 = __uint_as_float(cs.x << 16), s0 = __uint_as_float(cs.x & 0xFFFF0000u);
+  const float c1 = __uint_as_float(cs.y << 16), s1 = __uint_as_float(cs.y & 0xFFFF0000u);
+  auto rope4 = [&](uint2 raw) {
+    const float x0 = __uint_as_float(raw.x << 16), x1 = __uint_as_float(raw.x & 0xFFFF0000u);
+    const float x2 = __uint_as_float(raw.y << 16), x3 = __uint_as_float(raw.y & 0xFFFF0000u);
+    uint2 o;
+    o.x = float_to_bf16_bits(x0 * c0 - x1 * s0) | (float_to_bf16_bits(x1 * c0 + x0 * s0) << 16);
+    o.y = float_to_bf16_bits(x2 * c1 - x3 * s1) | (float_to_bf16_bits(x3 * c1 + x2 * s1) << 16);
+    return o;
+  };
+  __nv_bfloat16* kb = k_cache + ((int64_t)b * Hkv + kvh) * S * hd + lane * 4;
+  __nv_bfloat16* vb = v_cache + ((int64_t)b * Hkv + kvh) * S * hd + lane * 4;
+  if (j0 <= pos && pos < j1) {  // block-uniform: this CTA owns the new position
+    if (warp == 0) {
+      const uint2 kraw = *reinterpret_cast<const uint2*>(qkv + ((int64_t)b * heads + H + kvh) * hd + lane * 4);
+      const uint2 vraw = *reinterpret_cast<const uint2*>(qkv + ((int64_t)b * heads + H + Hkv + kvh) * hd + lane * 4);
+      *reinterpret_cast<uint2*>(kb + (int64_t)pos * hd) = rope4(kraw);
+      *reinterpret_cast<uint2*>(vb + (int64_t)pos * hd) = vraw;
+    }
+    __syncthreads();
+  }
+  float qv[4];
+  {
+    const uint2 r = rope4(*reinterpret_cast<const uint2*>(qkv + ((int64_t)b * heads + h) * hd + lane * 4));
+    qv[0] = __uint_as_float(r.x << 16) * scale;
+    qv[1] = __uint_as_float(r.x & 0xFFFF0000u) * scale;
+    qv[2] = __uint_as_float(r.y << 16) * scale;
+    qv[3] = __uint_as_float(r.y & 0xFFFF0000u) * scale;
+  }
+  float m = -INFINITY, l = 0.f, acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = j0; j < j1; j += 4) {
+    // four positions per trip: the loads and the four reductions are independent
+    uint2 kr[4], vr[4];
+    float sc[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int jj = min(j + u, j1 - 1);
+      kr[u] = *reinterpret_cast<const uint2*>(kb + (int64_t)jj * hd);
+      vr[u] = *reinterpret_cast<const uint2*>(vb + (int64_t)jj * hd);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      sc[u] = qv[0] * __uint_as_float(kr[u].x << 16) + qv[1] * __uint_as_float(kr[u].x & 0xFFFF0000u) +
+              qv[2] * __uint_as_float(kr[u].y << 16) + qv[3] * __uint_as_float(kr[u].y & 0xFFFF0000u);
+#pragma unroll
+    for (int o = 16; o; o >>= 1)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) sc[u] += __shfl_xor_sync(0xffffffffu, sc[u], o);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (j + u >= j1) break;
+      const float m_new = fmaxf(m, sc[u]);
+      const float corr = __expf(m - m_new);
+      const float p = __expf(sc[u] - m_new);
+      l = l * corr + p;
+      acc[0] = acc[0] * corr + p * __uint_as_float(vr[u].x << 16);
+      acc[1] = acc[1] * corr + p * __uint_as_float(vr[u].x & 0xFFFF0000u);
+      acc[2] = acc[2] * corr + p * __uint_as_float(vr[u].y << 16);
+      acc[3] = acc[3] * corr + p * __uint_as_float(vr[u].y & 0xFFFF0000u);
+      m = m_new;
+    }
+  }
+  if (n_split == 1) {
+    const float inv = 1.f / l;
+    uint2 o;
+    o.x = float_to_bf16_bits(acc[0] * inv) | (float_to_bf16_bits(acc[1] * inv) << 16);
+    o.y = float_to_bf16_bits(acc[2] * inv) | (float_to_bf16_bits(acc[3] * inv) << 16);
+    *reinterpret_cast<uint2*>(out + ((int64_t)b * H + h) * hd + lane * 4) = o;
+    return;
+  }
+  {
+    const int64_t slot = ((int64_t)b * H + h) * n_split + split;
+    *reinterpret_cast<float4*>(part_o + slot * hd + lane * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    if (lane == 0) {
+      part_ml[slot * 2] = m;
+      part_ml[slot * 2 + 1] = l;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&tickets[b * Hkv + kvh], 1u);
+    s_last = (t == (unsigned int)n_split - 1);
+    if (s_last) tickets[b * Hkv + kvh] = 0;  // every split has arrived: ready for the next launch
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // merge the n_split partials of this warp's q head
+  const int64_t bh = (int64_t)b * H + h;
+  float mm = -INFINITY;
+  for (int s = 0; s < n_split; ++s) mm = fmaxf(mm, __ldcg(part_ml + (bh * n_split + s) * 2));
+  float ll = 0.f, a[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int s = 0; s < n_split; ++s) {
+    const float ms = __ldcg(part_ml + (bh * n_split + s) * 2), ls = __ldcg(part_ml + (bh * n_split + s) * 2 + 1);
+    const float w = (ls > 0.f) ? __expf(ms - mm) : 0.f;
+    const float4 po = __ldcg(reinterpret_cast<const float4*>(part_o + (bh * n_split + s) * hd + lane * 4));
+    ll += ls * w;
+    a[0] += po.x * w; a[1] += po.y * w; a[2] += po.z * w; a[3] += po.w * w;
+  }
+  const float inv = 1.f / ll;
+  uint2 o;
+  o.x = float_to_bf16_bits(a[0] * inv) | (float_to_bf16_bits(a[1] * inv) << 16);
+  o.y = float_to_bf16_bits(a[2] * inv) | (float_to_bf16_bits(a[3] * inv) << 16);
+  *reinterpret_cast<uint2*>(out + bh * hd + lane * 4) = o;
+}
+
 // out = bf16( bf16(silu(gate)) * up ), gate_up = [B][2I] (rows of w1 then rows of w3) — model.py:486
 __global__ void silu_mul_kernel(const __nv_bfloat16* __restrict__ gate_up, __nv_bfloat16* __restrict__ out, int64_t B,
                                 int64_t I) {
@@ -277,6 +413,52 @@ extern "C" int ao_b200_decode_attention(const void* q, const void* k_cache, cons
 #undef AO_ATTN
   if (n_split > 1)
     decode_attn_merge_kernel<<<B * H, 128, 0, s>>>(part_o, part_ml, op, n_split);
+  return ao_launch_status();
+}
+
+extern "C" int64_t ao_b200_decode_attention_fused_workspace_bytes(int B, int H, int Hkv, int n_split) {
+  return (int64_t)B * H * n_split * (128 + 2) * sizeof(float) + (int64_t)B * Hkv * sizeof(unsigned int);
+}
+
+extern "C" int ao_b200_decode_attention_fused(const void* qkv, const void* freqs_cis, const int32_t* input_pos,
+                                              void* k_cache, void* v_cache, void* out, int B, int H, int Hkv,
+                                              int head_dim, int S, float scale, int n_split, void* workspace,
+                                              int64_t workspace_bytes, void* stream) {
+  AO_CHECK_ARG(qkv && freqs_cis && input_pos && k_cache && v_cache && out && workspace);
+  AO_CHECK_ARG(B > 0 && H > 0 && Hkv > 0 && S > 0 && n_split >= 1 && n_split <= 65535);
+  if (head_dim != 128 || H % Hkv != 0) return AO_B200_ERR_UNSUPPORTED;
+  if (workspace_bytes < ao_b200_decode_attention_fused_workspace_bytes(B, H, Hkv, n_split)) return AO_B200_ERR_WORKSPACE;
+  const int group = H / Hkv;
+  float* part_o = static_cast<float*>(workspace);
+  float* part_ml = part_o + (int64_t)B * H * n_split * 128;
+  unsigned int* tickets = reinterpret_cast<unsigned int*>(part_ml + (int64_t)B * H * n_split * 2);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(Hkv, B, n_split);
+  cfg.blockDim = dim3(group * 32);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  auto qp = static_cast<const __nv_bfloat16*>(qkv);
+  auto fp = static_cast<const __nv_bfloat16*>(freqs_cis);
+  auto kp = static_cast<__nv_bfloat16*>(k_cache);
+  auto vp = static_cast<__nv_bfloat16*>(v_cache);
+  auto op = static_cast<__nv_bfloat16*>(out);
+  cudaError_t e;
+#define AO_ATTN(G)                                                                                                  \
+  e = cudaLaunchKernelEx(&cfg, decode_attn_fused_kernel<G>, qp, fp, input_pos, kp, vp, op, part_o, part_ml, tickets, H, \
+                         Hkv, S, scale, n_split)
+  switch (group) {
+    case 1: AO_ATTN(1); break;
+    case 2: AO_ATTN(2); break;
+    case 4: AO_ATTN(4); break;
+    case 8: AO_ATTN(8); break;
+    default: return AO_B200_ERR_UNSUPPORTED;
+  }
+#undef AO_ATTN
+  if (e != cudaSuccess) return AO_B200_ERR_CUDA;
   return ao_launch_status();
 }
 
