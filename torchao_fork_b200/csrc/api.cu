@@ -7,6 +7,9 @@ int int4_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* pac
 int int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
                     int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
                     const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
+int int4_gemv_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+                 int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
+                 int64_t ld_res, int epilogue, bool pdl, cudaStream_t s);
 int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
               void* y, int64_t ldy, cudaStream_t s);
 }  // namespace ao
@@ -27,7 +30,7 @@ extern "C" int ao_b200_abi_version(void) { return 1; }
 #include <cstdlib>
 namespace {
 struct Tunables {
-  int gemv_version, stages, pdl;
+  int gemv_version, stages, pdl, gemv_tc;
   Tunables() {
     const char* v = std::getenv("AO_B200_GEMV");
     gemv_version = v ? std::atoi(v) : 3;
@@ -37,6 +40,8 @@ struct Tunables {
     if (stages > 16) stages = 16;
     const char* pd = std::getenv("AO_B200_PDL");
     pdl = pd ? std::atoi(pd) : 1;
+    const char* tc = std::getenv("AO_B200_GEMV_TC");  // 1: tcgen05 / tensor-memory decode GEMV where it applies
+    gemv_tc = tc ? std::atoi(tc) : 0;
   }
 };
 const Tunables& tunables() {
@@ -66,6 +71,12 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
     int e = AO_B200_ERR_WORKSPACE;
+    if (tunables().gemv_tc && mc <= 5) {
+      e = ao::int4_gemv_tc(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out, ldy,
+                           nullptr, 0.f, nullptr, 0, 0, tunables().pdl != 0, s);
+      if (e == AO_B200_OK) continue;
+      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+    }
     if (tunables().gemv_version == 3) {
       e = ao::int4_gemv_fused(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
                               N_out, ldy, nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
@@ -94,6 +105,12 @@ extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int
   AO_CHECK_ARG(!norm_weight || ao_aligned(norm_weight, 16));
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0);
+  if (tunables().gemv_tc) {
+    // tensor-memory kernel (M <= 5, Np % 128 == 0, activations + >= 3 ring stages must fit); else the mma.sync kernel
+    const int e = ao::int4_gemv_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
+                                   norm_eps, residual, ld_res, epilogue, tunables().pdl != 0, static_cast<cudaStream_t>(stream));
+    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+  }
   return ao::int4_gemv_fused(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
                              norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,
                              static_cast<cudaStream_t>(stream));
