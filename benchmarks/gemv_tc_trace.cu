@@ -10,6 +10,7 @@
 #include <cstdio>
 
 int main(int argc, char** argv) {
+  const bool pdl_flag = getenv("PDL") != nullptr;
   const int64_t N = argc > 1 ? atoll(argv[1]) : 128256, K = argc > 2 ? atoll(argv[2]) : 4096;
   const int G = 128, M = argc > 3 ? atoi(argv[3]) : 1;
   const int copies = argc > 4 ? atoi(argv[4]) : 4;
@@ -25,18 +26,22 @@ int main(int argc, char** argv) {
   cudaMemset(w, 0x5a, wbytes * copies);
   cudaMemset(sz, 0x3c, szbytes * copies);
   cudaMemset(x, 0x3c, M * K * 2);
+  void* ws;
+  const int64_t wsb = ao::int4_gemv_tc_workspace_bytes(Np);
+  cudaMalloc(&ws, wsb);
+  cudaMemset(ws, 0, wsb);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
   int rc = 0;
   for (int it = 0; it < 2 * copies; ++it)
     rc |= ao::int4_gemv_tc(x, M, K, K, w + (it % copies) * wbytes, sz + (it % copies) * (szbytes / 4), Np, Kp, G, y, N, Np, nullptr,
-                           0.f, nullptr, 0, 0, false, 0);
+                           0.f, nullptr, 0, 0, ws, wsb, pdl_flag, 0);
   cudaDeviceSynchronize();
   cudaEventRecord(e0);
   for (int it = 0; it < 3 * copies; ++it)
     rc |= ao::int4_gemv_tc(x, M, K, K, w + (it % copies) * wbytes, sz + (it % copies) * (szbytes / 4), Np, Kp, G, y, N, Np, nullptr,
-                           0.f, nullptr, 0, 0, false, 0);
+                           0.f, nullptr, 0, 0, ws, wsb, pdl_flag, 0);
   cudaEventRecord(e1);
   cudaDeviceSynchronize();
   float ms;

@@ -12,6 +12,7 @@
 #include <vector>
 
 int main(int argc, char** argv) {
+  const bool pdl_flag = getenv("PDL") != nullptr;
   const int64_t N = argc > 1 ? atoll(argv[1]) : 128256, K = argc > 2 ? atoll(argv[2]) : 4096;
   const int G = 128, M = argc > 3 ? atoi(argv[3]) : 1;
   const int max_stages = argc > 4 ? atoi(argv[4]) : 16;
@@ -34,12 +35,12 @@ int main(int argc, char** argv) {
   int rc = 0;
   for (int it = 0; it < 3 * copies; ++it)
     rc |= ao::int4_gemv_fused(x, M, K, K, w + (it % copies) * wbytes, sz + (it % copies) * (szbytes / 4), Np, Kp, G, y, N, Np,
-                              nullptr, 0.f, nullptr, 0, 0, max_stages, false, 0);
+                              nullptr, 0.f, nullptr, 0, 0, max_stages, pdl_flag, 0);
   cudaDeviceSynchronize();
   cudaEventRecord(e0);
   for (int it = 0; it < 5 * copies; ++it)
     rc |= ao::int4_gemv_fused(x, M, K, K, w + (it % copies) * wbytes, sz + (it % copies) * (szbytes / 4), Np, Kp, G, y, N, Np,
-                              nullptr, 0.f, nullptr, 0, 0, max_stages, false, 0);
+                              nullptr, 0.f, nullptr, 0, 0, max_stages, pdl_flag, 0);
   cudaEventRecord(e1);
   cudaDeviceSynchronize();
   float ms;

@@ -62,7 +62,7 @@ def main():
         return torch.cuda.current_stream().cuda_stream
 
     kinds = {
-        "wqkv": lambda: [l["wqkv"].launch_fused(e.h, e.qkv, st(), norm_w=l["attn_norm"], eps=e.eps) for l in e.layers],
+        "wqkv": lambda: [l["wqkv"].launch_fused(e.h, e.qkv, st(), norm_w=l["attn_norm"], eps=e.eps, ws=e.ws) for l in e.layers],
         "rope_kv_append": lambda: [_lib.check(L.ao_b200_rope_kv_append(
             e.qkv.data_ptr(), e.freqs.data_ptr(), e.pos.data_ptr(), e.q.data_ptr(), l["k_cache"].data_ptr(),
             l["v_cache"].data_ptr(), B, e.H, e.Hkv, e.hd, e.S, st()), "rope") for l in e.layers],
@@ -74,10 +74,10 @@ def main():
             e.qkv.data_ptr(), e.freqs.data_ptr(), e.pos.data_ptr(), l["k_cache"].data_ptr(), l["v_cache"].data_ptr(),
             e.o.data_ptr(), B, e.H, e.Hkv, e.hd, e.S, 1.0 / math.sqrt(e.hd), e.n_split, e.attn_fused_ws.data_ptr(),
             e.attn_fused_ws.numel(), st()), "attn_fused") for l in e.layers],
-        "wo": lambda: [l["wo"].launch_fused(e.o, e.h, st(), residual=e.h, epilogue=1) for l in e.layers],
-        "w13": lambda: [l["w13"].launch_fused(e.h, e.s, st(), norm_w=l["ffn_norm"], eps=e.eps, epilogue=2) for l in e.layers],
-        "w2": lambda: [l["w2"].launch_fused(e.s, e.h, st(), residual=e.h, epilogue=1) for l in e.layers],
-        "output": lambda: e.output.launch_fused(e.h, e.logits, st(), norm_w=e.out_norm, eps=e.eps),
+        "wo": lambda: [l["wo"].launch_fused(e.o, e.h, st(), residual=e.h, epilogue=1, ws=e.ws) for l in e.layers],
+        "w13": lambda: [l["w13"].launch_fused(e.h, e.s, st(), norm_w=l["ffn_norm"], eps=e.eps, epilogue=2, ws=e.ws) for l in e.layers],
+        "w2": lambda: [l["w2"].launch_fused(e.s, e.h, st(), residual=e.h, epilogue=1, ws=e.ws) for l in e.layers],
+        "output": lambda: e.output.launch_fused(e.h, e.logits, st(), norm_w=e.out_norm, eps=e.eps, ws=e.ws),
         "sample": lambda: e._sample(e.logits),
         "embed+bookkeeping": lambda: (torch.index_select(e.emb, 0, e.tok, out=e.h), e.tok.copy_(e.next_tok), e.pos.add_(1)),
     }

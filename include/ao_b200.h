@@ -135,13 +135,15 @@ AO_B200_API int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ld
  *   epilogue 2 (silu*mul): the packed weight holds w1 and w3 interleaved 8 rows / 8 rows per 16-row strip
  *                         (ops.interleave_gate_up); y[m][i] = bf16(bf16(silu(bf16(gate_i))) * bf16(up_i)), i < N_out/2.
  * Arithmetic: the affine dequant is applied per group in fp32 to the tensor-core partial sums (the fp32 dequant of
- * the reference's _weight_int4pack_mm_for_cpu) — see csrc/gemv_int4_fused.cu.  Returns AO_B200_ERR_WORKSPACE when
- * M * K does not fit the kernel's shared-memory staging (use ao_b200_int4_mm then). */
+ * the reference's _weight_int4pack_mm_for_cpu) — see csrc/gemv_int4_fused.cu, csrc/gemv_int4_tc.cu.
+ * workspace: ao_b200_int4_mm_workspace_bytes(M, Np, Kp) bytes, zero-initialised once by the caller (the kernels leave
+ * it zeroed); with NULL / too small a workspace the call still works but skips the tensor-memory kernel.  Returns
+ * AO_B200_ERR_WORKSPACE when M * K does not fit any decode kernel's shared-memory staging (use ao_b200_int4_mm then). */
 AO_B200_API int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx,
                             const void* packed, const void* scale_and_zero, int64_t Np, int64_t Kp,
                             int group_size, void* y, int64_t N_out, int64_t ldy,
                             const void* norm_weight, float norm_eps, const void* residual, int64_t ld_res,
-                            int epilogue, void* stream);
+                            int epilogue, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- int8 -------------- */
 

@@ -95,9 +95,11 @@ def test_residual_epilogue_in_place(m):
     # the C ABI allows y to alias the residual (the decode engine updates the residual stream in place)
     from torchao_fork_b200 import _lib
     h2 = h.clone()
-    _lib.check(_lib.lib().ao_b200_int4_gemv_fused(x.data_ptr(), m, k, k, packed.data_ptr(), sz.data_ptr(), n, k, gs,
-                                                 h2.data_ptr(), n, n, None, 0.0, h2.data_ptr(), n, 1,
-                                                 torch.cuda.current_stream().cuda_stream), "fused")
+    L = _lib.lib()
+    ws = torch.zeros(max(16, int(L.ao_b200_int4_mm_workspace_bytes(m, n, k))), dtype=torch.uint8, device=DEV)
+    _lib.check(L.ao_b200_int4_gemv_fused(x.data_ptr(), m, k, k, packed.data_ptr(), sz.data_ptr(), n, k, gs,
+                                         h2.data_ptr(), n, n, None, 0.0, h2.data_ptr(), n, 1, ws.data_ptr(), ws.numel(),
+                                         torch.cuda.current_stream().cuda_stream), "fused")
     assert torch.equal(h2, y)
 
 

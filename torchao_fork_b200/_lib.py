@@ -26,7 +26,7 @@ SIGNATURES = {
     "ao_b200_int4_mm_workspace_bytes": [_i64, _i64, _i64],
     "ao_b200_int4_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _i64, _i64, _vp, _i64, _vp],
     "ao_b200_int4_gemv_fused": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _i64, _i64, _vp, _f32, _vp, _i64,
-                                _i32, _vp],
+                                _i32, _vp, _i64, _vp],
     "ao_b200_int8_quantize": [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _vp, _vp],
     "ao_b200_int8_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp],
     "ao_b200_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _vp],

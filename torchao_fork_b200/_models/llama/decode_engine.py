@@ -71,13 +71,14 @@ class _Linear:
             return 0
         return int(_lib.lib().ao_b200_int4_mm_workspace_bytes(m, self.np_, self.kp))
 
-    def launch_fused(self, x, y, stream, norm_w=None, eps=0.0, residual=None, epilogue=0):
+    def launch_fused(self, x, y, stream, norm_w=None, eps=0.0, residual=None, epilogue=0, ws=None):
         """ao_b200_int4_gemv_fused: RMSNorm prologue (norm_w), epilogue 0 plain / 1 residual add / 2 SiLU*mul."""
         assert self.kind == "int4"
         _lib.check(_lib.lib().ao_b200_int4_gemv_fused(
             x.data_ptr(), x.shape[0], self.k, x.stride(0), self.packed.data_ptr(), self.sz.data_ptr(), self.np_,
             self.kp, self.group_size, y.data_ptr(), self.n, y.stride(0), _ptr(norm_w), eps, _ptr(residual),
-            0 if residual is None else residual.stride(0), epilogue, stream), "int4_gemv_fused")
+            0 if residual is None else residual.stride(0), epilogue, _ptr(ws), 0 if ws is None else ws.numel(), stream),
+            "int4_gemv_fused")
 
     def fused_fits(self, m):
         return self.kind == "int4" and m * (2 * self.kp + 16) <= 150 * 1024
@@ -179,25 +180,25 @@ class DecodeEngine:
         n = 0
         torch.index_select(self.emb, 0, self.tok, out=self.h)
         for l in self.layers:
-            l["wqkv"].launch_fused(self.h, self.qkv, st, norm_w=l["attn_norm"], eps=self.eps)
+            l["wqkv"].launch_fused(self.h, self.qkv, st, norm_w=l["attn_norm"], eps=self.eps, ws=self.ws)
             _lib.check(L.ao_b200_decode_attention_fused(
                 self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(), l["k_cache"].data_ptr(),
                 l["v_cache"].data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd, self.S,
                 1.0 / math.sqrt(self.hd), self.n_split, self.attn_fused_ws.data_ptr(), self.attn_fused_ws.numel(), st),
                 "decode_attention_fused")
             if self.tp is None:
-                l["wo"].launch_fused(self.o, self.h, st, residual=self.h, epilogue=1)
+                l["wo"].launch_fused(self.o, self.h, st, residual=self.h, epilogue=1, ws=self.ws)
             else:
-                l["wo"].launch_fused(self.o, self.delta, st)
+                l["wo"].launch_fused(self.o, self.delta, st, ws=self.ws)
                 self.tp.all_reduce_add(self.delta, self.h)
-            l["w13"].launch_fused(self.h, self.s, st, norm_w=l["ffn_norm"], eps=self.eps, epilogue=2)
+            l["w13"].launch_fused(self.h, self.s, st, norm_w=l["ffn_norm"], eps=self.eps, epilogue=2, ws=self.ws)
             if self.tp is None:
-                l["w2"].launch_fused(self.s, self.h, st, residual=self.h, epilogue=1)
+                l["w2"].launch_fused(self.s, self.h, st, residual=self.h, epilogue=1, ws=self.ws)
             else:
-                l["w2"].launch_fused(self.s, self.delta, st)
+                l["w2"].launch_fused(self.s, self.delta, st, ws=self.ws)
                 self.tp.all_reduce_add(self.delta, self.h)
             n += 5
-        self.output.launch_fused(self.h, self.logits, st, norm_w=self.out_norm, eps=self.eps)
+        self.output.launch_fused(self.h, self.logits, st, norm_w=self.out_norm, eps=self.eps, ws=self.ws)
         self.launches_per_step = n + 1
         logits = self.logits
         if self.tp is not None:

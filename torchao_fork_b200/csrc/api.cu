@@ -9,7 +9,8 @@ int int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const voi
                     const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
 int int4_gemv_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
                  int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
-                 int64_t ld_res, int epilogue, bool pdl, cudaStream_t s);
+                 int64_t ld_res, int epilogue, void* workspace, int64_t workspace_bytes, bool pdl, cudaStream_t s);
+int64_t int4_gemv_tc_workspace_bytes(int64_t Np);
 int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
               void* y, int64_t ldy, cudaStream_t s);
 }  // namespace ao
@@ -25,7 +26,7 @@ extern "C" const char* ao_b200_error_string(int code) {
   return "unknown error";
 }
 
-extern "C" int ao_b200_abi_version(void) { return 1; }
+extern "C" int ao_b200_abi_version(void) { return 2; }
 
 #include <cstdlib>
 namespace {
@@ -40,8 +41,11 @@ struct Tunables {
     if (stages > 16) stages = 16;
     const char* pd = std::getenv("AO_B200_PDL");
     pdl = pd ? std::atoi(pd) : 1;
-    const char* tc = std::getenv("AO_B200_GEMV_TC");  // 1: tcgen05 / tensor-memory decode GEMV where it applies
-    gemv_tc = tc ? std::atoi(tc) : 0;
+    // tcgen05 / tensor-memory decode GEMV: 0 never, 1 wherever it applies, 2 (default) for large weights only — its
+    // steady-state rate is higher (5.2 vs 4.6 TB/s) but its per-launch cost is ~3 us more (no co-residency with its
+    // neighbours in a PDL chain: it takes the whole SM's shared and tensor memory)
+    const char* tc = std::getenv("AO_B200_GEMV_TC");
+    gemv_tc = tc ? std::atoi(tc) : 2;
   }
 };
 const Tunables& tunables() {
@@ -51,8 +55,10 @@ const Tunables& tunables() {
 }  // namespace
 
 extern "C" int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
-  (void)M; (void)Np; (void)Kp;
-  return 0;  // the strip-parallel GEMVs reduce inside the CTA: no cross-CTA workspace (kept in the ABI for split-K kernels)
+  (void)M; (void)Kp;
+  // tickets + partial sums of the tensor-memory GEMV's split-K (row blocks shared by neighbouring CTAs); the mma.sync
+  // kernels reduce inside the CTA and need none
+  return ao::int4_gemv_tc_workspace_bytes(Np);
 }
 
 extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
@@ -62,7 +68,6 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   AO_CHECK_ARG(M > 0 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
   AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx && ldy >= N_out);
   AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale_and_zero, 64) && ao_aligned(y, 2));
-  (void)workspace; (void)workspace_bytes;
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0);
   auto s = static_cast<cudaStream_t>(stream);
@@ -71,9 +76,9 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
     int e = AO_B200_ERR_WORKSPACE;
-    if (tunables().gemv_tc && mc <= 5) {
+    if ((tunables().gemv_tc == 1 || (tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20)) && mc <= 5) {
       e = ao::int4_gemv_tc(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out, ldy,
-                           nullptr, 0.f, nullptr, 0, 0, tunables().pdl != 0, s);
+                           nullptr, 0.f, nullptr, 0, 0, workspace, workspace_bytes, tunables().pdl != 0, s);
       if (e == AO_B200_OK) continue;
       if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
     }
@@ -93,7 +98,8 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
 extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
                                        const void* scale_and_zero, int64_t Np, int64_t Kp, int group_size, void* y,
                                        int64_t N_out, int64_t ldy, const void* norm_weight, float norm_eps,
-                                       const void* residual, int64_t ld_res, int epilogue, void* stream) {
+                                       const void* residual, int64_t ld_res, int epilogue, void* workspace,
+                                       int64_t workspace_bytes, void* stream) {
   AO_CHECK_ARG(x && packed && scale_and_zero && y);
   AO_CHECK_ARG(M > 0 && M <= 16 && Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
   AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx);
@@ -105,10 +111,11 @@ extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int
   AO_CHECK_ARG(!norm_weight || ao_aligned(norm_weight, 16));
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0);
-  if (tunables().gemv_tc) {
+  if (tunables().gemv_tc == 1 || (tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20)) {
     // tensor-memory kernel (M <= 5, Np % 128 == 0, activations + >= 3 ring stages must fit); else the mma.sync kernel
     const int e = ao::int4_gemv_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
-                                   norm_eps, residual, ld_res, epilogue, tunables().pdl != 0, static_cast<cudaStream_t>(stream));
+                                   norm_eps, residual, ld_res, epilogue, workspace, workspace_bytes, tunables().pdl != 0,
+                                   static_cast<cudaStream_t>(stream));
     if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
   }
   return ao::int4_gemv_fused(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,

@@ -501,11 +501,15 @@ def _int4_gemv_fused_cuda(x, packed_w, group_size, scales_and_zeros, out_feature
         _check_cuda_bf16(norm_weight, "norm_weight")
         torch._check(norm_weight.numel() == x.size(1), lambda: "norm_weight must have K elements")
         norm_weight = norm_weight.contiguous()
+    L = _lib.lib()
+    ws_bytes = L.ao_b200_int4_mm_workspace_bytes(m, np_, kp)
+    ws = _workspace(x.device, ws_bytes)
     with torch.cuda.device(x.device):
-        _lib.check(_lib.lib().ao_b200_int4_gemv_fused(
+        _lib.check(L.ao_b200_int4_gemv_fused(
             x.data_ptr(), m, x.size(1), ldx, packed_w.data_ptr(), scales_and_zeros.data_ptr(), np_, kp, group_size,
             y.data_ptr(), out_features, n, None if norm_weight is None else norm_weight.data_ptr(), norm_eps,
-            None if residual is None else residual.data_ptr(), ld_res, epilogue, _stream(x)), "int4_gemv_fused")
+            None if residual is None else residual.data_ptr(), ld_res, epilogue,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream(x)), "int4_gemv_fused")
     return y
 
 
