@@ -275,109 +275,7 @@ __global__ void __launch_bounds__(kFThreads, (MT == 1 ? 2 : 1)) int4_gemv_fused_
   // ---- stage the activations: x (* norm_w) -> per-row power-of-two scaling -> fp16, the entries that meet a
   //      "1024 + 16 q" weight pre-divided by 16; then the per-segment correction sums ----
   const int chunks_per_row = KT * 8;  // 16-byte chunks of 8 elements over Kp
-  const int cpt = (chunks_per_row + kCT - 1) / kCT;  // chunks per thread and row
   constexpr int CPS = SEG / 8;  // chunks per segment: 4, 8 or 16
-  if (p.M * cpt <= 4) {
-    // ---- fast path (decode: M * K <= 16 K elements): every (row, chunk) a thread owns stays in registers between the
-    //      two passes; one barrier for the row statistics (every thread then folds the 16 partials itself, in a fixed
-    //      order), one at the end.  ~1.4 k clocks less than the general path on every launch of a decode step. ----
-    uint4 keep[4];
-    float ss_r[4], am_r[4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      keep[r] = make_uint4(0, 0, 0, 0);
-      ss_r[r] = 0.f;
-      am_r[r] = 0.f;
-      if (r < p.M * cpt) {
-        const int m = r / cpt, ci = (r - m * cpt) * kCT + tid;
-        const int64_t k0 = (int64_t)ci * 8;
-        if (ci < chunks_per_row && k0 < p.Kx) {
-          uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0);
-          float f[8];
-          unpack8(v, f);
-          if (p.norm_w != nullptr) {
-            float wn[8];
-            unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              ss_r[r] = fmaf(f[e], f[e], ss_r[r]);
-              f[e] = bf16r(f[e] * wn[e]);
-            }
-            uint32_t o[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
-            v = make_uint4(o[0], o[1], o[2], o[3]);
-          }
-#pragma unroll
-          for (int e = 0; e < 8; ++e) am_r[r] = fmaxf(am_r[r], fabsf(f[e]));
-          keep[r] = v;
-        }
-      }
-    }
-    for (int m = 0; m < p.M; ++m) {
-      float ss = 0.f, amax = 0.f;
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-        if (r / cpt == m) {
-          ss += ss_r[r];
-          amax = fmaxf(amax, am_r[r]);
-        }
-      ss = warp_sum_f(ss);
-      amax = warp_max_f(amax);
-      if (lane == 0) {
-        part[(m * kFConsumers + warp) * 2] = ss;
-        part[(m * kFConsumers + warp) * 2 + 1] = amax;
-      }
-    }
-    named_bar_sync(1, kCT);
-    AO_TRACE(5, 3);
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      if (r < p.M * cpt) {  // uniform
-        const int m = r / cpt, ci = (r - m * cpt) * kCT + tid;
-        float t = 0.f, amax = 0.f;
-#pragma unroll
-        for (int w = 0; w < kFConsumers; ++w) {
-          const float2 pw = *reinterpret_cast<const float2*>(&part[(m * kFConsumers + w) * 2]);
-          t += pw.x;
-          amax = fmaxf(amax, pw.y);
-        }
-        int e = 0;
-        if (amax > 0.f) e = (int)((__float_as_uint(amax) >> 23) & 0xFF) - 127 - 13;
-        e = max(-100, min(100, e));
-        const float up = __uint_as_float((uint32_t)(e + 127) << 23), dn = __uint_as_float((uint32_t)(127 - e) << 23);
-        if (tid == 0 && r == m * cpt) row_scale[m] = (p.norm_w != nullptr) ? up * rsqrtf(t / (float)p.Kx + p.eps) : up;
-        const float dn16 = dn * 0.0625f;
-        float xs = 0.f, xt = 0.f;
-        if (ci < chunks_per_row) {
-          float f[8];
-          unpack8(keep[r], f);
-          const __half2 h0 = __floats2half2_rn(f[0] * dn, f[1] * dn), h1 = __floats2half2_rn(f[2] * dn16, f[3] * dn16);
-          const __half2 h2 = __floats2half2_rn(f[4] * dn, f[5] * dn), h3 = __floats2half2_rn(f[6] * dn16, f[7] * dn16);
-          *reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16) =
-              make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
-                         *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
-          const float2 a0 = __half22float2(h0), a1 = __half22float2(h1), a2 = __half22float2(h2), a3 = __half22float2(h3);
-          const float plain = (a0.x + a0.y) + (a2.x + a2.y), div16 = (a1.x + a1.y) + (a3.x + a3.y);
-          xs = plain + div16;
-          xt = fmaf(16.f, div16, plain);
-        }
-#pragma unroll
-        for (int o = CPS / 2; o; o >>= 1) {
-          xs += __shfl_xor_sync(0xffffffffu, xs, o);
-          xt += __shfl_xor_sync(0xffffffffu, xt, o);
-        }
-        if (ci < chunks_per_row && (ci % CPS) == 0) {
-          const int sg = ci / CPS;
-          X_s[(sg * 2 + 0) * 8 * MT + m] = xt;
-          X_s[(sg * 2 + 1) * 8 * MT + m] = -fmaf(1024.f, xs, 8.f * xt);
-        }
-      }
-    }
-    named_bar_sync(1, kCT);
-    AO_TRACE(5, 5);
-    AO_TRACE(5, 6);
-  } else
   {
     for (int m = 0; m < p.M; ++m) {
       float ss = 0.f, amax = 0.f;
