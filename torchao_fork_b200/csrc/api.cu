@@ -11,6 +11,9 @@ int int4_gemv_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* 
                  int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
                  int64_t ld_res, int epilogue, void* workspace, int64_t workspace_bytes, bool pdl, cudaStream_t s);
 int64_t int4_gemv_tc_workspace_bytes(int64_t Np);
+int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np, int64_t Kp,
+                 int G, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s);
+int64_t int4_gemm_tc_workspace_bytes(int64_t M, int64_t Np, int64_t Kp);
 int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
               void* y, int64_t ldy, cudaStream_t s);
 }  // namespace ao
@@ -31,8 +34,11 @@ extern "C" int ao_b200_abi_version(void) { return 2; }
 #include <cstdlib>
 namespace {
 struct Tunables {
-  int gemv_version, stages, pdl, gemv_tc;
+  int gemv_version, stages, pdl, gemv_tc, gemm_tc;
   Tunables() {
+    // tcgen05 prefill GEMM for M > 16 (0: loop the decode GEMV over 16-row chunks instead — kept for A/B testing)
+    const char* gm = std::getenv("AO_B200_GEMM_TC");
+    gemm_tc = gm ? std::atoi(gm) : 1;
     const char* v = std::getenv("AO_B200_GEMV");
     gemv_version = v ? std::atoi(v) : 3;
     const char* st = std::getenv("AO_B200_STAGES");
@@ -55,10 +61,11 @@ const Tunables& tunables() {
 }  // namespace
 
 extern "C" int64_t ao_b200_int4_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
-  (void)M; (void)Kp;
-  // tickets + partial sums of the tensor-memory GEMV's split-K (row blocks shared by neighbouring CTAs); the mma.sync
-  // kernels reduce inside the CTA and need none
-  return ao::int4_gemv_tc_workspace_bytes(Np);
+  // [0, gemv): tickets + partial sums of the tensor-memory GEMV's split-K (row blocks shared by neighbouring CTAs; the
+  // tickets must stay zero between launches, so nothing else may ever be written there); [gemv, ...): the prefill
+  // GEMM's permuted copy of the activations (M > 16).  The mma.sync kernels reduce inside the CTA and need none.
+  const int64_t gemv = ao::int4_gemv_tc_workspace_bytes(Np);
+  return gemv + (M > 16 ? ao::int4_gemm_tc_workspace_bytes(M, Np, Kp) : 0);
 }
 
 extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
@@ -73,6 +80,13 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   auto s = static_cast<cudaStream_t>(stream);
   auto xb = static_cast<const __nv_bfloat16*>(x);
   auto yb = static_cast<__nv_bfloat16*>(y);
+  if (M > 16 && tunables().gemm_tc) {
+    // prefill: tensor-memory dequant-GEMM; its staging buffer sits after the GEMV region of the workspace
+    const int64_t off = ao::int4_gemv_tc_workspace_bytes(Np);
+    const int e = ao::int4_gemm_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy,
+                                   workspace ? static_cast<char*>(workspace) + off : nullptr, workspace_bytes - off, s);
+    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+  }
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
     int e = AO_B200_ERR_WORKSPACE;

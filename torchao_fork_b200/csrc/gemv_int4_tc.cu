@@ -573,10 +573,13 @@ static int tc_sm_count() {
 
 // workspace: [grid][2][5][128] fp32 partial sums (fixed size, FIRST: launches of different shapes share one
 // workspace, and only the tickets must stay zero between launches) + [n_blocks][4] tickets
-static size_t tc_ticket_bytes(int64_t Np) { return ((size_t)(Np / 128) * 16 + 255) / 256 * 256; }
+// (the ticket area has a FIXED size, so that whatever follows it in a shared workspace — the prefill GEMM's staging
+// buffer — never overlaps the tickets of a launch with more row blocks)
+constexpr size_t kTcTicketBytes = 1u << 20;  // 65536 row blocks = 8.4 M output rows
+static size_t tc_ticket_bytes(int64_t Np) { (void)Np; return kTcTicketBytes; }
 static size_t tc_partial_bytes() { return (size_t)tc_sm_count() * 2 * 5 * 128 * 4; }
 int64_t int4_gemv_tc_workspace_bytes(int64_t Np) {
-  if (Np % 128 != 0) return 0;
+  if (Np % 128 != 0 || (size_t)(Np / 128) * 16 > kTcTicketBytes) return 0;
   return (int64_t)(tc_ticket_bytes(Np) + tc_partial_bytes());
 }
 
@@ -629,6 +632,7 @@ int int4_gemv_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* 
                  int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
                  int64_t ld_res, int epilogue, void* workspace, int64_t workspace_bytes, bool pdl, cudaStream_t s) {
   if (M > 5 || Np % 128 != 0) return AO_B200_ERR_UNSUPPORTED;
+  if (int4_gemv_tc_workspace_bytes(Np) == 0) return AO_B200_ERR_UNSUPPORTED;
   if (workspace == nullptr || workspace_bytes < int4_gemv_tc_workspace_bytes(Np)) return AO_B200_ERR_WORKSPACE;
   GemvTcParams p;
   p.packed = static_cast<const uint8_t*>(packed);
