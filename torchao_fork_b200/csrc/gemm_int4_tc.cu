@@ -39,22 +39,39 @@ namespace ao {
 constexpr int kGmEpiWarps = 4, kGmDqWarps = 16;  // dequant warps: two sets of 8 (one strip each), alternating stages
 constexpr int kGmProducerWarp = kGmEpiWarps + kGmDqWarps, kGmMmaWarp = kGmProducerWarp + 1;
 constexpr int kGmThreads = (kGmMmaWarp + 1) * 32;  // 704
-constexpr int kGmWeightStage = 8 * 512;            // 8 strips x one 64-k tile
+constexpr int kGmWSlots = 3, kGmWSlotBytes = 8 * 4 * 512;  // weight ring: 256-k slices of the 128-row block (16 KB)
+constexpr int kGmMaxStages = 8;                            // activation ring slots (64 k each)
+constexpr int kGmHeader = 1024;                            // mbarriers + TMEM base address
+
+#ifdef AO_GM_TRACE
+constexpr int kGmTraceIts = 256;
+__device__ long long ao_gm_trace[4][kGmMmaWarp + 1][kGmTraceIts];
+#define GM_TRACE(kind, it)                                                                               \
+  do {                                                                                                   \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && (threadIdx.x & 31) == 0 && (it) < kGmTraceIts)             \
+      ao_gm_trace[kind][threadIdx.x >> 5][it] = clock64();                                               \
+  } while (0)
+#else
+#define GM_TRACE(kind, it) do { } while (0)
+#endif
 
 struct GemmTcParams {
   const uint8_t* packed;     // strip-major [Np/16][Kp/64][512 B]
   const uint32_t* sz;        // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
-  const __nv_bfloat16* xt;   // permuted activations [Kp/8 chunks][Mpad][8]
+  const __nv_bfloat16* xt;   // permuted activations [Mpad/NT][Kp/64][8 chunks][NT][8]
   __nv_bfloat16* y;          // [M][ldy]
-  int M, KT, stages, tmem_cols, cluster;
+  int M, KT, stages, tmem_cols, cluster, vec_store;
   int64_t Mpad, N_out, ldy;
 };
 
 // ---- activations -> chunk-major, k-permuted copy ------------------------------------------------------------------
-// xt[(kt * 8 + q) * Mpad + m][c * 2 + e] = x[m][64 kt + 32 half + 8 c + 2 i + e],  q = 4 half + i, rows >= M and
-// columns >= Kx are zero.  One thread = one (row, 64-k tile): 128 bytes in, 8 x 16 bytes out (coalesced over rows).
+// xt[m / NT][kt][q][m % NT][c * 2 + e] = x[m][64 kt + 32 half + 8 c + 2 i + e],  q = 4 half + i; rows >= M and columns
+// >= Kx are zero.  The (NT rows x 64 k) tile of one pipeline stage is one contiguous NT * 128 bytes, already in the
+// core-matrix order of the MMA's shared-memory operand.  One thread = one (row, 64-k tile): 128 bytes in, 8 x 16
+// bytes out (coalesced over rows).
 __global__ void __launch_bounds__(256) x_permute_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int64_t Kx,
-                                                        int64_t ldx, int64_t Mpad, int KT, __nv_bfloat16* __restrict__ xt) {
+                                                        int64_t ldx, int64_t Mpad, int KT, int NT,
+                                                        __nv_bfloat16* __restrict__ xt) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= Mpad * KT) return;
   const int64_t kt = idx / Mpad, m = idx - kt * Mpad;
@@ -70,7 +87,7 @@ __global__ void __launch_bounds__(256) x_permute_kernel(const __nv_bfloat16* __r
   for (int q = 0; q < 8; ++q) {
     const int half = q >> 2, i = q & 3;
     const uint4 o = make_uint4(in[16 * half + i], in[16 * half + 4 + i], in[16 * half + 8 + i], in[16 * half + 12 + i]);
-    *reinterpret_cast<uint4*>(xt + ((kt * 8 + q) * Mpad + m) * 8) = o;
+    *reinterpret_cast<uint4*>(xt + ((((m / NT) * KT + kt) * 8 + q) * NT + m % NT) * 8) = o;
   }
 }
 
@@ -134,27 +151,40 @@ __device__ __forceinline__ bool gm_elect_one() {
 }
 
 // ---- the GEMM -----------------------------------------------------------------------------------------------------
-// grid (Np / 128, Mpad / NT).  Shared memory: `stages` x [8 x 512 B packed weights | 8 chunks x NT x 16 B activations],
-// then the mbarriers.  Tensor memory: columns [0, NT) accumulator, NT + 32 slot .. + 32: the A tile of ring slot `slot`.
+// grid (Np / 128, Mpad / NT), clusters of CL CTAs along x.  Shared memory: 1 KB of mbarriers, the WEIGHT ring
+// (kGmWSlots x [8 strips x 4 tiles x 512 B]: a strip's consecutive k-tiles are contiguous in the packed layout, so a
+// 256-k slice of the row block is 8 copies of 2 KB), the ACTIVATION ring (`stages` x [8 chunks x NT x 16 B], one 64-k
+// tile per slot, each CTA of the cluster multicasting its 1 / CL share as ONE copy).  A bulk copy costs its issuing
+// warp ~100 clocks, so copies per 64 k are what bounds the producer: 3 here (first version: 10, producer-bound at
+// 1200 clocks per tile against 512 of MMA).  Tensor memory: columns [0, NT) accumulator, NT + 32 slot ..: A tiles.
 template <int G, int NT>
 __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmTcParams p) {
   extern __shared__ __align__(1024) uint8_t gm_smem[];
-  constexpr uint32_t kStageBytes = kGmWeightStage + NT * 128;
+  constexpr uint32_t kXStage = NT * 128;
   constexpr uint32_t kChunk = NT * 16;  // bytes between consecutive 8-k chunks of the B tile (descriptor LBO)
   const int stages = p.stages, KT = p.KT;
-  uint64_t* full = reinterpret_cast<uint64_t*>(gm_smem + (size_t)stages * kStageBytes);
-  uint64_t* empty = full + stages;
-  uint64_t* a_full = empty + stages;
-  uint64_t* d_full = a_full + stages;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(gm_smem);
+  uint64_t* wempty = wfull + kGmWSlots;
+  uint64_t* xfull = wempty + kGmWSlots;
+  uint64_t* empty = xfull + kGmMaxStages;
+  uint64_t* a_full = empty + kGmMaxStages;
+  uint64_t* d_full = a_full + kGmMaxStages;
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(d_full + 1);
+  uint8_t* wring = gm_smem + kGmHeader;
+  uint8_t* xring = wring + kGmWSlots * kGmWSlotBytes;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nb = blockIdx.x, mt = blockIdx.y;
+  const int CL = p.cluster;
 
   if (warp == kGmMmaWarp) {
     if (lane == 0) {
+      for (int s = 0; s < kGmWSlots; ++s) {
+        mbar_init(&wfull[s], 1);
+        mbar_init(&wempty[s], 32);  // 8 strips x 4 tiles, one arrival per (dequant warp, tile)
+      }
       for (int s = 0; s < stages; ++s) {
-        mbar_init(&full[s], 1);
-        mbar_init(&empty[s], p.cluster);
+        mbar_init(&xfull[s], 1);
+        mbar_init(&empty[s], CL);
         mbar_init(&a_full[s], 8);
       }
       mbar_init(d_full, 1);
@@ -168,27 +198,25 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
   __syncthreads();
   gm_cluster_sync();  // every CTA's barriers exist before a peer multicasts into them
   gm_fence_after();
-  const int CL = p.cluster;
   const uint32_t crank = CL > 1 ? gm_cluster_rank() : 0u;
   const uint16_t cmask = (uint16_t)((1u << CL) - 1);
   const uint32_t tb = *reinterpret_cast<volatile uint32_t*>(tmem_base_s);
-  const uint32_t smem0 = smem_u32(gm_smem);
+  const uint32_t wring_u = smem_u32(wring), xring_u = smem_u32(xring);
 
   if (warp == kGmProducerWarp) {
-    // ---- TMA producer: lanes 0..7 one weight strip each; lanes 8.. one activation chunk each, this CTA's share
-    // (chunks q = rank, rank + CL, ...) multicast to the whole cluster ----------------------------------------------
-    const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), 0, KT) * 512;
-    const int xq = (int)crank + (lane - 8) * CL;  // chunk this lane fetches (lanes 8 .. 8 + 8 / CL - 1)
-    const __nv_bfloat16* xsrc = p.xt + ((int64_t)(xq & 7) * p.Mpad + (int64_t)mt * NT) * 8;
+    // ---- TMA producer, activations: one multicast copy (this CTA's share of the stage) per 64-k tile ----------------
+    const uint32_t share = kXStage / CL;
+    const uint8_t* xsrc = reinterpret_cast<const uint8_t*>(p.xt) + (int64_t)mt * KT * kXStage + crank * share;
     for (int it = 0; it < KT; ++it) {
+      GM_TRACE(0, it);
       const int slot = it % stages;
       if (it >= stages) mbar_wait(&empty[slot], ((it / stages) - 1) & 1);
-      uint8_t* st = gm_smem + (size_t)slot * kStageBytes;
-      if (lane == 0) mbar_arrive_expect_tx(&full[slot], kStageBytes);
+      GM_TRACE(1, it);
+      if (gm_elect_one()) {
+        mbar_arrive_expect_tx(&xfull[slot], kXStage);
+        gm_bulk_g2s_multicast(xring + slot * kXStage + crank * share, xsrc + (int64_t)it * kXStage, share, &xfull[slot], cmask);
+      }
       __syncwarp();
-      if (lane < 8) bulk_g2s(st + lane * 512, wsrc + (int64_t)it * 512, 512, &full[slot]);
-      else if (xq < 8)
-        gm_bulk_g2s_multicast(st + kGmWeightStage + xq * kChunk, xsrc + (int64_t)it * 8 * p.Mpad * 8, kChunk, &full[slot], cmask);
     }
   } else if (warp == kGmMmaWarp) {
     // ---- MMA issue: 4 x (M128, N = NT, K16) per 64-k tile, whole warp in uniform control flow ---------------------
@@ -197,11 +225,14 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     for (int it = 0; it < KT; ++it) {
       const int slot = it % stages;
       const uint32_t par = (it / stages) & 1;
+      GM_TRACE(0, it);
       mbar_wait(&a_full[slot], par);
-      mbar_wait(&full[slot], par);
+      GM_TRACE(1, it);
+      mbar_wait(&xfull[slot], par);
       gm_fence_after();
+      GM_TRACE(2, it);
       if (gm_elect_one()) {
-        const uint32_t bx = smem0 + slot * kStageBytes + kGmWeightStage;
+        const uint32_t bx = xring_u + slot * kXStage;
         const uint32_t a0 = tb + NT + slot * 32;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
@@ -212,6 +243,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
         if (it == KT - 1) gm_commit(d_full);
       }
       __syncwarp();
+      GM_TRACE(3, it);
     }
   } else if (warp >= kGmEpiWarps) {
     // ---- dequant warps: packed words -> bf16 W' (reference arithmetic, one rounding) -> tensor memory -------------
@@ -248,8 +280,11 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
           szn[h][1] = __ldg(szp + (grp + h) * 16 + 8);
         }
       }
-      mbar_wait(&full[slot], (it / stages) & 1);
-      const uint4 w4 = lds128(smem0 + slot * kStageBytes + strip * 512 + lane * 16);
+      const int wc = it >> 2, ws = wc % kGmWSlots;
+      GM_TRACE(0, it);
+      mbar_wait(&wfull[ws], (wc / kGmWSlots) & 1);
+      GM_TRACE(1, it);
+      const uint4 w4 = lds128(wring_u + ws * kGmWSlotBytes + strip * 2048 + (it & 3) * 512 + lane * 16);
       const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
       uint32_t r[16];
 #pragma unroll
@@ -261,30 +296,75 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
 #pragma unroll
         for (int i = 0; i < 4; ++i) r[2 * (4 * half + i) + hrow] = o[i];
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&wempty[ws]);  // the words are in registers
+      if (it >= stages) mbar_wait(&empty[slot], ((it / stages) - 1) & 1);  // the MMAs that read this A slot retired
+      gm_fence_after();
+      GM_TRACE(2, it);
       gm_st_16x128b_x8(taddr0 + slot * 32, r);
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      GM_TRACE(3, it);
       gm_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_full[slot]);
     }
   } else {
-    // ---- epilogue: thread = weight row (TMEM lane), 32 prompt rows per tcgen05.ld ---------------------------------
+    if (warp == 0) {
+      // ---- TMA producer, weights (this warp has nothing else to do until the accumulator is final): slice wc = k-tiles
+      // 4 wc .. 4 wc + 3 of the row block, 8 copies of 2 KB, into ring slot wc % kGmWSlots as soon as the dequant
+      // warps have released it.  Kept off the activation producer: a bulk copy costs its issuing warp ~130 clocks.
+      const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), 0, KT) * 512;
+      for (int wc = 0; wc * 4 < KT; ++wc) {
+        const int ws = wc % kGmWSlots, t0 = wc * 4;
+        if (wc >= kGmWSlots) mbar_wait(&wempty[ws], ((wc / kGmWSlots) - 1) & 1);
+        const uint32_t tiles = (uint32_t)(KT - t0 < 4 ? KT - t0 : 4);
+        if (lane == 0) mbar_arrive_expect_tx(&wfull[ws], 8 * 512 * tiles);
+        __syncwarp();
+        if (lane < 8) bulk_g2s(wring + ws * kGmWSlotBytes + lane * 2048, wsrc + (int64_t)t0 * 512, 512 * tiles, &wfull[ws]);
+        __syncwarp();
+      }
+    }
+    // ---- epilogue: thread = weight row (TMEM lane); fp32 -> bf16, transposed through the (now idle) rings so that
+    // the global stores are 16-byte pieces of 256-byte output rows -----------------------------------------------
+    GM_TRACE(0, 0);
     mbar_wait(d_full, 0);
     gm_fence_after();
-    const int64_t n = (int64_t)nb * 128 + 32 * warp + lane;
+    GM_TRACE(1, 0);
+    constexpr uint32_t kPitch = 128 * 2 + 16;
+    const uint32_t tile_u = wring_u;
+    const int nl = 32 * warp + lane;
 #pragma unroll 1
     for (int cc = 0; cc < NT / 32; ++cc) {
       uint32_t d[32];
       gm_ld_32x32b_x32(tb + ((uint32_t)(32 * warp) << 16) + 32 * cc, d);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      const int64_t m0 = (int64_t)mt * NT + 32 * cc;
-      if (n < p.N_out) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (m0 + j < p.M) p.y[(m0 + j) * p.ldy + n] = __float2bfloat16_rn(__uint_as_float(d[j]));
+      for (int j = 0; j < 32; ++j) {
+        const unsigned short b = __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(d[j])));
+        asm volatile("st.shared.u16 [%0], %1;" ::"r"(tile_u + (uint32_t)(32 * cc + j) * kPitch + nl * 2), "h"(b) : "memory");
       }
     }
     gm_fence_before();
+    named_bar_sync(1, kGmEpiWarps * 32);
+    const int t = threadIdx.x, col = t & 15;
+    const int64_t n0 = (int64_t)nb * 128 + col * 8;
+#pragma unroll 4
+    for (int r0 = 0; r0 < NT; r0 += 8) {
+      const int row = r0 + (t >> 4);
+      const int64_t m = (int64_t)mt * NT + row;
+      if (m >= p.M || n0 >= p.N_out) continue;
+      const uint4 v = lds128(tile_u + (uint32_t)row * kPitch + col * 16);
+      __nv_bfloat16* dst = p.y + m * p.ldy + n0;
+      if (p.vec_store && n0 + 8 <= p.N_out) {
+        *reinterpret_cast<uint4*>(dst) = v;
+      } else {
+        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (n0 + e < p.N_out) dst[e] = __ushort_as_bfloat16((unsigned short)(vv[e >> 1] >> (16 * (e & 1))));
+      }
+    }
+    GM_TRACE(2, 0);
   }
   __syncthreads();
   gm_cluster_sync();  // peers may still be arriving on this CTA's barriers
@@ -307,24 +387,27 @@ int64_t int4_gemm_tc_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
 
 template <int G, int NT>
 static int launch_gemm_tc(GemmTcParams& p, int64_t Np, cudaStream_t s) {
-  constexpr size_t kStageBytes = kGmWeightStage + NT * 128;
+  constexpr size_t kStageBytes = NT * 128;
+  constexpr size_t kFixed = kGmHeader + kGmWSlots * kGmWSlotBytes;
   static int max_smem = -1;
   if (max_smem < 0) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   }
-  int stages = (int)(((size_t)max_smem - 1024) / kStageBytes);
+  int stages = (int)(((size_t)max_smem - kFixed) / kStageBytes);
   const int max_by_tmem = (512 - NT) / 32;
   if (stages > max_by_tmem) stages = max_by_tmem;
-  if (stages > 8) stages = 8;
+  if (stages > kGmMaxStages) stages = kGmMaxStages;
   if (stages > p.KT) stages = p.KT;
   if (stages < 1) return AO_B200_ERR_UNSUPPORTED;
   p.stages = stages;
   int cols = 32;
   while (cols < NT + 32 * stages) cols <<= 1;
   p.tmem_cols = cols;
-  const size_t smem = stages * kStageBytes + (3 * stages + 1) * 8 + 16;
+  size_t smem = kFixed + stages * kStageBytes;
+  const size_t epi = kGmHeader + (size_t)NT * (128 * 2 + 16);  // the epilogue's transposed output tile overlays the rings
+  if (smem < epi) smem = epi;
   auto kern = int4_gemm_tc_kernel<G, NT>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -369,9 +452,10 @@ int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* 
   p.Mpad = (M + NT - 1) / NT * NT;
   p.N_out = N_out;
   p.ldy = ldy;
+  p.vec_store = (ldy % 8 == 0 && ao_aligned(y, 16)) ? 1 : 0;
   if (p.Mpad / NT > 65535) return AO_B200_ERR_UNSUPPORTED;
   const int64_t items = p.Mpad * p.KT;
-  x_permute_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), M, Kx, ldx, p.Mpad, p.KT,
+  x_permute_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), M, Kx, ldx, p.Mpad, p.KT, NT,
                                                                    static_cast<__nv_bfloat16*>(workspace));
   if (cudaGetLastError() != cudaSuccess) return AO_B200_ERR_CUDA;
 #define AO_GM(GG)                                                        \
