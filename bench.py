@@ -203,7 +203,8 @@ def build_model(spec, device, tp=None):
     old = torch.get_default_dtype()
     torch.set_default_dtype(torch.bfloat16)
     try:
-        if tp is not None and tp.world_size > 1:
+        if (tp is not None and tp.world_size > 1) or cfg.n_layer * cfg.dim * cfg.intermediate_size > 4e10:
+            # sharded and / or too large to hold in bf16 next to its quantized copy: layer-streamed builder
             from torchao_fork_b200._models.llama.tp import build_tp_transformer
             model = build_tp_transformer(cfg, tp, device, spec)
         else:
@@ -373,8 +374,14 @@ def run_b200(args):
                                         "sample": f"unavailable: {type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
+        # tear-down: the graph holds NCCL kernels, release it before the communicator; exit without
+        # destroy_process_group (it can block on a communicator that captured graphs have used)
+        eng.graph = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():

@@ -290,7 +290,9 @@ class DecodeEngine:
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # with NCCL in the step, other threads (the process group's watchdog) may touch CUDA during the capture
+        mode = {} if self.tp is None else {"capture_error_mode": "thread_local"}
+        with torch.cuda.graph(self.graph, **mode):
             self._launch_step()
         self.tok.copy_(tok0)
         self.pos.copy_(pos0)
