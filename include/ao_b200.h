@@ -208,6 +208,24 @@ AO_B200_API int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int6
 AO_B200_API int ao_b200_sample(const void* logits, int64_t ldl, int64_t B, int64_t V, float temperature, int top_k,
                                const void* noise, int64_t ldq, void* next_tok, void* stream);
 
+/* ---- tensor-parallel exchange over NVLink peer memory (new: the reference has no int4 TP path; SURVEY.md section 8e
+ * names the collective it replaces: ncclAllReduce(sum, bf16) of [B][dim] after the row-parallel wo and w2) ------------
+ * One process per GPU.  Every rank allocates ONE exchange buffer with ao_b200_tp_alloc (cudaMalloc, zeroed; returns the
+ * 64-byte CUDA IPC handle), hands the handle to its peers (any host channel), and opens theirs with ao_b200_tp_open.
+ * bufs[r] = rank r's buffer as seen from this process (own pointer at bufs[rank]).
+ *   ao_b200_tp_allreduce_add: h[i] = bf16( h[i] + sum_r partial_r[i] ), i < n, summed in rank order in fp32 — bit-identical
+ *   on every rank.  One launch: pushes `partial` to all peers, flags, waits for theirs (bounded spin; on time-out the
+ *   status word is set and the call returns garbage instead of hanging), sums, adds.  All ranks must issue the same
+ *   sequence of calls (n may vary, max_elems and world may not).  n % 8 == 0, n <= max_elems <= 131072. */
+AO_B200_API int64_t ao_b200_tp_buffer_bytes(int world, int64_t max_elems);
+AO_B200_API int ao_b200_tp_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_out /* 64 bytes */);
+AO_B200_API int ao_b200_tp_open(const void* ipc_handle /* 64 bytes */, void** peer_ptr);
+AO_B200_API int ao_b200_tp_close(void* peer_ptr);
+AO_B200_API int ao_b200_tp_free(void* dev_ptr);
+AO_B200_API int ao_b200_tp_status(const void* own_buf, int* status_out /* 0 ok, 1 a peer timed out */);
+AO_B200_API int ao_b200_tp_allreduce_add(const void* partial, void* h, int64_t n, void* const* bufs, int rank, int world,
+                                         int64_t max_elems, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

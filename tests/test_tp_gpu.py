@@ -38,21 +38,34 @@ def _worker(rank, world, port, q):
         B, S = 2, 64
         prompt = torch.randint(0, cfg.vocab_size, (B, 8), generator=torch.Generator().manual_seed(1)).to(dev)
         outs = {}
+        forced = torch.randint(0, cfg.vocab_size, (6, B), generator=torch.Generator().manual_seed(2)).to(dev)
         for name, c in (("tp1", None), ("tp2", ctx)):
             model = build_tp_transformer(cfg, c, dev, spec, seed=11)
-            gen = Generator(model, B, S, temperature=0.0, top_k=None, use_graph=True, tp=c if c is not None and c.world_size > 1 else None)
+            gen = Generator(model, B, S, temperature=0.0, top_k=None, use_graph=True, tp=c)
+            # teacher-forced: eager prefill fills the cache, then 6 graph steps on FIXED tokens (a random-init model has
+            # near-tied logits, so free-running greedy decoding may legitimately fork on a rounding difference)
+            prefill_logits = model(prompt, torch.arange(8, device=dev, dtype=torch.int32))[:, -1].float().clone()
+            step_logits = []
+            for i in range(forced.shape[0]):
+                gen.engine.set_state(forced[i], 8 + i)
+                gen.engine.step()
+                lg = gen.engine.logits if c is None else ctx.gather_logits(gen.engine.logits)
+                step_logits.append(lg.float().clone())
             seq = gen.generate(prompt, 12)
-            full_logits = gen.engine.logits if c is None else ctx.gather_logits(gen.engine.logits)
-            outs[name] = (seq.clone(), full_logits.float().clone())
+            outs[name] = (seq.clone(), prefill_logits, torch.stack(step_logits))
+            gen.engine.graph = None
         torch.cuda.synchronize()
-        s1, l1 = outs["tp1"]
-        s2, l2 = outs["tp2"]
+        s1, p1, l1 = outs["tp1"]
+        s2, p2, l2 = outs["tp2"]
         assert s1.shape == s2.shape == (B, 20)
-        assert l1.shape == l2.shape == (B, cfg.vocab_size)
-        assert torch.equal(s1[:, :9], s2[:, :9])                       # prompt + the prefill's token
-        sq = compute_error(l1, l2).item()
+        assert l1.shape == l2.shape == (6, B, cfg.vocab_size)
+        assert compute_error(p1, p2).item() >= 35.0, compute_error(p1, p2).item()
+        per_step = [compute_error(l1[i], l2[i]).item() for i in range(l1.shape[0])]
+        sq = min(per_step)
         same = (s1 == s2).float().mean().item()
-        assert same >= 0.9 or sq >= 35.0, (same, sq)
+        assert sq >= 35.0, per_step
+        if ctx.peer is not None:
+            assert ctx.peer.status() == 0
         # every rank decoded the same tokens
         t = s2.clone()
         dist.broadcast(t, 0)
@@ -65,6 +78,111 @@ def _worker(rank, world, port, q):
     except Exception as e:
         import traceback
         q.put((rank, "".join(traceback.format_exception(type(e), e, e.__traceback__)), 0.0, 0.0))
+
+
+def _peer_worker(rank, world, port, q):
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                          LOCAL_RANK=str(rank))
+        import torch.distributed as dist
+        from torchao_fork_b200._models.llama.tp import TPContext
+
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        ctx = TPContext.from_env(backend="nccl", device=dev)
+        peer = ctx.enable_peer_exchange(16 * 1024)
+        assert peer is not None
+        g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+        def expected(partial, h):
+            parts = [torch.empty_like(partial) for _ in range(world)]
+            dist.all_gather(parts, partial)
+            acc = torch.zeros_like(partial, dtype=torch.float32)
+            for p in parts:                      # rank order, fp32: what the kernel does
+                acc += p.float()
+            return (h.float() + acc).to(torch.bfloat16)
+
+        # eager calls, sizes from one 16-byte chunk to the full buffer (1 .. 2 CTAs), back to back
+        for n in [8, 1024, 4096, 8192, 8200, 16 * 1024] * 3:
+            partial = torch.randn(n, device=dev, generator=g).to(torch.bfloat16)
+            h = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(n)).to(torch.bfloat16)
+            want = expected(partial, h)
+            ctx.all_reduce_add(partial, h)
+            assert torch.equal(h, want), (n, (h.float() - want.float()).abs().max().item())
+        # replicated state stays bit-identical across ranks
+        chk = h.clone()
+        dist.broadcast(chk, 0)
+        assert torch.equal(chk, h)
+        # inside a CUDA graph, replayed (the epoch lives on the device)
+        partial = torch.randn(2, 4096, device=dev, generator=g).to(torch.bfloat16)
+        h = torch.zeros(2, 4096, device=dev, dtype=torch.bfloat16)
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            ctx.all_reduce_add(partial, h)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+            for _ in range(3):
+                ctx.all_reduce_add(partial, h)
+        h.zero_()
+        want = torch.zeros_like(h)
+        for _ in range(5):
+            graph.replay()
+            for _ in range(3):
+                want = expected(partial, want)
+        torch.cuda.synchronize()
+        assert torch.equal(h, want)
+        assert peer.status() == 0
+        # timing (informational): 30 calls per replay
+        g2 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g2, capture_error_mode="thread_local"):
+            for _ in range(30):
+                ctx.all_reduce_add(partial[:1], h[:1])
+        g2.replay()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            g2.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / 300
+        del graph, g2
+        q.put((rank, "ok", us, 0.0))
+        q.close()
+        q.join_thread()
+        torch.cuda.synchronize()
+        os._exit(0)
+    except Exception as e:
+        import traceback
+        q.put((rank, "".join(traceback.format_exception(type(e), e, e.__traceback__)), 0.0, 0.0))
+
+
+def _run(worker, world=2, timeout=300):
+    port = _free_port()
+    mpctx = mp.get_context("spawn")
+    q = mpctx.Queue()
+    procs = [mpctx.Process(target=worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    try:
+        results = [q.get(timeout=timeout) for _ in range(world)]
+    finally:
+        for p in procs:
+            p.join(timeout=30)
+            if p.is_alive():
+                p.kill()
+    return sorted(results)
+
+
+@pytest.mark.timeout(400)
+def test_peer_memory_allreduce_add_is_exact_and_replayable():
+    for rank, status, us, _ in _run(_peer_worker):
+        assert status == "ok", f"rank {rank}:\n{status}"
+        print(f"rank {rank}: peer all-reduce + add of 8 KB: {us:.2f} us per call (graph, back to back)")
 
 
 @pytest.mark.timeout(600)

@@ -38,10 +38,17 @@ SIGNATURES = {
                                        _vp],
     "ao_b200_silu_mul": [_vp, _vp, _i64, _i64, _vp],
     "ao_b200_sample": [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _i64, _vp, _vp],
+    "ao_b200_tp_buffer_bytes": [_i32, _i64],
+    "ao_b200_tp_alloc": [_i64, ctypes.POINTER(ctypes.c_void_p), _vp],
+    "ao_b200_tp_open": [_vp, ctypes.POINTER(ctypes.c_void_p)],
+    "ao_b200_tp_close": [_vp],
+    "ao_b200_tp_free": [_vp],
+    "ao_b200_tp_status": [_vp, ctypes.POINTER(ctypes.c_int)],
+    "ao_b200_tp_allreduce_add": [_vp, _vp, _i64, ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i64, _vp],
 }
 _RESTYPES = {"ao_b200_error_string": ctypes.c_char_p, "ao_b200_int4_mm_workspace_bytes": _i64,
              "ao_b200_decode_attention_workspace_bytes": _i64,
-             "ao_b200_decode_attention_fused_workspace_bytes": _i64}
+             "ao_b200_decode_attention_fused_workspace_bytes": _i64, "ao_b200_tp_buffer_bytes": _i64}
 
 DIV_IEEE, DIV_RECIP = 0, 1
 

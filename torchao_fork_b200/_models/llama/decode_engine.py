@@ -111,6 +111,8 @@ class DecodeEngine:
         self.temperature, self.top_k = temperature, top_k
         self.tp = tp  # tensor-parallel context (tp.py) or None
         dev = model.tok_embeddings.weight.device
+        if tp is not None and tp.world_size > 1:
+            tp.enable_peer_exchange(16 * cfg.dim)  # h / delta are [B <= 16][dim]
         self.device = dev
         bf = dict(dtype=torch.bfloat16, device=dev)
         B, D = batch_size, cfg.dim

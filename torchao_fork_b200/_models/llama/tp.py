@@ -30,6 +30,64 @@ import torch.nn as nn
 from .model import ModelArgs, Transformer
 
 
+class PeerExchange:
+    """NVLink peer-memory exchange buffers of one rank (include/ao_b200.h, ao_b200_tp_*): allocated by the C library,
+    IPC handles swapped over the process group's host channel, peers' buffers opened once.  `allreduce_add` is one
+    kernel launch: h += sum over ranks of partial (csrc/tp_comm.cu)."""
+
+    def __init__(self, rank: int, world_size: int, max_elems: int, device, group=None):
+        import ctypes
+
+        from ... import _lib
+
+        self._lib, self._ct = _lib, ctypes
+        L = _lib.lib()
+        self.rank, self.world_size, self.max_elems = rank, world_size, int(max_elems)
+        nbytes = int(L.ao_b200_tp_buffer_bytes(world_size, self.max_elems))
+        if nbytes == 0:
+            raise ValueError(f"peer exchange does not cover world={world_size}, max_elems={max_elems}")
+        with torch.cuda.device(device):
+            own, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+            _lib.check(L.ao_b200_tp_alloc(nbytes, ctypes.byref(own), handle), "tp_alloc")
+            handles = [None] * world_size
+            dist.all_gather_object(handles, bytes(handle.raw), group=group)
+            self.own = own.value
+            self.bufs = (ctypes.c_void_p * world_size)()
+            self._opened = []
+            for r, hnd in enumerate(handles):
+                if r == rank:
+                    self.bufs[r] = self.own
+                else:
+                    peer = ctypes.c_void_p()
+                    _lib.check(L.ao_b200_tp_open(ctypes.create_string_buffer(hnd, 64), ctypes.byref(peer)), f"tp_open(rank {r})")
+                    self.bufs[r] = peer.value
+                    self._opened.append(peer.value)
+        dist.barrier(group=group)  # nobody pushes before everybody has zeroed and published its buffer
+
+    def allreduce_add(self, partial: torch.Tensor, h: torch.Tensor):
+        assert partial.is_contiguous() and h.is_contiguous() and partial.dtype == h.dtype == torch.bfloat16
+        assert partial.numel() == h.numel()
+        self._lib.check(self._lib.lib().ao_b200_tp_allreduce_add(
+            partial.data_ptr(), h.data_ptr(), partial.numel(), self.bufs, self.rank, self.world_size, self.max_elems,
+            torch.cuda.current_stream(partial.device).cuda_stream), "tp_allreduce_add")
+        return h
+
+    def status(self) -> int:
+        """0 = ok, 1 = a peer never arrived within the kernel's spin bound (results are garbage)."""
+        st = self._ct.c_int(0)
+        self._lib.check(self._lib.lib().ao_b200_tp_status(self.own, self._ct.byref(st)), "tp_status")
+        return st.value
+
+    def close(self):
+        L = self._lib.lib()
+        for p in self._opened:
+            L.ao_b200_tp_close(p)
+        self._opened = []
+        if self.own:
+            L.ao_b200_tp_free(self.own)
+            self.own = None
+
+
 class TPContext:
     """Rank / world size of the tensor-parallel group and the three collectives the model needs."""
 
@@ -39,7 +97,15 @@ class TPContext:
         self.world_size = dist.get_world_size(group) if world_size is None else int(world_size)
         self.device = device
         self._gather = {}
+        self.peer: Optional[PeerExchange] = None
         assert 0 <= self.rank < self.world_size
+
+    def enable_peer_exchange(self, max_elems: int):
+        """Decode path: replace NCCL all-reduce + add by the one-launch NVLink peer-memory kernel for tensors of up to
+        max_elems bf16 elements.  AO_B200_TP_PEER=0 keeps NCCL (A/B comparison)."""
+        if self.world_size > 1 and self.peer is None and os.environ.get("AO_B200_TP_PEER", "1") != "0":
+            self.peer = PeerExchange(self.rank, self.world_size, max_elems, self.device, self.group)
+        return self.peer
 
     @classmethod
     def from_env(cls, backend: Optional[str] = None, device=None):
@@ -60,6 +126,8 @@ class TPContext:
 
     def all_reduce_add(self, delta: torch.Tensor, h: torch.Tensor) -> torch.Tensor:
         """h += sum over ranks of delta  (the residual add that follows a row-parallel projection)."""
+        if self.peer is not None and delta.is_cuda and delta.numel() <= self.peer.max_elems and delta.numel() % 8 == 0:
+            return self.peer.allreduce_add(delta, h)
         self.all_reduce(delta)
         return h.add_(delta)
 
