@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--quant", default="int4")
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--prefill", type=int, default=0, help="also run one eager prefill of this many tokens (prefill GEMM)")
     args = ap.parse_args()
     cfg = ModelArgs.from_name("Llama-3-8B")
     cfg.n_layer = args.layers
@@ -36,6 +37,12 @@ def main():
     for _ in range(args.steps):
         gen.engine.step()
     torch.cuda.synchronize()
+    if args.prefill:
+        model.setup_caches(args.batch, args.prefill + 8)
+        idx = torch.randint(0, cfg.vocab_size, (args.batch, args.prefill), device="cuda")
+        with torch.no_grad():
+            model(idx, torch.arange(args.prefill, device="cuda", dtype=torch.int32))
+        torch.cuda.synchronize()
     print("ok", gen.engine.launches_per_step, "launches/step")
 
 

@@ -571,7 +571,11 @@ static bool plan_fused(int M, int MT, int64_t Kp, int max_stages, FusedPlan& pl)
   }();
   const size_t one_per_sm = 226 * 1024;
   int st = 0;
-  if (fixed + 4 * stage_b <= two_per_sm) {
+  static const size_t min2 = []() {  // fewest ring stages for which two co-resident CTAs still beat one with a deep ring
+    const char* e = std::getenv("AO_B200_MIN_STAGES2");
+    return (size_t)(e ? std::atoi(e) : 4);  // 3 measured slower on w2 (K = 14336): 394 vs 350 us per 32 layers
+  }();
+  if (fixed + min2 * stage_b <= two_per_sm) {
     st = (int)((two_per_sm - fixed) / stage_b);
   } else if (fixed + 3 * stage_b <= one_per_sm) {
     st = (int)((one_per_sm - fixed) / stage_b);
