@@ -23,7 +23,7 @@
 
 namespace ao {
 
-constexpr int kTpMaxWorld = 8, kTpMaxCtas = 16, kTpThreads = 1024;
+constexpr int kTpMaxWorld = 8, kTpMaxCtas = 32, kTpThreads = 512;
 constexpr int kTpHeaderBytes = 256;
 constexpr long long kTpSpinClocks = 4000000000ll;  // ~2 s at 1.9 GHz
 
@@ -49,46 +49,67 @@ tp_allreduce_add_kernel(const __nv_bfloat16* __restrict__ partial, __nv_bfloat16
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(hdr) + 1;  // every CTA reads it before the last one bumps it
   const int slot = e & 1;
   const int64_t i = ((int64_t)blockIdx.x * kTpThreads + threadIdx.x) * 8;  // 8 bf16 per thread = 4 packets
-  // packet of elements (i + 2 j, i + 2 j + 1) from rank r: data_off + (r * max_n / 2 + (i / 2 + j)) * 8
+  // packet j of this thread (elements i + 2 j, i + 2 j + 1) from rank r sits at
+  //   data_off + (r * max_n / 2 + pk0 + 32 j) * 8,  pk0 = (global warp * 4) * 32 + lane:
+  // one warp-wide store instruction covers 256 contiguous bytes = two full 128-byte lines on the link (lane-major
+  // packets would make it 32 partial sectors)
   const size_t data_off = kTpHeaderBytes + ((size_t)slot * world) * (max_n / 2) * 8;
+  const size_t pk0 = (size_t)((blockIdx.x * kTpThreads + threadIdx.x) >> 5) * 128 + (threadIdx.x & 31);
   if (i < n) {
     const uint4 v = *reinterpret_cast<const uint4*>(partial + i);
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
     for (int d = 1; d < world; ++d) {  // staggered so that the ranks do not all hit the same peer first
       const int p = (rank + d) % world;
-      uint8_t* dst = peers.buf[p] + data_off + ((size_t)rank * (max_n / 2) + i / 2) * 8;
+      uint8_t* dst = peers.buf[p] + data_off + ((size_t)rank * (max_n / 2) + pk0) * 8;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) st_packet(dst + 8 * j, w[j], e);
+      for (int j = 0; j < 4; ++j) st_packet(dst + 256 * j, w[j], e);
     }
     const uint4 hv = *reinterpret_cast<const uint4*>(h + i);  // in flight while the packets cross the link
+    // poll: ALL packets of ALL peers are requested before any tag is looked at (one L2 round trip per sweep instead of
+    // one per packet: 6.4 -> see profiles/ us at world 2, and no growth with the world size)
+    uint32_t u[kTpMaxWorld - 1][4];
+    const long long t0 = clock64();
+    for (;;) {
+      bool all = true;
+#pragma unroll
+      for (int d = 1; d < kTpMaxWorld; ++d) {
+        if (d < world) {
+          const int r = (rank + d) % world;
+          const uint8_t* src = mine + data_off + ((size_t)r * (max_n / 2) + pk0) * 8;
+          uint2 pk[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) pk[j] = ld_packet(src + 256 * j);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            all = all && (pk[j].y == e);
+            u[d - 1][j] = pk[j].x;
+          }
+        }
+      }
+      if (all) break;
+      if (clock64() - t0 > kTpSpinClocks) {  // a peer never arrived: flag the error, do not hang the GPU
+        atomicExch(hdr + 2, 1u);
+        break;
+      }
+    }
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    const long long t0 = clock64();
-    for (int r = 0; r < world; ++r) {
-      uint32_t u[4];
-      if (r == rank) {
+    for (int r = 0; r < world; ++r) {  // rank order, whatever the polling order was
+      const int d = (r - rank + world) % world;
+      uint32_t q[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) u[j] = w[j];
-      } else {
-        const uint8_t* src = mine + data_off + ((size_t)r * (max_n / 2) + i / 2) * 8;
+      for (int j = 0; j < 4; ++j) q[j] = w[j];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint2 pk = ld_packet(src + 8 * j);
-          while (pk.y != e) {
-            if (clock64() - t0 > kTpSpinClocks) {  // a peer never arrived: flag the error, do not hang the GPU
-              atomicExch(hdr + 2, 1u);
-              break;
-            }
-            pk = ld_packet(src + 8 * j);
-          }
-          u[j] = pk.x;
+      for (int dd = 1; dd < kTpMaxWorld; ++dd)
+        if (dd == d) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) q[j] = u[dd - 1][j];
         }
-      }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        acc[2 * j] += bf16_bits_to_float(u[j] & 0xffffu);
-        acc[2 * j + 1] += bf16_bits_to_float(u[j] >> 16);
+        acc[2 * j] += bf16_bits_to_float(q[j] & 0xffffu);
+        acc[2 * j + 1] += bf16_bits_to_float(q[j] >> 16);
       }
     }
     float hf[8];
