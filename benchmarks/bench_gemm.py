@@ -32,9 +32,29 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--m", type=int, nargs="+", default=[32, 128, 256, 1024, 2048, 4096, 8192])
     ap.add_argument("--gs", type=int, default=128)
+    ap.add_argument("--int8", action="store_true", help="int8 weight-only: ours vs the reference's eager formula")
     args = ap.parse_args()
     shapes = [(6144, 4096), (4096, 4096), (28672, 4096), (4096, 14336)]
     rows = []
+    if args.int8:
+        for n, k in shapes:
+            torch.manual_seed(0)
+            w = torch.randn(n, k, dtype=torch.bfloat16, device="cuda")
+            q, sc = T.b200_int8_quantize(w, 1e-7, True)
+            packed = T.b200_int8_pack(q)
+            wb = q.to(torch.bfloat16)
+            for m in args.m:
+                x = torch.randn(m, k, dtype=torch.bfloat16, device="cuda")
+                t_ours = timeit(lambda: T.b200_int8_weight_only_mm(x, packed, sc))
+                t_ref = timeit(lambda: torch.mm(x, q.t().to(torch.bfloat16)) * sc)   # plain_layout.py:256-262, eager
+                t_bf16 = timeit(lambda: torch.nn.functional.linear(x, wb))
+                fl = 2.0 * m * n * k
+                rows.append({"kind": "int8", "N": n, "K": k, "M": m, "ours_us": round(t_ours, 1),
+                             "ref_eager_us": round(t_ref, 1), "cublas_bf16_us": round(t_bf16, 1),
+                             "ours_tflops": round(fl / t_ours * 1e-6, 1), "ref_eager_tflops": round(fl / t_ref * 1e-6, 1),
+                             "cublas_bf16_tflops": round(fl / t_bf16 * 1e-6, 1)})
+                print(json.dumps(rows[-1]), flush=True)
+        return
     for n, k in shapes:
         torch.manual_seed(0)
         w = torch.randn(n, k, dtype=torch.bfloat16, device="cuda")

@@ -77,7 +77,8 @@ def main():
         w = torch.randn(n, k, dtype=torch.bfloat16, device=dev)
         if args.int8:
             q, s = T.b200_int8_quantize(w, 1e-7, True)
-            ws = [(q.clone(), s.clone()) for _ in range(copies)]
+            pk8 = T.b200_int8_pack(q)
+            ws = [(pk8.clone(), s.clone()) for _ in range(copies)]
         else:
             p, sz = T.b200_int4_quantize_pack(w, args.group, 1e-6, True)
             ws = [(p.clone(), sz.clone()) for _ in range(copies)]

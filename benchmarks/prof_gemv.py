@@ -23,6 +23,7 @@ x = torch.randn(a.m, a.k, dtype=torch.bfloat16, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 if a.int8:
     q, s = T.b200_int8_quantize(w, 1e-7, True)
+    q = T.b200_int8_pack(q)
     f = lambda: T.b200_int8_weight_only_mm(x, q, s)
 else:
     p, sz = T.b200_int4_quantize_pack(w, a.group, 1e-6, True)

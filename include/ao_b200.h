@@ -154,11 +154,32 @@ AO_B200_API int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, in
 AO_B200_API int ao_b200_int8_quantize(const void* w, int64_t N, int64_t K, int64_t ldw, float eps, int div_mode,
                           int8_t* q, void* scale, void* stream);
 
+/* strip-major int8 layout (this library's format): uint8 [Np/16][Kp/64][2][32][16], BIASED bytes u = q + 128.
+ *   strip s (16 rows) x k-tile kt (64 k) = 1024 contiguous bytes = two 32-k halves of 512 bytes; inside a half lane
+ *   l = (g = l>>2, c = l&3) owns 16 bytes = 4 words; word j holds row 16 s + g + 8 (j&1), k0 = 64 kt + 32 h + 8 c + 4 (j>>1),
+ *   bytes k0 .. k0+3.  As with the int4 layout all tiles of a strip are contiguous (Kp * 16 bytes), the lane chunk is the
+ *   A fragment of two m16n8k16 MMAs and the (lane, column) pattern of a tcgen05.st.16x128b.  Rows >= N / columns >= K hold
+ *   q = 0.  PlainAQTTensorImpl.int_data (plain_layout.py:47-229) is recovered exactly by ao_b200_int8_unpack. */
+AO_B200_API int ao_b200_int8_pack(const int8_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp, void* packed, void* stream);
+AO_B200_API int ao_b200_int8_unpack(const void* packed, int64_t Np, int64_t Kp, int64_t N, int64_t K, int8_t* q, void* stream);
+
 /* Replacement for _linear_fp_act_int8_weight_impl (plain_layout.py:250-266):
- *   y = bf16( bf16( x @ q^T ) * scale ).   x bf16 [M][K] (ldx), q int8 [N][K], scale bf16 [N]. */
-AO_B200_API int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx,
-                    const int8_t* q, const void* scale, int64_t N,
-                    void* y, int64_t ldy, void* stream);
+ *   y = bf16( bf16( x @ q^T ) * scale ).   x bf16 [M][Kx] (ldx; k >= Kx reads as zero), packed strip-major int8 (Np x Kp),
+ *   scale bf16 [N_out], y bf16 [M][N_out] (ldy).  M <= 16: TMA-ring GEMV (gemv_int8_fused.cu); larger M: tcgen05 GEMM
+ *   (needs Np % 128 == 0 and a workspace of ao_b200_int8_mm_workspace_bytes; otherwise the GEMV is looped). */
+AO_B200_API int64_t ao_b200_int8_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp);
+AO_B200_API int ao_b200_int8_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx,
+                    const void* packed, const void* scale, int64_t Np, int64_t Kp,
+                    void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* int8 sibling of ao_b200_int4_gemv_fused (same prologue / epilogue semantics, M <= 16).  For epilogue 2 the packed
+ * weight and `scale` hold w1 / w3 interleaved 8 rows / 8 rows per strip.  Returns AO_B200_ERR_WORKSPACE when M * Kp does
+ * not fit the shared-memory staging (use ao_b200_int8_mm then). */
+AO_B200_API int ao_b200_int8_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx,
+                            const void* packed, const void* scale, int64_t Np, int64_t Kp,
+                            void* y, int64_t N_out, int64_t ldy,
+                            const void* norm_weight, float norm_eps, const void* residual, int64_t ld_res,
+                            int epilogue, void* stream);
 
 /* ---------------------------------------------------------------- decode-step glue ---- */
 /* The non-GEMM remainder of one Llama decode step (reference:

@@ -380,6 +380,33 @@ def dequantize_int8(q, scale):
     return bf16_round(q.astype(F32) * scale.reshape(-1, 1).astype(F32))
 
 
+# ---- the B200 strip-major int8 layout (this build's own; include/ao_b200.h) ----
+# uint8 [N/16][K/64][2 halves][32 lanes][16]: biased bytes u = q + 128; word j (4 bytes) of lane l=(g=l>>2, c=l&3) in
+# half h of tile (s, kt) holds row 16 s + g + 8 (j&1), k0 = 64 kt + 32 h + 8 c + 4 (j>>1), bytes k0..k0+3.
+def pack_int8_b200(q):
+    n, k = q.shape
+    assert n % 16 == 0 and k % 64 == 0
+    u = (q.astype(np.int16) + 128).astype(np.uint8)
+    u6 = u.reshape(n // 16, 16, k // 64, 2, 4, 2, 4)   # [s][row][kt][h][c][j>>1][4]
+    out = np.zeros((n // 16, k // 64, 2, 32, 4, 4), dtype=np.uint8)
+    for lane in range(32):
+        g, c = lane >> 2, lane & 3
+        for j in range(4):
+            out[:, :, :, lane, j, :] = u6[:, g + 8 * (j & 1), :, :, c, j >> 1, :]
+    return out.reshape(n // 16, k // 64, 1024)
+
+
+def unpack_int8_b200(packed):
+    s_, kt_ = packed.shape[0], packed.shape[1]
+    p = packed.reshape(s_, kt_, 2, 32, 4, 4)
+    u6 = np.zeros((s_, 16, kt_, 2, 4, 2, 4), dtype=np.uint8)
+    for lane in range(32):
+        g, c = lane >> 2, lane & 3
+        for j in range(4):
+            u6[:, g + 8 * (j & 1), :, :, c, j >> 1, :] = p[:, :, :, lane, j, :]
+    return (u6.reshape(s_ * 16, kt_ * 64).astype(np.int16) - 128).astype(np.int8)
+
+
 def sqnr_db(ref, x):
     """Reference: torchao/quantization/utils.py:51-55 compute_error."""
     ref = ref.astype(np.float64)

@@ -293,8 +293,10 @@ def test_int8_quantize_matches_golden(path):
     q, s = T.b200_int8_quantize(w, float(np.finfo(np.float32).eps), False)
     assert np.array_equal(bits_of(s), g["scale"])
     assert np.array_equal(q.cpu().numpy(), g["q"])
+    packed = T.b200_int8_pack(q)
+    assert torch.equal(T.b200_int8_unpack(packed, q.shape[0], q.shape[1]), q)
     x = bf16_from_bits(g["x"])
-    y = T.b200_int8_weight_only_mm(x, q, s)
+    y = T.b200_int8_weight_only_mm(x, packed, s)
     assert o.sqnr_db(o.from_bits(g["y_cpu"]), as_f32(y)) >= 40.0
 
 
@@ -315,13 +317,14 @@ def test_int8_mm_matches_reference_formula(shape, m):
     w = torch.randn(n, k, dtype=torch.bfloat16, device=DEV)
     x = torch.randn(m, k, dtype=torch.bfloat16, device=DEV)
     q, s = T.b200_int8_quantize(w, torch.finfo(torch.float32).eps, True)
-    y = T.b200_int8_weight_only_mm(x, q, s)
+    packed = T.b200_int8_pack(q)
+    y = T.b200_int8_weight_only_mm(x, packed, s)
     y_ref = torch.mm(x, q.t().to(torch.bfloat16)) * s          # plain_layout.py:256-262
     assert compute_error(y_ref, y).item() >= 40.0
     assert mean_abs_rel(y_ref, y) < 1e-2
     # exact-integer activations make the fp32 accumulation order-independent -> bit-exact
     xi = torch.randint(-4, 5, (m, k), device=DEV).to(torch.bfloat16)
-    yi = T.b200_int8_weight_only_mm(xi, q, s)
+    yi = T.b200_int8_weight_only_mm(xi, packed, s)
     yi_ref = torch.mm(xi, q.t().to(torch.bfloat16)) * s
     assert torch.equal(yi, yi_ref)
 
@@ -386,7 +389,11 @@ def test_opcheck():
     opcheck(T.b200_int4_dequantize, (packed, sz2, 64), test_utils=utils)
     opcheck(T.b200_int8_quantize, (w, 1e-7, True), test_utils=utils)
     q8, s8 = T.b200_int8_quantize(w, 1e-7, True)
-    opcheck(T.b200_int8_weight_only_mm, (x, q8, s8), test_utils=utils)
+    opcheck(T.b200_int8_pack, (q8,), test_utils=utils)
+    p8 = T.b200_int8_pack(q8)
+    opcheck(T.b200_int8_unpack, (p8, 64, 256), test_utils=utils)
+    opcheck(T.b200_int8_weight_only_mm, (x, p8, s8), test_utils=utils)
+    opcheck(T.b200_int8_gemv_fused, (x, p8, s8, None, 0.0, None, 0), test_utils=utils)
 
 
 def test_errors_are_loud():

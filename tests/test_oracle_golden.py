@@ -137,3 +137,16 @@ def test_recip_mode_differs_rarely():
     s0, _ = o.choose_qparams_tinygemm(w, 128, div_mode="ieee")
     s1, _ = o.choose_qparams_tinygemm(w, 128, div_mode="recip")
     assert (s0 != s1).mean() < 1e-2
+
+
+def test_int8_b200_layout_round_trip_and_word_contract():
+    rng = np.random.default_rng(7)
+    q = rng.integers(-128, 128, size=(48, 192), dtype=np.int8)
+    p = o.pack_int8_b200(q)
+    assert p.shape == (3, 3, 1024) and p.dtype == np.uint8
+    assert np.array_equal(o.unpack_int8_b200(p), q)
+    # the contract the kernels rely on: half h, lane (g, c), word j -> row g + 8 (j & 1), k0 = 32 h + 8 c + 4 (j >> 1)
+    s, kt, h, g, c, j = 1, 2, 1, 5, 3, 2
+    word = p[s, kt].reshape(2, 32, 4, 4)[h, 4 * g + c, j]
+    row, k0 = 16 * s + g + 8 * (j & 1), 64 * kt + 32 * h + 8 * c + 4 * (j >> 1)
+    assert np.array_equal(word.astype(np.int16) - 128, q[row, k0:k0 + 4].astype(np.int16))

@@ -57,9 +57,20 @@ class _Linear:
         elif isinstance(w0, AffineQuantizedTensor) and isinstance(w0.tensor_impl, PlainAQTTensorImpl):
             self.kind = "int8"
             impls = [w.tensor_impl for w in weights]
-            self.q = torch.cat([i.int_data for i in impls], dim=0).contiguous() if len(impls) > 1 else impls[0].int_data
-            self.scale = torch.cat([i.scale for i in impls], dim=0).contiguous() if len(impls) > 1 else impls[0].scale
-            self.weight_bytes = self.q.numel() + self.scale.numel() * 2
+            assert all(not i.transposed for i in impls)
+            if interleave_gate_up:
+                from ...ops import interleave_gate_up_int8 as _ilv8
+                assert len(impls) == 2 and int(weights[0].shape[0]) % 8 == 0
+                q, self.scale = _ilv8(impls[0].int_data, impls[0].scale, impls[1].int_data, impls[1].scale)
+                self.packed = torch.ops.torchao.b200_int8_pack(q)
+                self.interleaved = True
+            elif len(impls) > 1:
+                self.packed = torch.ops.torchao.b200_int8_pack(torch.cat([i.int_data for i in impls], dim=0))
+                self.scale = torch.cat([i.scale for i in impls], dim=0).contiguous()
+            else:
+                self.packed, self.scale = impls[0].packed, impls[0].scale.contiguous()
+            self.np_, self.kp = self.packed.shape[0] * 16, self.packed.shape[1] * 64
+            self.weight_bytes = self.n * self.k + self.scale.numel() * 2
         else:
             self.kind = "bf16"  # unquantized line: library GEMM (cuBLAS), for comparison only
             self.w = torch.cat([w.detach() for w in weights], dim=0).contiguous() if len(weights) > 1 else w0.detach()
@@ -67,12 +78,21 @@ class _Linear:
             self.weight_bytes = self.w.numel() * 2
 
     def workspace_bytes(self, m):
-        if self.kind != "int4":
-            return 0
-        return int(_lib.lib().ao_b200_int4_mm_workspace_bytes(m, self.np_, self.kp))
+        if self.kind == "int4":
+            return int(_lib.lib().ao_b200_int4_mm_workspace_bytes(m, self.np_, self.kp))
+        if self.kind == "int8":
+            return int(_lib.lib().ao_b200_int8_mm_workspace_bytes(m, self.np_, self.kp))
+        return 0
 
     def launch_fused(self, x, y, stream, norm_w=None, eps=0.0, residual=None, epilogue=0, ws=None):
-        """ao_b200_int4_gemv_fused: RMSNorm prologue (norm_w), epilogue 0 plain / 1 residual add / 2 SiLU*mul."""
+        """ao_b200_int4_gemv_fused / ao_b200_int8_gemv_fused: RMSNorm prologue (norm_w), epilogue 0 plain / 1 residual
+        add / 2 SiLU*mul."""
+        if self.kind == "int8":
+            _lib.check(_lib.lib().ao_b200_int8_gemv_fused(
+                x.data_ptr(), x.shape[0], self.k, x.stride(0), self.packed.data_ptr(), self.scale.data_ptr(), self.np_,
+                self.kp, y.data_ptr(), self.n, y.stride(0), _ptr(norm_w), eps, _ptr(residual),
+                0 if residual is None else residual.stride(0), epilogue, stream), "int8_gemv_fused")
+            return
         assert self.kind == "int4"
         _lib.check(_lib.lib().ao_b200_int4_gemv_fused(
             x.data_ptr(), x.shape[0], self.k, x.stride(0), self.packed.data_ptr(), self.sz.data_ptr(), self.np_,
@@ -81,7 +101,7 @@ class _Linear:
             "int4_gemv_fused")
 
     def fused_fits(self, m):
-        return self.kind == "int4" and m * (2 * self.kp + 16) <= 150 * 1024
+        return self.kind in ("int4", "int8") and m * (2 * self.kp + 16) <= 150 * 1024
 
     def launch(self, x: torch.Tensor, y: torch.Tensor, ws: Optional[torch.Tensor], stream: int):
         m = x.shape[0]
@@ -92,8 +112,9 @@ class _Linear:
                                          self.n, y.stride(0), _ptr(ws), 0 if ws is None else ws.numel(), stream),
                        "int4_mm")
         elif self.kind == "int8":
-            _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, self.k, x.stride(0), self.q.data_ptr(),
-                                         self.scale.data_ptr(), self.n, y.data_ptr(), y.stride(0), stream), "int8_mm")
+            _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, self.k, x.stride(0), self.packed.data_ptr(),
+                                         self.scale.data_ptr(), self.np_, self.kp, y.data_ptr(), self.n, y.stride(0),
+                                         None, 0, stream), "int8_mm")
         else:
             torch.mm(x, self.w.t(), out=y)
 
@@ -122,7 +143,8 @@ class DecodeEngine:
         self.layers = []
         probe = [_Linear([model.layers[0].attention.wqkv.weight]), _Linear([model.layers[0].feed_forward.w2.weight])]
         self.fused = (fused and all(l.fused_fits(batch_size) for l in probe)
-                      and int(model.layers[0].feed_forward.w1.weight.shape[0]) % 128 == 0)
+                      and int(model.layers[0].feed_forward.w1.weight.shape[0]) % 128 == 0
+                      and type(model.layers[0].feed_forward.w1.weight) is type(model.layers[0].feed_forward.w3.weight))
         for blk in model.layers:
             ff = blk.feed_forward
             fuse = int(ff.w1.weight.shape[0]) % 128 == 0 and type(ff.w1.weight) is type(ff.w3.weight)

@@ -14,8 +14,13 @@ int64_t int4_gemv_tc_workspace_bytes(int64_t Np);
 int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np, int64_t Kp,
                  int G, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s);
 int64_t int4_gemm_tc_workspace_bytes(int64_t M, int64_t Np, int64_t Kp);
-int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
-              void* y, int64_t ldy, cudaStream_t s);
+int int8_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Kp,
+              void* y, int64_t N_out, int64_t ldy, cudaStream_t s);
+int int8_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Np,
+                    int64_t Kp, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
+                    int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
+int int8_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Np,
+                 int64_t Kp, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s);
 }  // namespace ao
 
 extern "C" const char* ao_b200_error_string(int code) {
@@ -29,7 +34,7 @@ extern "C" const char* ao_b200_error_string(int code) {
   return "unknown error";
 }
 
-extern "C" int ao_b200_abi_version(void) { return 2; }
+extern "C" int ao_b200_abi_version(void) { return 3; }
 
 #include <cstdlib>
 namespace {
@@ -137,18 +142,51 @@ extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int
                              static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int ao_b200_int8_mm(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale,
-                               int64_t N, void* y, int64_t ldy, void* stream) {
-  AO_CHECK_ARG(x && q && scale && y && M > 0 && N > 0 && K > 0);
-  AO_CHECK_ARG(ldx % 8 == 0 && ldx >= K && ldy >= N && ao_aligned(x, 16) && ao_aligned(q, 16));
-  if (K % 16 != 0) return AO_B200_ERR_UNSUPPORTED;
+extern "C" int64_t ao_b200_int8_mm_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
+  return M > 16 ? ao::int4_gemm_tc_workspace_bytes(M, Np, Kp) : 0;  // the prefill GEMM's permuted copy of the activations
+}
+
+static int int8_args_ok(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Np,
+                        int64_t Kp, const void* y, int64_t N_out) {
+  AO_CHECK_ARG(x && packed && scale && y && M > 0);
+  AO_CHECK_ARG(Np > 0 && Kp > 0 && Np % 16 == 0 && Kp % 64 == 0 && N_out > 0 && N_out <= Np);
+  AO_CHECK_ARG(Kx > 0 && Kx <= Kp && Kx % 8 == 0 && ldx % 8 == 0 && ldx >= Kx);
+  AO_CHECK_ARG(ao_aligned(x, 16) && ao_aligned(packed, 16) && ao_aligned(scale, 2));
+  return AO_B200_OK;
+}
+
+extern "C" int ao_b200_int8_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale,
+                               int64_t Np, int64_t Kp, void* y, int64_t N_out, int64_t ldy, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  if (int e = int8_args_ok(x, M, Kx, ldx, packed, scale, Np, Kp, y, N_out)) return e;
+  AO_CHECK_ARG(ldy >= N_out);
   auto s = static_cast<cudaStream_t>(stream);
   auto xb = static_cast<const __nv_bfloat16*>(x);
   auto yb = static_cast<__nv_bfloat16*>(y);
+  if (M > 16 && tunables().gemm_tc) {
+    const int e = ao::int8_gemm_tc(x, M, Kx, ldx, packed, scale, Np, Kp, y, N_out, ldy, workspace, workspace_bytes, s);
+    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+  }
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
-    int e = ao::int8_gemv(xb + m0 * ldx, mc, K, ldx, q, scale, N, yb + m0 * ldy, ldy, s);
+    int e = ao::int8_gemv_fused(xb + m0 * ldx, mc, Kx, ldx, packed, scale, Np, Kp, yb + m0 * ldy, N_out, ldy, nullptr, 0.f,
+                                nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
+    if (e == AO_B200_ERR_WORKSPACE) e = ao::int8_gemv(xb + m0 * ldx, mc, Kx, ldx, packed, scale, Kp, yb + m0 * ldy, N_out, ldy, s);
     if (e) return e;
   }
   return AO_B200_OK;
+}
+
+extern "C" int ao_b200_int8_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed,
+                                       const void* scale, int64_t Np, int64_t Kp, void* y, int64_t N_out, int64_t ldy,
+                                       const void* norm_weight, float norm_eps, const void* residual, int64_t ld_res,
+                                       int epilogue, void* stream) {
+  if (int e = int8_args_ok(x, M, Kx, ldx, packed, scale, Np, Kp, y, N_out)) return e;
+  AO_CHECK_ARG(M <= 16 && epilogue >= 0 && epilogue <= 2);
+  AO_CHECK_ARG(epilogue != 1 || residual != nullptr);
+  AO_CHECK_ARG(epilogue != 2 || (N_out % 16 == 0 && ldy >= N_out / 2));
+  AO_CHECK_ARG(epilogue == 2 || ldy >= N_out);
+  AO_CHECK_ARG(!norm_weight || ao_aligned(norm_weight, 16));
+  return ao::int8_gemv_fused(x, M, Kx, ldx, packed, scale, Np, Kp, y, N_out, ldy, norm_weight, norm_eps, residual, ld_res,
+                             epilogue, tunables().stages, tunables().pdl != 0, static_cast<cudaStream_t>(stream));
 }

@@ -69,6 +69,19 @@ __device__ __forceinline__ void dequant_word(uint32_t w, uint32_t s2, uint32_t z
   }
 }
 
+// 4 biased int8 (u = q + 128, one register) -> 2 bf16x2 registers (q0,q1), (q2,q3), exact: byte-insert into the fp32
+// 1.5 * 2^23 magic, subtract, pack pairs
+__device__ __forceinline__ void u8x4_to_bf16x2x2(uint32_t u, uint32_t& o01, uint32_t& o23) {
+  constexpr uint32_t kMagic = 0x4B400000u;         // 1.5 * 2^23
+  constexpr float kBias = 12582912.0f + 128.0f;
+  const float f0 = __uint_as_float(__byte_perm(u, kMagic, 0x7650)) - kBias;
+  const float f1 = __uint_as_float(__byte_perm(u, kMagic, 0x7651)) - kBias;
+  const float f2 = __uint_as_float(__byte_perm(u, kMagic, 0x7652)) - kBias;
+  const float f3 = __uint_as_float(__byte_perm(u, kMagic, 0x7653)) - kBias;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o01) : "f"(f1), "f"(f0));
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o23) : "f"(f3), "f"(f2));
+}
+
 // D(16x8, f32) += A(16x16, bf16, row) * B(16x8, bf16, col)
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                                uint32_t a3, uint32_t b0, uint32_t b1) {

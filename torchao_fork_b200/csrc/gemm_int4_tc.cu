@@ -39,7 +39,7 @@ namespace ao {
 constexpr int kGmEpiWarps = 4, kGmDqWarps = 16;  // dequant warps: two sets of 8 (one strip each), alternating stages
 constexpr int kGmProducerWarp = kGmEpiWarps + kGmDqWarps, kGmMmaWarp = kGmProducerWarp + 1;
 constexpr int kGmThreads = (kGmMmaWarp + 1) * 32;  // 704
-constexpr int kGmWSlots = 3, kGmWSlotBytes = 8 * 4 * 512;  // weight ring: 256-k slices of the 128-row block (16 KB)
+constexpr int kGmWSlots = 3, kGmWSlotBytes = 8 * 4 * 512;  // weight ring: 16 KB slices of the 128-row block (256 k of int4, 128 k of int8)
 constexpr int kGmMaxStages = 8;                            // activation ring slots (64 k each)
 constexpr int kGmHeader = 1024;                            // mbarriers + TMEM base address
 
@@ -58,6 +58,7 @@ __device__ long long ao_gm_trace[4][kGmMmaWarp + 1][kGmTraceIts];
 struct GemmTcParams {
   const uint8_t* packed;     // strip-major [Np/16][Kp/64][512 B]
   const uint32_t* sz;        // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
+  const __nv_bfloat16* scale8;  // int8 (G == 0): per-row scale [N_out], applied to the bf16-rounded accumulator
   const __nv_bfloat16* xt;   // permuted activations [Mpad/NT][Kp/64][8 chunks][NT][8]
   __nv_bfloat16* y;          // [M][ldy]
   int M, KT, stages, tmem_cols, cluster, vec_store;
@@ -157,9 +158,14 @@ __device__ __forceinline__ bool gm_elect_one() {
 // tile per slot, each CTA of the cluster multicasting its 1 / CL share as ONE copy).  A bulk copy costs its issuing
 // warp ~100 clocks, so copies per 64 k are what bounds the producer: 3 here (first version: 10, producer-bound at
 // 1200 clocks per tile against 512 of MMA).  Tensor memory: columns [0, NT) accumulator, NT + 32 slot ..: A tiles.
+// G == 0: int8 weights (strip-major biased int8, 1 KB per 16 x 64 tile, per-row scale in the epilogue) — same pipeline,
+// the dequant warps convert bytes to bf16 exactly instead of applying the int4 affine.
 template <int G, int NT>
 __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmTcParams p) {
   extern __shared__ __align__(1024) uint8_t gm_smem[];
+  constexpr bool kI8 = (G == 0);
+  constexpr int kTileB = kI8 ? 1024 : 512;                    // bytes of one (strip, 64-k) tile
+  constexpr int kSlotTiles = kGmWSlotBytes / (8 * kTileB);    // k-tiles per weight-ring slot: 4 (int4) / 2 (int8)
   constexpr uint32_t kXStage = NT * 128;
   constexpr uint32_t kChunk = NT * 16;  // bytes between consecutive 8-k chunks of the B tile (descriptor LBO)
   const int stages = p.stages, KT = p.KT;
@@ -180,7 +186,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     if (lane == 0) {
       for (int s = 0; s < kGmWSlots; ++s) {
         mbar_init(&wfull[s], 1);
-        mbar_init(&wempty[s], 32);  // 8 strips x 4 tiles, one arrival per (dequant warp, tile)
+        mbar_init(&wempty[s], 8 * kSlotTiles);  // one arrival per (dequant warp = strip, tile)
       }
       for (int s = 0; s < stages; ++s) {
         mbar_init(&xfull[s], 1);
@@ -249,13 +255,14 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     // ---- dequant warps: packed words -> bf16 W' (reference arithmetic, one rounding) -> tensor memory -------------
     const int dq = (warp - kGmEpiWarps) & 7, set = (warp - kGmEpiWarps) >> 3, qd = warp & 3, strip = 2 * qd + (dq >> 2);
     const int g = lane >> 2;
-    constexpr int kGroupsPerTile = G >= 64 ? 1 : 64 / G;
-    const int n_groups = KT * 64 / G;
-    const uint32_t* szp = p.sz + ((int64_t)(nb * 8 + strip) * n_groups) * 16 + g;
+    constexpr int GG = kI8 ? 64 : G;  // (int8: no per-group parameters; GG only keeps the int4 index math well-formed)
+    constexpr int kGroupsPerTile = GG >= 64 ? 1 : 64 / GG;
+    const int n_groups = KT * 64 / GG;
+    const uint32_t* szp = kI8 ? nullptr : p.sz + ((int64_t)(nb * 8 + strip) * n_groups) * 16 + g;
     const uint32_t taddr0 = tb + ((uint32_t)(32 * qd + 16 * (dq >> 2)) << 16) + NT;
     uint32_t szn[kGroupsPerTile][2];
-    {
-      const int64_t grp = G >= 64 ? (int64_t)set * 64 / G : (int64_t)set * kGroupsPerTile;
+    if constexpr (!kI8) {
+      const int64_t grp = GG >= 64 ? (int64_t)set * 64 / GG : (int64_t)set * kGroupsPerTile;
 #pragma unroll
       for (int h = 0; h < kGroupsPerTile; ++h) {
         szn[h][0] = __ldg(szp + (grp + h) * 16);
@@ -265,36 +272,52 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     for (int it = set; it < KT; it += 2) {
       const int slot = it % stages;
       uint32_t s2[kGroupsPerTile][2], z2[kGroupsPerTile][2];
+      if constexpr (!kI8) {
 #pragma unroll
-      for (int h = 0; h < kGroupsPerTile; ++h)
+        for (int h = 0; h < kGroupsPerTile; ++h)
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-          s2[h][r] = __byte_perm(szn[h][r], 0, 0x1010);
-          z2[h][r] = __byte_perm(szn[h][r], 0, 0x3232);
-        }
-      if (it + 2 < KT) {
-        const int64_t grp = G >= 64 ? (int64_t)(it + 2) * 64 / G : (int64_t)(it + 2) * kGroupsPerTile;
+          for (int r = 0; r < 2; ++r) {
+            s2[h][r] = __byte_perm(szn[h][r], 0, 0x1010);
+            z2[h][r] = __byte_perm(szn[h][r], 0, 0x3232);
+          }
+        if (it + 2 < KT) {
+          const int64_t grp = GG >= 64 ? (int64_t)(it + 2) * 64 / GG : (int64_t)(it + 2) * kGroupsPerTile;
 #pragma unroll
-        for (int h = 0; h < kGroupsPerTile; ++h) {
-          szn[h][0] = __ldg(szp + (grp + h) * 16);
-          szn[h][1] = __ldg(szp + (grp + h) * 16 + 8);
+          for (int h = 0; h < kGroupsPerTile; ++h) {
+            szn[h][0] = __ldg(szp + (grp + h) * 16);
+            szn[h][1] = __ldg(szp + (grp + h) * 16 + 8);
+          }
         }
       }
-      const int wc = it >> 2, ws = wc % kGmWSlots;
+      const int wc = it / kSlotTiles, ws = wc % kGmWSlots;
       GM_TRACE(0, it);
       mbar_wait(&wfull[ws], (wc / kGmWSlots) & 1);
       GM_TRACE(1, it);
-      const uint4 w4 = lds128(wring_u + ws * kGmWSlotBytes + strip * 2048 + (it & 3) * 512 + lane * 16);
-      const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
+      const uint32_t wtile = wring_u + ws * kGmWSlotBytes + strip * (kSlotTiles * kTileB) + (it % kSlotTiles) * kTileB + lane * 16;
       uint32_t r[16];
+      if constexpr (kI8) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {  // word j: row g + 8 (j & 1), k half j >> 1
-        const int half = j >> 1, hrow = j & 1;
-        const int h = kGroupsPerTile > 1 ? half * (kGroupsPerTile / 2) : 0;
-        uint32_t o[4];
-        dequant_word(w[j], s2[h][hrow], z2[h][hrow], o);
+        for (int half = 0; half < 2; ++half) {  // lane chunk of a half: words (row g, k 0-3), (g+8, k 0-3), (g, k 4-7), (g+8, k 4-7)
+          const uint4 w4 = lds128(wtile + half * 512);
+          const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) r[2 * (4 * half + i) + hrow] = o[i];
+          for (int j = 0; j < 4; ++j) {
+            const int hrow = j & 1, i0 = 2 * (j >> 1);
+            u8x4_to_bf16x2x2(w[j], r[2 * (4 * half + i0) + hrow], r[2 * (4 * half + i0 + 1) + hrow]);
+          }
+        }
+      } else {
+        const uint4 w4 = lds128(wtile);
+        const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {  // word j: row g + 8 (j & 1), k half j >> 1
+          const int half = j >> 1, hrow = j & 1;
+          const int h = kGroupsPerTile > 1 ? half * (kGroupsPerTile / 2) : 0;
+          uint32_t o[4];
+          dequant_word(w[j], s2[h][hrow], z2[h][hrow], o);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) r[2 * (4 * half + i) + hrow] = o[i];
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&wempty[ws]);  // the words are in registers
@@ -313,14 +336,15 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
       // ---- TMA producer, weights (this warp has nothing else to do until the accumulator is final): slice wc = k-tiles
       // 4 wc .. 4 wc + 3 of the row block, 8 copies of 2 KB, into ring slot wc % kGmWSlots as soon as the dequant
       // warps have released it.  Kept off the activation producer: a bulk copy costs its issuing warp ~130 clocks.
-      const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), 0, KT) * 512;
-      for (int wc = 0; wc * 4 < KT; ++wc) {
-        const int ws = wc % kGmWSlots, t0 = wc * 4;
+      const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), 0, KT) * kTileB;
+      for (int wc = 0; wc * kSlotTiles < KT; ++wc) {
+        const int ws = wc % kGmWSlots, t0 = wc * kSlotTiles;
         if (wc >= kGmWSlots) mbar_wait(&wempty[ws], ((wc / kGmWSlots) - 1) & 1);
-        const uint32_t tiles = (uint32_t)(KT - t0 < 4 ? KT - t0 : 4);
-        if (lane == 0) mbar_arrive_expect_tx(&wfull[ws], 8 * 512 * tiles);
+        const uint32_t tiles = (uint32_t)(KT - t0 < kSlotTiles ? KT - t0 : kSlotTiles);
+        if (lane == 0) mbar_arrive_expect_tx(&wfull[ws], 8 * kTileB * tiles);
         __syncwarp();
-        if (lane < 8) bulk_g2s(wring + ws * kGmWSlotBytes + lane * 2048, wsrc + (int64_t)t0 * 512, 512 * tiles, &wfull[ws]);
+        if (lane < 8)
+          bulk_g2s(wring + ws * kGmWSlotBytes + lane * (kSlotTiles * kTileB), wsrc + (int64_t)t0 * kTileB, kTileB * tiles, &wfull[ws]);
         __syncwarp();
       }
     }
@@ -333,6 +357,11 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     constexpr uint32_t kPitch = 128 * 2 + 16;
     const uint32_t tile_u = wring_u;
     const int nl = 32 * warp + lane;
+    float sc8 = 1.f;
+    if constexpr (kI8) {
+      const int64_t n = (int64_t)nb * 128 + nl;
+      sc8 = n < p.N_out ? __bfloat162float(p.scale8[n]) : 0.f;
+    }
 #pragma unroll 1
     for (int cc = 0; cc < NT / 32; ++cc) {
       uint32_t d[32];
@@ -340,7 +369,9 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const unsigned short b = __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(d[j])));
+        // int8: mm result rounded to bf16, THEN multiplied by the row scale and rounded again (plain_layout.py:256-262)
+        const unsigned short b = kI8 ? __bfloat16_as_ushort(__float2bfloat16_rn(bf16r(__uint_as_float(d[j])) * sc8))
+                                     : __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(d[j])));
         asm volatile("st.shared.u16 [%0], %1;" ::"r"(tile_u + (uint32_t)(32 * cc + j) * kPitch + nl * 2), "h"(b) : "memory");
       }
     }
@@ -435,16 +466,19 @@ static int launch_gemm_tc(GemmTcParams& p, int64_t Np, cudaStream_t s) {
   return cudaLaunchKernelEx(&cfg, kern, p) == cudaSuccess ? AO_B200_OK : AO_B200_ERR_CUDA;
 }
 
-// x [M][ldx] bf16 (first Kx columns valid), y [M][ldy] bf16; workspace: >= int4_gemm_tc_workspace_bytes(M, Np, Kp)
-int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np, int64_t Kp,
-                 int G, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s) {
+// x [M][ldx] bf16 (first Kx columns valid), y [M][ldy] bf16; workspace: >= int4_gemm_tc_workspace_bytes(M, Np, Kp).
+// G == 0: int8 weights (`sz` is then the bf16 per-row scale)
+static int gemm_tc_any(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+                       int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes,
+                       cudaStream_t s) {
   const int64_t need = int4_gemm_tc_workspace_bytes(M, Np, Kp);
   if (need == 0 || Np / 128 > 2147483647 || M > ((int64_t)1 << 24)) return AO_B200_ERR_UNSUPPORTED;
   if (workspace == nullptr || workspace_bytes < need || !ao_aligned(workspace, 16)) return AO_B200_ERR_WORKSPACE;
   const int NT = gm_tile_rows(M);
   GemmTcParams p{};
   p.packed = static_cast<const uint8_t*>(packed);
-  p.sz = static_cast<const uint32_t*>(sz);
+  p.sz = G ? static_cast<const uint32_t*>(sz) : nullptr;
+  p.scale8 = G ? nullptr : static_cast<const __nv_bfloat16*>(sz);
   p.xt = static_cast<const __nv_bfloat16*>(workspace);
   p.y = static_cast<__nv_bfloat16*>(y);
   p.M = (int)M;
@@ -465,6 +499,7 @@ int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* 
     default: return launch_gemm_tc<GG, 256>(p, Np, s);                   \
   }
   switch (G) {
+    case 0: AO_GM(0)
     case 32: AO_GM(32)
     case 64: AO_GM(64)
     case 128: AO_GM(128)
@@ -472,6 +507,18 @@ int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* 
   }
 #undef AO_GM
   return AO_B200_ERR_UNSUPPORTED;
+}
+
+int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np, int64_t Kp,
+                 int G, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s) {
+  if (!(G == 32 || G == 64 || G == 128 || G == 256)) return AO_B200_ERR_UNSUPPORTED;
+  return gemm_tc_any(x, M, Kx, ldx, packed, sz, Np, Kp, G, y, N_out, ldy, workspace, workspace_bytes, s);
+}
+
+// int8 weight-only prefill GEMM: packed = strip-major biased int8 (Np % 128 == 0), scale bf16 [N_out]
+int int8_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Np,
+                 int64_t Kp, void* y, int64_t N_out, int64_t ldy, void* workspace, int64_t workspace_bytes, cudaStream_t s) {
+  return gemm_tc_any(x, M, Kx, ldx, packed, scale, Np, Kp, 0, y, N_out, ldy, workspace, workspace_bytes, s);
 }
 
 }  // namespace ao

@@ -1,5 +1,5 @@
-// int8 weight-only: symmetric per-row quantize (bit-exact with the reference's eager bf16 ops)
-// and the decode GEMV  y = bf16( bf16(x @ q^T) * scale ).
+// int8 weight-only: symmetric per-row quantize (bit-exact with the reference's eager bf16 ops), the strip-major
+// pack / unpack, and the fallback decode GEMV  y = bf16( bf16(x @ q^T) * scale ).
 #include "common.cuh"
 
 namespace ao {
@@ -83,37 +83,76 @@ __global__ void __launch_bounds__(256) int8_quantize_kernel(const __nv_bfloat16*
 }
 
 // ---------------------------------------------------------------------------------------
-// GEMV (M <= 16).  q is plain row-major int8 [N][K] (PlainAQTTensorImpl.int_data, kept
-// bit-identical to the reference's tensor).  A CTA owns 16 rows; warps split K; lane (g,c)
-// reads 16 bytes of row g and of row g+8 per 64-wide k step and converts int8 -> bf16 exactly
-// (xor 0x80, byte-insert into the fp32 1.5*2^23 magic, subtract, pack pairs to bf16x2).
+// strip-major int8 layout (include/ao_b200.h): uint8 [Np/16][Kp/64][2 halves][32 lanes][16 B], BIASED (u = q + 128).
+// Lane l = (g = l >> 2, c = l & 3) of half h owns 4 words; word j holds row 16 s + g + 8 (j & 1),
+// k0 = 64 kt + 32 h + 8 c + 4 (j >> 1), bytes k0 .. k0 + 3.  One thread per 16-byte chunk.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) int8_pack_kernel(const int8_t* __restrict__ q, int64_t N, int64_t K, int64_t Np,
+                                                        int64_t Kp, uint4* __restrict__ packed) {
+  const int64_t KT = Kp / 64, total = (Np / 16) * KT * 64;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int lane = (int)(idx & 31), h = (int)((idx >> 5) & 1);
+    const int64_t tile = idx >> 6, s = tile / KT, kt = tile - s * KT;
+    const int g = lane >> 2, c = lane & 3;
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t row = 16 * s + g + 8 * (j & 1), k0 = 64 * kt + 32 * h + 8 * c + 4 * (j >> 1);
+      uint32_t v = 0x80808080u;  // q = 0
+      if (row < N) {
+        if (k0 + 4 <= K && (K & 3) == 0) {
+          v = *reinterpret_cast<const uint32_t*>(q + row * K + k0) ^ 0x80808080u;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (k0 + e < K) v = (v & ~(0xFFu << (8 * e))) | ((((uint32_t)(uint8_t)q[row * K + k0 + e]) ^ 0x80u) << (8 * e));
+        }
+      }
+      w[j] = v;
+    }
+    packed[idx] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) int8_unpack_kernel(const uint4* __restrict__ packed, int64_t Np, int64_t Kp, int64_t N,
+                                                          int64_t K, int8_t* __restrict__ q) {
+  const int64_t KT = Kp / 64, total = (Np / 16) * KT * 64;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int lane = (int)(idx & 31), h = (int)((idx >> 5) & 1);
+    const int64_t tile = idx >> 6, s = tile / KT, kt = tile - s * KT;
+    const int g = lane >> 2, c = lane & 3;
+    const uint4 v = packed[idx];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t row = 16 * s + g + 8 * (j & 1), k0 = 64 * kt + 32 * h + 8 * c + 4 * (j >> 1);
+      if (row >= N) continue;
+      const uint32_t t = w[j] ^ 0x80808080u;
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (k0 + e < K) q[row * K + k0 + e] = (int8_t)((t >> (8 * e)) & 0xFFu);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Fallback GEMV (M <= 16) for shapes whose activations do not fit the fused kernel's shared-memory staging
+// (gemv_int8_fused.cu).  A CTA owns a strip; warps split the k-tiles; a lane's 16-byte chunk is rows g / g + 8 of a
+// 32-k half, converted exactly to bf16 (byte-insert into the fp32 1.5 * 2^23 magic, subtract, pack pairs).
 // ---------------------------------------------------------------------------------------
 constexpr int kI8Warps = 8;
 
-// 4 int8 (one register) -> 2 bf16x2 registers: (b0,b1), (b2,b3)
-__device__ __forceinline__ void i8x4_to_bf16x2x2(uint32_t v, uint32_t& o01, uint32_t& o23) {
-  const uint32_t u = v ^ 0x80808080u;  // b + 128 in 0..255
-  constexpr uint32_t kMagic = 0x4B400000u;         // 1.5 * 2^23
-  constexpr float kBias = 12582912.0f + 128.0f;
-  const float f0 = __uint_as_float(__byte_perm(u, kMagic, 0x7650)) - kBias;
-  const float f1 = __uint_as_float(__byte_perm(u, kMagic, 0x7651)) - kBias;
-  const float f2 = __uint_as_float(__byte_perm(u, kMagic, 0x7652)) - kBias;
-  const float f3 = __uint_as_float(__byte_perm(u, kMagic, 0x7653)) - kBias;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o01) : "f"(f1), "f"(f0));
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o23) : "f"(f3), "f"(f2));
-}
-
 template <int MT>
-__global__ void __launch_bounds__(kI8Warps * 32) int8_gemv_kernel(const int8_t* __restrict__ q,
+__global__ void __launch_bounds__(kI8Warps * 32) int8_gemv_kernel(const uint8_t* __restrict__ packed,
                                                                   const __nv_bfloat16* __restrict__ scale,
                                                                   const __nv_bfloat16* __restrict__ x,
-                                                                  __nv_bfloat16* __restrict__ y, int M, int64_t N,
-                                                                  int64_t K, int64_t ldx, int64_t ldy) {
+                                                                  __nv_bfloat16* __restrict__ y, int M, int64_t N_out,
+                                                                  int64_t Kx, int KT, int64_t ldx, int64_t ldy) {
   __shared__ float red[kI8Warps][MT][32][4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, c = lane & 3;
-  const int64_t strips = (N + 15) / 16;
-  const int64_t k_steps = (K + 63) / 64;  // K % 16 == 0 checked by the host; tail chunks predicated
+  const int64_t strips = (N_out + 15) / 16;
+  const int n_half = 2 * KT;  // 32-k halves of a strip, 512 bytes each
 
   for (int64_t strip = blockIdx.x; strip < strips; strip += gridDim.x) {
     float acc[MT][4];
@@ -121,45 +160,35 @@ __global__ void __launch_bounds__(kI8Warps * 32) int8_gemv_kernel(const int8_t* 
     for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[mt][i] = 0.f;
-    const int64_t r0 = strip * 16 + g, r1 = r0 + 8;
-    const bool v0 = r0 < N, v1 = r1 < N;
-    const int8_t* p0 = q + r0 * K + 16 * c;
-    const int8_t* p1 = q + r1 * K + 16 * c;
+    const uint8_t* wp = packed + strip * (int64_t)KT * 1024 + lane * 16;
 
     constexpr int U = 4;
-    for (int64_t ks0 = warp * U; ks0 < k_steps; ks0 += kI8Warps * U) {
-      uint4 a0[U], a1[U];
-      uint4 xv[U][MT][2];
+    for (int h0 = warp * U; h0 < n_half; h0 += kI8Warps * U) {
+      uint4 a[U];
+      uint4 xv[U][MT];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const int64_t ks = ks0 + u;
-        const bool ok = ks < k_steps && ks * 64 + 16 * c < K;
-        a0[u] = (ok && v0) ? ldg128(p0 + ks * 64) : make_uint4(0, 0, 0, 0);
-        a1[u] = (ok && v1) ? ldg128(p1 + ks * 64) : make_uint4(0, 0, 0, 0);
+        const int hh = h0 + u;
+        const bool ok = hh < n_half;
+        a[u] = ok ? ldg128(wp + (int64_t)hh * 512) : make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
           const int m = g + 8 * mt;
-          const __nv_bfloat16* xp = x + m * ldx + ks * 64 + 16 * c;
-          const bool xo = ok && m < M;
-          xv[u][mt][0] = xo ? __ldg(reinterpret_cast<const uint4*>(xp)) : make_uint4(0, 0, 0, 0);
-          xv[u][mt][1] = xo ? __ldg(reinterpret_cast<const uint4*>(xp) + 1) : make_uint4(0, 0, 0, 0);
+          const int64_t k0 = (int64_t)hh * 32 + 8 * c;
+          xv[u][mt] = (ok && m < M && k0 < Kx) ? __ldg(reinterpret_cast<const uint4*>(x + m * ldx + k0)) : make_uint4(0, 0, 0, 0);
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const uint32_t w0[4] = {a0[u].x, a0[u].y, a0[u].z, a0[u].w};
-        const uint32_t w1[4] = {a1[u].x, a1[u].y, a1[u].z, a1[u].w};
+        uint32_t g01, g23, h01, h23, g45, g67, h45, h67;
+        u8x4_to_bf16x2x2(a[u].x, g01, g23);  // row g,     k 8c .. 8c+3
+        u8x4_to_bf16x2x2(a[u].y, h01, h23);  // row g + 8
+        u8x4_to_bf16x2x2(a[u].z, g45, g67);  // row g,     k 8c+4 .. 8c+7
+        u8x4_to_bf16x2x2(a[u].w, h45, h67);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {  // 4 k's per register -> one MMA (k-slots {2c,2c+1},{2c+8,2c+9})
-          uint32_t lo01, lo23, hi01, hi23;
-          i8x4_to_bf16x2x2(w0[i], lo01, lo23);
-          i8x4_to_bf16x2x2(w1[i], hi01, hi23);
-#pragma unroll
-          for (int mt = 0; mt < MT; ++mt) {
-            const uint4 xa = xv[u][mt][i >> 1];
-            const uint32_t b0 = (i & 1) ? xa.z : xa.x, b1 = (i & 1) ? xa.w : xa.y;
-            mma_bf16_16816(acc[mt], lo01, hi01, lo23, hi23, b0, b1);
-          }
+        for (int mt = 0; mt < MT; ++mt) {
+          mma_bf16_16816(acc[mt], g01, h01, g23, h23, xv[u][mt].x, xv[u][mt].y);
+          mma_bf16_16816(acc[mt], g45, h45, g67, h67, xv[u][mt].z, xv[u][mt].w);
         }
       }
     }
@@ -175,6 +204,8 @@ __global__ void __launch_bounds__(kI8Warps * 32) int8_gemv_kernel(const int8_t* 
         const float4 v = *reinterpret_cast<const float4*>(&red[w][mt][lane][0]);
         s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
+      const int64_t r0 = strip * 16 + g, r1 = r0 + 8;
+      const bool v0 = r0 < N_out, v1 = r1 < N_out;
       const int m0 = 2 * c + 8 * mt;
       const float sc0 = v0 ? __bfloat162float(scale[r0]) : 0.f;
       const float sc1 = v1 ? __bfloat162float(scale[r1]) : 0.f;
@@ -192,21 +223,42 @@ __global__ void __launch_bounds__(kI8Warps * 32) int8_gemv_kernel(const int8_t* 
   }
 }
 
-int int8_gemv(const void* x, int64_t M, int64_t K, int64_t ldx, const int8_t* q, const void* scale, int64_t N,
-              void* y, int64_t ldy, cudaStream_t s) {
-  const int64_t strips = (N + 15) / 16;
+int int8_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* scale, int64_t Kp,
+              void* y, int64_t N_out, int64_t ldy, cudaStream_t s) {
+  const int64_t strips = (N_out + 15) / 16;
   const int grid = static_cast<int>(strips < (int64_t)kNumSMs * 8 ? strips : (int64_t)kNumSMs * 8);
   auto xp = static_cast<const __nv_bfloat16*>(x);
   auto yp = static_cast<__nv_bfloat16*>(y);
   auto sp = static_cast<const __nv_bfloat16*>(scale);
+  auto wp = static_cast<const uint8_t*>(packed);
   if (M <= 8)
-    int8_gemv_kernel<1><<<grid, kI8Warps * 32, 0, s>>>(q, sp, xp, yp, (int)M, N, K, ldx, ldy);
+    int8_gemv_kernel<1><<<grid, kI8Warps * 32, 0, s>>>(wp, sp, xp, yp, (int)M, N_out, Kx, (int)(Kp / 64), ldx, ldy);
   else
-    int8_gemv_kernel<2><<<grid, kI8Warps * 32, 0, s>>>(q, sp, xp, yp, (int)M, N, K, ldx, ldy);
+    int8_gemv_kernel<2><<<grid, kI8Warps * 32, 0, s>>>(wp, sp, xp, yp, (int)M, N_out, Kx, (int)(Kp / 64), ldx, ldy);
   return ao_launch_status();
 }
 
 }  // namespace ao
+
+extern "C" int ao_b200_int8_pack(const int8_t* q, int64_t N, int64_t K, int64_t Np, int64_t Kp, void* packed, void* stream) {
+  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 16 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(ao_aligned(packed, 16) && ((K & 3) != 0 || ao_aligned(q, 4)));
+  const int64_t total = (Np / 16) * (Kp / 64) * 64;
+  const int64_t blocks = (total + 255) / 256;
+  ao::int8_pack_kernel<<<(unsigned)(blocks < 148 * 32 ? blocks : 148 * 32), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      q, N, K, Np, Kp, static_cast<uint4*>(packed));
+  return ao_launch_status();
+}
+
+extern "C" int ao_b200_int8_unpack(const void* packed, int64_t Np, int64_t Kp, int64_t N, int64_t K, int8_t* q, void* stream) {
+  AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 16 == 0 && Kp % 64 == 0);
+  AO_CHECK_ARG(ao_aligned(packed, 16));
+  const int64_t total = (Np / 16) * (Kp / 64) * 64;
+  const int64_t blocks = (total + 255) / 256;
+  ao::int8_unpack_kernel<<<(unsigned)(blocks < 148 * 32 ? blocks : 148 * 32), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(packed), Np, Kp, N, K, q);
+  return ao_launch_status();
+}
 
 extern "C" int ao_b200_int8_quantize(const void* w, int64_t N, int64_t K, int64_t ldw, float eps, int div_mode,
                                      int8_t* q, void* scale, void* stream) {

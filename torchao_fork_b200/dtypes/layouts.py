@@ -236,41 +236,51 @@ register_aqt_quantized_linear_dispatch(_linear_bf16_act_uint4_weight_check, _lin
 # ---------------------------------------------------------------------------------------- int8
 @register_layout(PlainLayout)
 class PlainAQTTensorImpl(AQTTensorImpl):
-    """int8 storage: int_data int8 (N, K) row-major, scale bf16 (N,), zero_point int64 (N,) == 0.
-    reference: plain_layout.py:47-229."""
+    """int8 storage.  The reference keeps int_data int8 (N, K) row-major (plain_layout.py:47-229); here the bytes live in
+    the strip-major biased layout (include/ao_b200.h: `packed` uint8 (Np/16, Kp/64, 1024)) that the TMA-ring GEMV and
+    the tcgen05 GEMM stream, and `int_data` is recovered exactly (unpack kernel) whenever it is asked for.
+    scale bf16 (N,), zero_point int64 (N,) == 0."""
 
-    def __new__(cls, int_data, scale, zero_point, _layout, transposed=False):
-        shape = int_data.shape[::-1] if transposed else int_data.shape
-        return _wrapper(cls, int_data, shape)
+    def __new__(cls, packed, scale, zero_point, _layout, shape, transposed=False):
+        n, k = shape
+        return torch.Tensor._make_wrapper_subclass(cls, (k, n) if transposed else (n, k), device=packed.device,
+                                                   dtype=torch.int8, layout=packed.layout, requires_grad=False)
 
-    def __init__(self, int_data, scale, zero_point, _layout, transposed=False):
-        self.int_data = int_data
+    def __init__(self, packed, scale, zero_point, _layout, shape, transposed=False):
+        self.packed = packed
         self.scale = scale
         self.zero_point = zero_point
         self._layout = _layout
+        self._nk = (int(shape[0]), int(shape[1]))
         self.transposed = transposed
 
     def __tensor_flatten__(self):
-        names = ["int_data", "scale"] + (["zero_point"] if self.zero_point is not None else [])
-        return names, [self._layout, self.transposed]
+        names = ["packed", "scale"] + (["zero_point"] if self.zero_point is not None else [])
+        return names, [self._layout, self._nk, self.transposed]
 
     @classmethod
     def __tensor_unflatten__(cls, tensor_data_dict, tensor_attributes, outer_size, outer_stride):
-        _layout, transposed = tensor_attributes
-        return cls(tensor_data_dict["int_data"], tensor_data_dict["scale"], tensor_data_dict.get("zero_point"),
-                   _layout, transposed)
+        _layout, nk, transposed = tensor_attributes
+        return cls(tensor_data_dict["packed"], tensor_data_dict["scale"], tensor_data_dict.get("zero_point"),
+                   _layout, nk, transposed)
 
     @classmethod
     def from_hp(cls, weight, eps, zero_point_dtype, _layout):
-        """bf16 (N, K) -> int8 data + scale in ONE kernel."""
+        """bf16 (N, K) -> int8 data + scale in ONE kernel, then the strip-major pack."""
         q, scale = torch.ops.torchao.b200_int8_quantize(weight, eps, _qp.CUDA_DIV_SEMANTICS)
         zp = torch.zeros(scale.shape, dtype=zero_point_dtype, device=weight.device)
-        return cls(q, scale, zp, _layout)
+        return cls(torch.ops.torchao.b200_int8_pack(q), scale, zp, _layout, q.shape)
 
     @classmethod
     def from_plain(cls, int_data, scale, zero_point, _layout):
         assert isinstance(_layout, PlainLayout)
-        return cls(int_data, scale, zero_point, _layout)
+        assert int_data.dtype == torch.int8 and int_data.dim() == 2, "int_data must be 2-D int8"
+        return cls(torch.ops.torchao.b200_int8_pack(int_data), scale, zero_point, _layout, int_data.shape)
+
+    @property
+    def int_data(self):
+        """the reference's field: int8 (N, K) row-major (materialised by the unpack kernel, bit-exact)."""
+        return torch.ops.torchao.b200_int8_unpack(self.packed, self._nk[0], self._nk[1])
 
     def get_plain(self):
         return self.int_data, self.scale, self.zero_point
@@ -279,8 +289,8 @@ class PlainAQTTensorImpl(AQTTensorImpl):
         return self._layout
 
     def _apply_fn_to_data(self, fn):
-        return self.__class__(fn(self.int_data), fn(self.scale), fn(self.zero_point) if self.zero_point is not None else None,
-                              self._layout, self.transposed)
+        return self.__class__(fn(self.packed), fn(self.scale), fn(self.zero_point) if self.zero_point is not None else None,
+                              self._layout, self._nk, self.transposed)
 
     def to(self, *args, **kwargs):
         device, _, _, _ = torch._C._nn._parse_to(*args, **kwargs)
@@ -288,13 +298,12 @@ class PlainAQTTensorImpl(AQTTensorImpl):
         return self._apply_fn_to_data(lambda t: t.to(device))
 
     def t(self):
-        return self.__class__(self.int_data, self.scale, self.zero_point, self._layout, not self.transposed)
+        return self.__class__(self.packed, self.scale, self.zero_point, self._layout, self._nk, not self.transposed)
 
     def copy_(self, src):
-        if not (isinstance(src, PlainAQTTensorImpl) and self.int_data.shape == src.int_data.shape
-                and self.transposed == src.transposed):
+        if not (isinstance(src, PlainAQTTensorImpl) and self._nk == src._nk and self.transposed == src.transposed):
             raise ValueError(f"Not supported args for copy_ due to metadata mistach: {self, src}")
-        self.int_data.copy_(src.int_data)
+        self.packed.copy_(src.packed)
         self.scale.copy_(src.scale)
         if self.zero_point is not None and src.zero_point is not None:
             self.zero_point.copy_(src.zero_point)
@@ -313,7 +322,8 @@ class PlainAQTTensorImpl(AQTTensorImpl):
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
         if func is aten.slice.Tensor:
-            # reference: plain_layout.py:160-200 — rows slice data + qparams, columns slice data only
+            # reference: plain_layout.py:160-200 — rows slice data + qparams, columns slice data only.  Done on the plain
+            # view (unpack -> slice -> pack): slicing happens at load / shard time, not on the hot path.
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])
             assert step == 1 and dim in (0, 1) and not self.transposed
             data = aten.slice.Tensor(self.int_data, dim, start, end, 1).contiguous()
@@ -322,7 +332,8 @@ class PlainAQTTensorImpl(AQTTensorImpl):
                 zp = aten.slice.Tensor(self.zero_point, 0, start, end, 1) if self.zero_point is not None else None
             else:
                 scale, zp = self.scale, self.zero_point
-            return return_and_correct_aliasing(func, args, kwargs, self.__class__(data, scale, zp, self._layout))
+            new = self.__class__(torch.ops.torchao.b200_int8_pack(data), scale, zp, self._layout, data.shape)
+            return return_and_correct_aliasing(func, args, kwargs, new)
         raise NotImplementedError(f"PlainAQTTensorImpl dispatch: attempting to run {func}, this is not supported")
 
 
@@ -353,7 +364,7 @@ def _linear_fp_act_int8_weight_impl(input_tensor, weight_tensor, bias):
         raise NotImplementedError("B200 int8 weight-only linear takes bfloat16 activations")
     impl = weight_tensor.tensor_impl
     x2d = input_tensor.reshape(-1, input_tensor.shape[-1])
-    y = torch.ops.torchao.b200_int8_weight_only_mm(x2d, impl.int_data, impl.scale)
+    y = torch.ops.torchao.b200_int8_weight_only_mm(x2d, impl.packed, impl.scale)
     y = y.reshape(*input_tensor.shape[:-1], y.shape[-1])
     if bias is not None:
         y += bias.to(y.dtype)

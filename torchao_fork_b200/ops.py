@@ -29,7 +29,11 @@ _SCHEMAS = {
     "b200_tinygemm_pack": "(Tensor int_data, int inner_k_tiles) -> Tensor",
     "b200_int4_weight_only_mm": "(Tensor x, Tensor packed_w, int group_size, Tensor scales_and_zeros, int out_features) -> Tensor",
     "b200_int8_quantize": "(Tensor w, float eps, bool cuda_div_semantics) -> (Tensor, Tensor)",
-    "b200_int8_weight_only_mm": "(Tensor x, Tensor int_data, Tensor scale) -> Tensor",
+    "b200_int8_pack": "(Tensor int_data) -> Tensor",
+    "b200_int8_unpack": "(Tensor packed_w, int out_features, int in_features) -> Tensor",
+    "b200_int8_weight_only_mm": "(Tensor x, Tensor packed_w, Tensor scale) -> Tensor",
+    "b200_int8_gemv_fused": "(Tensor x, Tensor packed_w, Tensor scale, Tensor? norm_weight, float norm_eps, "
+                            "Tensor? residual, int epilogue) -> Tensor",
 }
 
 
@@ -376,10 +380,12 @@ def _(x: Tensor, packed_w: Tensor, group_size: int, scales_and_zeros: Tensor, ou
 _WORKSPACES = {}
 
 
-def _workspace(device, nbytes):
+def _workspace(device, nbytes, tag="int4"):
+    """Per (device, stream, tag) scratch.  The int4 buffer carries the tensor-memory GEMV's tickets (must stay zero), so
+    the int8 GEMM's staging copy lives in its own buffer."""
     if nbytes == 0:
         return None
-    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    key = (device, torch.cuda.current_stream(device).cuda_stream, tag)
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
@@ -435,31 +441,136 @@ def _int8_quantize_cuda(w: Tensor, eps: float, cuda_div_semantics: bool):
     return q, scale
 
 
+def padded_int8_shape(n: int, k: int) -> Tuple[int, int]:
+    """strip-major int8 layout: N -> x128 (row blocks of the prefill GEMM), K -> x64 (k-tiles)."""
+    return _round_up(n, 128), _round_up(k, 64)
+
+
+def _int8_packed_checks(packed_w):
+    torch._check(packed_w.is_cuda and packed_w.dtype is torch.uint8 and packed_w.dim() == 3 and packed_w.size(2) == 1024
+                 and packed_w.is_contiguous(),
+                 lambda: "packed int8 weight must be a contiguous CUDA uint8 tensor (Np/16, Kp/64, 1024)")
+    return packed_w.size(0) * 16, packed_w.size(1) * 64
+
+
+@register_custom_op("torchao::b200_int8_pack")
+def _(int_data: Tensor):
+    np_, kp = padded_int8_shape(int_data.size(0), int_data.size(1))
+    return torch.empty((np_ // 16, kp // 64, 1024), dtype=torch.uint8, device=int_data.device)
+
+
+@_impl_cuda("b200_int8_pack")
+def _int8_pack_cuda(int_data: Tensor):
+    """PlainAQTTensorImpl.int_data int8 (N, K) -> strip-major biased int8 (include/ao_b200.h)."""
+    torch._check(int_data.is_cuda and int_data.dtype is torch.int8 and int_data.dim() == 2,
+                 lambda: "int_data must be a 2-D CUDA int8 tensor")
+    int_data = int_data.contiguous()
+    n, k = int_data.shape
+    np_, kp = padded_int8_shape(n, k)
+    packed = torch.empty((np_ // 16, kp // 64, 1024), dtype=torch.uint8, device=int_data.device)
+    with torch.cuda.device(int_data.device):
+        _lib.check(_lib.lib().ao_b200_int8_pack(int_data.data_ptr(), n, k, np_, kp, packed.data_ptr(), _stream(int_data)),
+                   "int8_pack")
+    return packed
+
+
+@register_custom_op("torchao::b200_int8_unpack")
+def _(packed_w: Tensor, out_features: int, in_features: int):
+    return torch.empty((out_features, in_features), dtype=torch.int8, device=packed_w.device)
+
+
+@_impl_cuda("b200_int8_unpack")
+def _int8_unpack_cuda(packed_w: Tensor, out_features: int, in_features: int):
+    np_, kp = _int8_packed_checks(packed_w)
+    torch._check(0 < out_features <= np_ and 0 < in_features <= kp, lambda: "out/in features exceed the packed shape")
+    q = torch.empty((out_features, in_features), dtype=torch.int8, device=packed_w.device)
+    with torch.cuda.device(packed_w.device):
+        _lib.check(_lib.lib().ao_b200_int8_unpack(packed_w.data_ptr(), np_, kp, out_features, in_features, q.data_ptr(),
+                                                  _stream(packed_w)), "int8_unpack")
+    return q
+
+
 @register_custom_op("torchao::b200_int8_weight_only_mm")
-def _(x: Tensor, int_data: Tensor, scale: Tensor):
-    return torch.empty((x.size(0), int_data.size(0)), dtype=torch.bfloat16, device=x.device)
+def _(x: Tensor, packed_w: Tensor, scale: Tensor):
+    return torch.empty((x.size(0), scale.numel()), dtype=torch.bfloat16, device=x.device)
 
 
 @_impl_cuda("b200_int8_weight_only_mm")
-def _int8_mm_cuda(x: Tensor, int_data: Tensor, scale: Tensor):
+def _int8_mm_cuda(x: Tensor, packed_w: Tensor, scale: Tensor):
     """y = (x @ int_data.T.to(bf16)) * scale with the reference's two bf16 roundings
-    (torchao/dtypes/uintx/plain_layout.py:250-266)."""
+    (torchao/dtypes/uintx/plain_layout.py:250-266); out_features = scale.numel()."""
     _check_cuda_bf16(x, "activation")
     _check_cuda_bf16(scale, "scale")
-    torch._check(int_data.dtype is torch.int8 and int_data.dim() == 2, lambda: "int_data must be 2-D int8")
-    torch._check(x.dim() == 2 and x.size(1) == int_data.size(1), lambda: "x / weight K mismatch")
-    torch._check(int_data.size(1) % 16 == 0, lambda: "int8 weight-only mm needs in_features % 16 == 0")
-    torch._check(scale.numel() == int_data.size(0), lambda: "scale must have one entry per output row")
-    int_data, scale = int_data.contiguous(), scale.contiguous()
-    m, n = x.size(0), int_data.size(0)
+    np_, kp = _int8_packed_checks(packed_w)
+    n = scale.numel()
+    torch._check(x.dim() == 2 and x.size(1) <= kp, lambda: "x / weight K mismatch")
+    torch._check(0 < n <= np_, lambda: "scale must have one entry per output row")
+    scale = scale.contiguous()
+    m = x.size(0)
     y = torch.empty((m, n), dtype=torch.bfloat16, device=x.device)
     if m == 0:
         return y
+    if x.size(1) % 8 != 0:
+        x = torch.nn.functional.pad(x, (0, (-x.size(1)) % 8))
     x, ldx = _rows(x)
+    L = _lib.lib()
+    ws_bytes = L.ao_b200_int8_mm_workspace_bytes(m, np_, kp)
+    ws = _workspace(x.device, ws_bytes, "int8")
     with torch.cuda.device(x.device):
-        _lib.check(_lib.lib().ao_b200_int8_mm(x.data_ptr(), m, x.size(1), ldx, int_data.data_ptr(), scale.data_ptr(),
-                                              n, y.data_ptr(), n, _stream(x)), "int8_mm")
+        _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, x.size(1), ldx, packed_w.data_ptr(), scale.data_ptr(), np_, kp,
+                                     y.data_ptr(), n, n, ws.data_ptr() if ws is not None else None, ws_bytes, _stream(x)),
+                   "int8_mm")
     return y
+
+
+@register_custom_op("torchao::b200_int8_gemv_fused")
+def _(x, packed_w, scale, norm_weight, norm_eps, residual, epilogue):
+    n = scale.numel() // 2 if epilogue == 2 else scale.numel()
+    return torch.empty((x.size(0), n), dtype=torch.bfloat16, device=x.device)
+
+
+@_impl_cuda("b200_int8_gemv_fused")
+def _int8_gemv_fused_cuda(x, packed_w, scale, norm_weight, norm_eps, residual, epilogue):
+    """int8 Llama-block GEMV with RMSNorm prologue / residual or SiLU*mul epilogue (include/ao_b200.h)."""
+    np_, kp = _int8_packed_checks(packed_w)
+    _check_cuda_bf16(x, "activation")
+    _check_cuda_bf16(scale, "scale")
+    out_features = scale.numel()
+    torch._check(x.dim() == 2 and 0 < x.size(0) <= 16 and x.size(1) <= kp and x.size(1) % 8 == 0,
+                 lambda: f"x must be (M<=16, K<={kp}, K%8==0), got {tuple(x.shape)}")
+    torch._check(0 < out_features <= np_, lambda: "out_features out of range")
+    torch._check(epilogue in (0, 1, 2), lambda: "epilogue must be 0 (plain), 1 (residual) or 2 (silu*mul)")
+    x, ldx = _rows(x)
+    scale = scale.contiguous()
+    m = x.size(0)
+    n = out_features // 2 if epilogue == 2 else out_features
+    y = torch.empty((m, n), dtype=torch.bfloat16, device=x.device)
+    ld_res = 0
+    if epilogue == 1:
+        torch._check(residual is not None and tuple(residual.shape) == (m, n), lambda: "residual must be (M, N)")
+        _check_cuda_bf16(residual, "residual")
+        residual = residual.contiguous()
+        ld_res = residual.stride(0)
+    if norm_weight is not None:
+        _check_cuda_bf16(norm_weight, "norm_weight")
+        torch._check(norm_weight.numel() == x.size(1), lambda: "norm_weight must have K elements")
+        norm_weight = norm_weight.contiguous()
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ao_b200_int8_gemv_fused(
+            x.data_ptr(), m, x.size(1), ldx, packed_w.data_ptr(), scale.data_ptr(), np_, kp, y.data_ptr(), out_features, n,
+            None if norm_weight is None else norm_weight.data_ptr(), norm_eps,
+            None if residual is None else residual.data_ptr(), ld_res, epilogue, _stream(x)), "int8_gemv_fused")
+    return y
+
+
+def interleave_gate_up_int8(q1: Tensor, s1: Tensor, q3: Tensor, s3: Tensor) -> Tuple[Tensor, Tensor]:
+    """w1 (gate) / w3 (up) plain int8 (I, K) + scales (I,) -> fused (2I, K) / (2I,) whose 16-row strip t holds rows
+    8t..8t+7 of w1 as rows 0..7 and rows 8t..8t+7 of w3 as rows 8..15 (the SiLU*mul epilogue's pairing)."""
+    torch._check(q1.shape == q3.shape and q1.size(0) % 8 == 0, lambda: "w1 / w3 shape mismatch")
+    i, k = q1.shape
+    q = torch.stack([q1.view(i // 8, 8, k), q3.view(i // 8, 8, k)], dim=1).reshape(2 * i, k)
+    s = torch.stack([s1.view(i // 8, 8), s3.view(i // 8, 8)], dim=1).reshape(2 * i)
+    return q.contiguous(), s.contiguous()
 
 
 # ------------------------------------------------------------------ fused decode GEMV (M <= 16)
