@@ -83,6 +83,8 @@ def test_mm_prefill_gemm(shape, m):
 @pytest.mark.parametrize("shape", [(6144, 4096), (1024, 8192), (2048, 1024)], ids=str)
 def test_rmsnorm_prologue_and_residual(shape, m):
     n, k = shape
+    if m * (2 * k + 16) > 150 * 1024:
+        pytest.skip("activations do not fit the fused kernel's staging (ao_b200_int8_mm falls back to the plain GEMV)")
     q, s, packed = _quant(n, k, 3 * n + m)
     x = (torch.randn(m, k, device=DEV) * 3).to(torch.bfloat16)
     nw = (1 + 0.1 * torch.randn(k, device=DEV)).to(torch.bfloat16)
