@@ -7,6 +7,9 @@ int int4_gemv(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* pac
 int int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
                     int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
                     const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
+int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
+                   int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
+                   const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s);
 int int4_gemv_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
                  int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps, const void* residual,
                  int64_t ld_res, int epilogue, void* workspace, int64_t workspace_bytes, bool pdl, cudaStream_t s);
@@ -39,7 +42,7 @@ extern "C" int ao_b200_abi_version(void) { return 3; }
 #include <cstdlib>
 namespace {
 struct Tunables {
-  int gemv_version, stages, pdl, gemv_tc, gemm_tc;
+  int gemv_version, stages, pdl, gemv_tc, gemm_tc, gemv_imma;
   Tunables() {
     // tcgen05 prefill GEMM for M > 16 (0: loop the decode GEMV over 16-row chunks instead — kept for A/B testing)
     const char* gm = std::getenv("AO_B200_GEMM_TC");
@@ -57,6 +60,9 @@ struct Tunables {
     // neighbours in a PDL chain: it takes the whole SM's shared and tensor memory)
     const char* tc = std::getenv("AO_B200_GEMV_TC");
     gemv_tc = tc ? std::atoi(tc) : 2;
+    // integer-MMA decode GEMV (M <= 2, G = 128; gemv_int4_imma.cu): 1 (default) wherever it applies, 0 never
+    const char* im = std::getenv("AO_B200_GEMV_IMMA");
+    gemv_imma = im ? std::atoi(im) : 1;
   }
 };
 const Tunables& tunables() {
@@ -101,6 +107,12 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
       if (e == AO_B200_OK) continue;
       if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
     }
+    if (tunables().gemv_imma && mc <= 2 && group_size == 128) {
+      e = ao::int4_gemv_imma(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out, ldy,
+                             nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
+      if (e == AO_B200_OK) continue;
+      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+    }
     if (tunables().gemv_version == 3) {
       e = ao::int4_gemv_fused(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
                               N_out, ldy, nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
@@ -135,6 +147,12 @@ extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int
     const int e = ao::int4_gemv_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
                                    norm_eps, residual, ld_res, epilogue, workspace, workspace_bytes, tunables().pdl != 0,
                                    static_cast<cudaStream_t>(stream));
+    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+  }
+  if (tunables().gemv_imma && M <= 2 && group_size == 128) {
+    const int e = ao::int4_gemv_imma(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
+                                     norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,
+                                     static_cast<cudaStream_t>(stream));
     if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
   }
   return ao::int4_gemv_fused(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
