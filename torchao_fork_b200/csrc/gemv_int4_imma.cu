@@ -37,7 +37,7 @@ struct GemvIParams {
   const __nv_bfloat16* norm_w;
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;
-  int M, stages, epilogue;
+  int M, stages, epilogue, hold;
   int KT;                         // Kp / 64 (even: Kp % 128 == 0)
   int64_t Kx, ldx, N_out, ldy, ld_res;
   int n_strips, strips_base, strips_rem;
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   float* red = reinterpret_cast<float*>(smem_i + p.off_red);   // [2][16 warps][32][4]
   float* part = reinterpret_cast<float*>(smem_i + p.off_misc); // [2 rows][16 warps][2 = {sum sq, amax}]
   float* row_scale = part + 2 * kIConsumers * 2;               // [2]: 2^-e (* rsqrt(mean sq + eps))
-  float* row_up = row_scale + 2;                               // [2]: 2^e
+  float* row_up = row_scale + 2;                               // (spare)
   uint64_t* full = reinterpret_cast<uint64_t*>(row_up + 2);
   uint64_t* empty = full + p.stages;
   uint64_t* red_full = empty + p.stages;
@@ -199,27 +199,64 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   const int g = lane >> 2, c = lane & 3;
   const int tid = threadIdx.x;  // 0 .. 511
   constexpr int kCT = kIConsumers * 32;
+  constexpr int kHold = 4;            // chunks a thread keeps in registers between the two staging passes
+  const int chunks_per_row = KT * 8;  // 8-element chunks over Kp
+  const int n_iter = (chunks_per_row + kCT - 1) / kCT;
+  // Fast path (M = 1, Kp <= 16384): every thread owns <= 4 chunks; all of their loads are issued at once and the
+  // normalised bf16 values stay in registers between the two passes.  The norm weights do not depend on the previous
+  // kernel, so they are fetched BEFORE the dependency wait (they are a DRAM miss: read once per token).
+  const bool hold = p.hold != 0 && p.M == 1 && n_iter <= kHold;
+  uint4 xr[kHold], wn4[kHold];
+#pragma unroll
+  for (int i = 0; i < kHold; ++i) xr[i] = wn4[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (hold && p.norm_w != nullptr) {
+#pragma unroll
+    for (int i = 0; i < kHold; ++i) {
+      const int ci = i * kCT + tid;
+      if ((int64_t)ci * 8 < p.Kx) wn4[i] = __ldg(reinterpret_cast<const uint4*>(p.norm_w + (int64_t)ci * 8));
+    }
+  }
   grid_dependency_wait();
 
-  // ---- stage the activations.  Pass 1: sum of squares and max magnitude of x (* norm_w).  Pass 2 (x re-read: it is
-  //      L1 / L2 resident and nothing writes it while this kernel runs): fixed point, limbs, per-group limb sums. ----
-  const int chunks_per_row = KT * 8;  // 8-element chunks over Kp
+  // ---- stage the activations.  Pass 1: sum of squares and max magnitude of x (* norm_w).  Pass 2: fixed point,
+  //      limbs, per-group limb sums (general path: x re-read — it is L1 / L2 resident and nothing writes it while this
+  //      kernel runs). ----
+  auto load_norm = [&](int m, int64_t k0, float (&f)[8], float& ss) {
+    unpack8(*reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0), f);
+    if (p.norm_w != nullptr) {
+      float wn[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        ss = fmaf(f[e], f[e], ss);
+        f[e] = bf16r(f[e] * wn[e]);
+      }
+    }
+  };
   {
-    for (int m = 0; m < p.M; ++m) {
+    if (hold) {
       float ss = 0.f, amax = 0.f;
-      for (int ci = tid; ci < chunks_per_row; ci += kCT) {
-        const int64_t k0 = (int64_t)ci * 8;
-        if (k0 >= p.Kx) continue;
+#pragma unroll
+      for (int i = 0; i < kHold; ++i) {
+        const int ci = i * kCT + tid;
+        if ((int64_t)ci * 8 < p.Kx) xr[i] = *reinterpret_cast<const uint4*>(p.x + (int64_t)ci * 8);
+      }
+#pragma unroll
+      for (int i = 0; i < kHold; ++i) {
         float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0), f);
+        unpack8(xr[i], f);
         if (p.norm_w != nullptr) {
           float wn[8];
-          unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
+          unpack8(wn4[i], wn);
+          uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             ss = fmaf(f[e], f[e], ss);
             f[e] = bf16r(f[e] * wn[e]);
           }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
+          xr[i] = make_uint4(o[0], o[1], o[2], o[3]);
         }
 #pragma unroll
         for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
@@ -227,87 +264,118 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
       ss = warp_sum_i(ss);
       amax = warp_max_i(amax);
       if (lane == 0) {
-        part[(m * kIConsumers + warp) * 2] = ss;
-        part[(m * kIConsumers + warp) * 2 + 1] = amax;
+        part[warp * 2] = ss;
+        part[warp * 2 + 1] = amax;
+      }
+    } else {
+      for (int m = 0; m < p.M; ++m) {
+        float ss = 0.f, amax = 0.f;
+        for (int ci = tid; ci < chunks_per_row; ci += kCT) {
+          const int64_t k0 = (int64_t)ci * 8;
+          if (k0 >= p.Kx) continue;
+          float f[8];
+          load_norm(m, k0, f, ss);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
+        }
+        ss = warp_sum_i(ss);
+        amax = warp_max_i(amax);
+        if (lane == 0) {
+          part[(m * kIConsumers + warp) * 2] = ss;
+          part[(m * kIConsumers + warp) * 2 + 1] = amax;
+        }
       }
     }
     named_bar_sync(1, kCT);
-    if (warp < p.M) {
+    // every warp reduces the 16 partials of every row itself (no second hand-over through shared memory)
+    float up_m[2];
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
       float t = 0.f, amax = 0.f;
-      if (lane < kIConsumers) {
-        t = part[(warp * kIConsumers + lane) * 2];
-        amax = part[(warp * kIConsumers + lane) * 2 + 1];
+      if (m < p.M && lane < kIConsumers) {
+        t = part[(m * kIConsumers + lane) * 2];
+        amax = part[(m * kIConsumers + lane) * 2 + 1];
       }
       t = warp_sum_i(t);
       amax = warp_max_i(amax);
-      if (lane == 0) {
-        // 2^e brings the row's largest magnitude into [2^21, 2^22): |round(x 2^e)| <= 2^22 fits three balanced int8 limbs
-        int e = 0;
-        if (amax > 0.f) e = 21 - ((int)((__float_as_uint(amax) >> 23) & 0xFF) - 127);
-        e = max(-100, min(100, e));
-        const float up = __uint_as_float((uint32_t)(e + 127) << 23), dn = __uint_as_float((uint32_t)(127 - e) << 23);
-        row_up[warp] = up;
-        row_scale[warp] = (p.norm_w != nullptr) ? dn * rsqrtf(t / (float)p.Kx + p.eps) : dn;
+      // 2^e brings the row's largest magnitude into [2^21, 2^22): |round(x 2^e)| <= 2^22 fits three balanced int8 limbs
+      int e = 0;
+      if (amax > 0.f) e = 21 - ((int)((__float_as_uint(amax) >> 23) & 0xFF) - 127);
+      e = max(-100, min(100, e));
+      up_m[m] = __uint_as_float((uint32_t)(e + 127) << 23);
+      if (warp == m && lane == 0 && m < p.M) {
+        const float dn = __uint_as_float((uint32_t)(127 - e) << 23);
+        row_scale[m] = (p.norm_w != nullptr) ? dn * rsqrtf(t / (float)p.Kx + p.eps) : dn;  // read by the epilogue warp (after barrier 2)
       }
     }
-    named_bar_sync(1, kCT);
-    for (int m = 0; m < p.M; ++m) {
-      const float up = row_up[m];
+    // one chunk (8 activations f[] of row m at chunk index ci) -> limbs in shared memory + group sums.  Executed by whole
+    // warps in uniform control flow (the group sums are shuffles); `valid` = the chunk exists.
+    auto emit = [&](int m, int ci, bool valid, const float (&f)[8], float up) {
       uint8_t* rows = x_s + (size_t)(3 * m) * p.limb_row_bytes;
-      for (int base = 0; base < chunks_per_row; base += kCT) {
-        const int ci = base + tid;
-        int sl0 = 0, sl1 = 0, sl2 = 0;
-        if (ci < chunks_per_row) {
+      int sl0 = 0, sl1 = 0, sl2 = 0;
+      if (valid) {
+        // Balanced limbs without per-digit carries: X + 0x808080 = sum (a_i + 128) 256^i, so its bytes xor 0x80 ARE the
+        // two's-complement limbs a_i.  x * 2^e + 1.5 * 2^23 puts X + 2^22 into the float's mantissa (|X| <= 2^22 - 1 after
+        // the clamp), one integer add turns that into X + 0x808080, byte permutes gather limb i of the 8 elements in the
+        // order of the weight bytes after the nibble split: (k0, k0+4, k0+1, k0+5 | k0+2, k0+6, k0+3, k0+7).
+        uint32_t v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float t = fminf(fmaxf(fmaf(f[e], up, kIMagicF), kIMagicF - 4194303.f), kIMagicF + 4194303.f);
+          v[e] = __float_as_uint(t) + 0x00408080u;  // low 24 bits = X + 0x808080
+        }
+        uint32_t lw[3][2];
+#pragma unroll
+        for (int l = 0; l < 3; ++l) {
+          // limb l lives in byte (2 - l) of every v: selectors pick that byte of the two sources
+          const uint32_t sel = l == 0 ? 0x0062u : (l == 1 ? 0x0051u : 0x0040u);
+          const uint32_t p04 = __byte_perm(v[0], v[4], sel), p15 = __byte_perm(v[1], v[5], sel);   // (k0, k0+4), (k0+1, k0+5)
+          const uint32_t p26 = __byte_perm(v[2], v[6], sel), p37 = __byte_perm(v[3], v[7], sel);
+          lw[l][0] = __byte_perm(p04, p15, 0x5410) ^ 0x80808080u;
+          lw[l][1] = __byte_perm(p26, p37, 0x5410) ^ 0x80808080u;
+        }
+        sl0 = __dp4a((int)lw[0][0], 0x01010101, __dp4a((int)lw[0][1], 0x01010101, 0));
+        sl1 = __dp4a((int)lw[1][0], 0x01010101, __dp4a((int)lw[1][1], 0x01010101, 0));
+        sl2 = __dp4a((int)lw[2][0], 0x01010101, __dp4a((int)lw[2][1], 0x01010101, 0));
+        *reinterpret_cast<uint2*>(rows + (size_t)ci * 8) = make_uint2(lw[0][0], lw[0][1]);
+        *reinterpret_cast<uint2*>(rows + p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[1][0], lw[1][1]);
+        *reinterpret_cast<uint2*>(rows + 2 * p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[2][0], lw[2][1]);
+      }
+      // a 128-k group = 16 consecutive chunks = 16 consecutive lanes (kCT % 16 == 0)
+#pragma unroll
+      for (int o = 8; o; o >>= 1) {
+        sl0 += __shfl_xor_sync(0xffffffffu, sl0, o);
+        sl1 += __shfl_xor_sync(0xffffffffu, sl1, o);
+        sl2 += __shfl_xor_sync(0xffffffffu, sl2, o);
+      }
+      if (valid && (ci & 15) == 0) {
+        float* S = S_s + (ci >> 4) * 8 + 3 * m;
+        S[0] = (float)sl0; S[1] = (float)sl1; S[2] = (float)sl2;
+      }
+    };
+    if (hold) {
+#pragma unroll
+      for (int it = 0; it < kHold; ++it) {
+        if (it < n_iter) {
+          const int ci = it * kCT + tid;
+          float f[8];
+          unpack8(xr[it], f);  // zero beyond Kx
+          emit(0, ci, ci < chunks_per_row, f, up_m[0]);
+        }
+      }
+    } else {
+      for (int m = 0; m < p.M; ++m) {
+        for (int it = 0; it < n_iter; ++it) {
+          const int ci = it * kCT + tid;
           const int64_t k0 = (int64_t)ci * 8;
           float f[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = 0.f;
-          if (k0 < p.Kx) {
-            unpack8(*reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0), f);
-            if (p.norm_w != nullptr) {
-              float wn[8];
-              unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = bf16r(f[e] * wn[e]);
-            }
+          if (ci < chunks_per_row && k0 < p.Kx) {
+            float dummy = 0.f;
+            load_norm(m, k0, f, dummy);
           }
-          // Balanced limbs without per-digit carries: X + 0x808080 = sum (a_i + 128) 256^i, so its bytes xor 0x80 ARE the
-          // two's-complement limbs a_i.  x * 2^e + 1.5 * 2^23 puts X + 2^22 into the float's mantissa (|X| <= 2^22 - 1 after
-          // the clamp), one integer add turns that into X + 0x808080, byte permutes gather limb i of the 8 elements in the
-          // order of the weight bytes after the nibble split: (k0, k0+4, k0+1, k0+5 | k0+2, k0+6, k0+3, k0+7).
-          uint32_t v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float t = fminf(fmaxf(fmaf(f[e], up, kIMagicF), kIMagicF - 4194303.f), kIMagicF + 4194303.f);
-            v[e] = __float_as_uint(t) + 0x00408080u;  // low 24 bits = X + 0x808080
-          }
-          uint32_t lw[3][2];
-#pragma unroll
-          for (int l = 0; l < 3; ++l) {
-            // limb l lives in byte (2 - l) of every v: selectors pick that byte of the two sources
-            const uint32_t sel = l == 0 ? 0x0062u : (l == 1 ? 0x0051u : 0x0040u);
-            const uint32_t p04 = __byte_perm(v[0], v[4], sel), p15 = __byte_perm(v[1], v[5], sel);   // (k0, k0+4), (k0+1, k0+5)
-            const uint32_t p26 = __byte_perm(v[2], v[6], sel), p37 = __byte_perm(v[3], v[7], sel);
-            lw[l][0] = __byte_perm(p04, p15, 0x5410) ^ 0x80808080u;
-            lw[l][1] = __byte_perm(p26, p37, 0x5410) ^ 0x80808080u;
-          }
-          sl0 = __dp4a((int)lw[0][0], 0x01010101, __dp4a((int)lw[0][1], 0x01010101, 0));
-          sl1 = __dp4a((int)lw[1][0], 0x01010101, __dp4a((int)lw[1][1], 0x01010101, 0));
-          sl2 = __dp4a((int)lw[2][0], 0x01010101, __dp4a((int)lw[2][1], 0x01010101, 0));
-          *reinterpret_cast<uint2*>(rows + (size_t)ci * 8) = make_uint2(lw[0][0], lw[0][1]);
-          *reinterpret_cast<uint2*>(rows + p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[1][0], lw[1][1]);
-          *reinterpret_cast<uint2*>(rows + 2 * p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[2][0], lw[2][1]);
-        }
-        // a 128-k group = 16 consecutive chunks = 16 consecutive lanes (kCT % 16 == 0)
-#pragma unroll
-        for (int o = 8; o; o >>= 1) {
-          sl0 += __shfl_xor_sync(0xffffffffu, sl0, o);
-          sl1 += __shfl_xor_sync(0xffffffffu, sl1, o);
-          sl2 += __shfl_xor_sync(0xffffffffu, sl2, o);
-        }
-        if (ci < chunks_per_row && (ci & 15) == 0) {
-          float* S = S_s + (ci >> 4) * 8 + 3 * m;
-          S[0] = (float)sl0; S[1] = (float)sl1; S[2] = (float)sl2;
+          emit(m, ci, ci < chunks_per_row, f, m == 0 ? up_m[0] : up_m[1]);
         }
       }
     }
@@ -428,6 +496,10 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
   p.y = static_cast<__nv_bfloat16*>(y);
   p.M = (int)M;
   p.epilogue = epilogue;
+  {
+    static const int hold = []() { const char* e = std::getenv("AO_B200_IMMA_HOLD"); return e ? std::atoi(e) : 1; }();
+    p.hold = hold;
+  }
   p.KT = (int)(Kp / 64);
   p.Kx = Kx; p.ldx = ldx; p.N_out = N_out; p.ldy = ldy; p.ld_res = ld_res;
   p.n_strips = (int)((N_out + 15) / 16);
@@ -451,7 +523,14 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
     sms = v > 0 ? v : kNumSMs;
   }
   const int max_grid = sms * (pl.smem <= 113 * 1024 ? 2 : 1);
-  const int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
+  // balanced waves: every CTA gets the same number of strips (+-1 at most on the last few), e.g. 1792 strips on 296 slots
+  // -> 256 CTAs x 7 instead of 16 CTAs with a 7th strip while 280 idle
+  int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
+  {
+    static const bool balance = []() { const char* e = std::getenv("AO_B200_BALANCE"); return e ? std::atoi(e) != 0 : false; }();
+    const int per = (p.n_strips + grid - 1) / grid;
+    if (balance) grid = (p.n_strips + per - 1) / per;
+  }
   p.strips_base = p.n_strips / grid;
   p.strips_rem = p.n_strips % grid;
   cudaLaunchConfig_t cfg{};

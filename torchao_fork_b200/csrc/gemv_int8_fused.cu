@@ -404,7 +404,14 @@ static int launch8(Gemv8Params& p, const Plan8& pl, bool pdl, cudaStream_t s) {
     attr_done = true;
   }
   const int max_grid = sm_count8() * (pl.smem <= 113 * 1024 && MT == 1 ? 2 : 1);
-  const int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
+  // balanced waves: every CTA gets the same number of strips (+-1 at most on the last few), e.g. 1792 strips on 296 slots
+  // -> 256 CTAs x 7 instead of 16 CTAs with a 7th strip while 280 idle
+  int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
+  {
+    static const bool balance = []() { const char* e = std::getenv("AO_B200_BALANCE"); return e ? std::atoi(e) != 0 : false; }();
+    const int per = (p.n_strips + grid - 1) / grid;
+    if (balance) grid = (p.n_strips + per - 1) / per;
+  }
   p.strips_base = p.n_strips / grid;
   p.strips_rem = p.n_strips % grid;
   cudaLaunchConfig_t cfg{};
