@@ -377,6 +377,7 @@ def run_b200(args):
         # tear-down: the graph holds NCCL kernels, release it before the communicator; exit without
         # destroy_process_group (it can block on a communicator that captured graphs have used)
         eng.graph = None
+        eng.graph_stream = None
         torch.cuda.synchronize()
         dist.barrier()
         sys.stdout.flush()

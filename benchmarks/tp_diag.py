@@ -71,6 +71,7 @@ def main():
     torch.cuda.synchronize()
     stage(f"20 graph steps: {e0.elapsed_time(e1) / 20 * 1e3:.1f} us per step")
     gen.engine.graph = None
+    gen.engine.graph_stream = None
     del gen, g
     import gc
     gc.collect()

@@ -54,6 +54,7 @@ def _worker(rank, world, port, q):
             seq = gen.generate(prompt, 12)
             outs[name] = (seq.clone(), prefill_logits, torch.stack(step_logits))
             gen.engine.graph = None
+            gen.engine.graph_stream = None
         torch.cuda.synchronize()
         s1, p1, l1 = outs["tp1"]
         s2, p2, l2 = outs["tp2"]

@@ -12,6 +12,7 @@ w1 and w3 are fused by concatenating their packed rows (row-wise quantization: t
 exactly the two quantized weights stacked), which cuts one launch per layer.
 """
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -179,7 +180,11 @@ class DecodeEngine:
         lins = [self.output] + [l[k] for l in self.layers for k in ("wqkv", "wo", "w13", "w1", "w3", "w2") if l[k]]
         ws_bytes = max(l.workspace_bytes(B) for l in lins)
         self.ws = torch.zeros(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
-        self.n_split = max(1, min(64, -(-self.S // 16)))
+        # sequence splits of the decode attention: one 32-position block per split up to S = 1024 (a block is one DRAM
+        # round trip; fewer splits = fewer CTAs and a cheaper merge), <= 32 (the merge keeps one split per lane)
+        self.n_split = max(1, min(32, -(-self.S // 32)))
+        if os.environ.get("AO_B200_ATTN_SPLIT"):  # tuning knob: sequence splits of the decode attention
+            self.n_split = max(1, int(os.environ["AO_B200_ATTN_SPLIT"]))
         awb = int(_lib.lib().ao_b200_decode_attention_workspace_bytes(B, self.H, self.n_split))
         self.attn_ws = torch.zeros(max(awb, 16), dtype=torch.uint8, device=dev)
         fwb = int(_lib.lib().ao_b200_decode_attention_fused_workspace_bytes(B, self.H, self.Hkv, self.n_split))
@@ -188,6 +193,7 @@ class DecodeEngine:
             self.out_norm.numel() + sum(l["attn_norm"].numel() + l["ffn_norm"].numel() for l in self.layers))
         self._noise = None
         self.graph = None
+        self.graph_stream = None
         self.launches_per_step = 0
 
     # ------------------------------------------------------------------ one step, eager launches
@@ -318,6 +324,25 @@ class DecodeEngine:
         mode = {} if self.tp is None else {"capture_error_mode": "thread_local"}
         with torch.cuda.graph(self.graph, **mode):
             self._launch_step()
+        self.tok.copy_(tok0)
+        self.pos.copy_(pos0)
+        torch.cuda.synchronize(self.device)
+        return self
+
+    def capture_streaming(self, h_tok: torch.Tensor, h_out: torch.Tensor):
+        """A second graph for the serving loop: [H2D copy of the fed token from pinned `h_tok`] -> the step -> [D2H copy of
+        the sampled token into pinned `h_out`], so one replay + one stream sync is a whole host-visible step (the copies
+        are memcpy nodes; issuing them as separate calls costs the host ~20 us each per token)."""
+        assert h_tok.is_pinned() and h_out.is_pinned() and self.graph is not None
+        tok0, pos0 = self.tok.clone(), self.pos.clone()
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        mode = {} if self.tp is None else {"capture_error_mode": "thread_local"}
+        with torch.cuda.graph(g, **mode):
+            self.tok.copy_(h_tok, non_blocking=True)
+            self._launch_step()
+            h_out.copy_(self.next_tok, non_blocking=True)
+        self.graph_stream = g
         self.tok.copy_(tok0)
         self.pos.copy_(pos0)
         torch.cuda.synchronize(self.device)

@@ -94,6 +94,18 @@ class Generator:
             out = torch.empty(B, n, dtype=torch.int64)
             self.h_tok.copy_(eng.tok)
             stream = torch.cuda.current_stream(dev)
+            if eng.graph is not None and eng.graph_stream is None:
+                eng.capture_streaming(self.h_tok, self.h_out)
+            if eng.graph_stream is not None:
+                # one replay = H2D of the fed token + the step + D2H of the sampled token (memcpy nodes in the graph)
+                h_tok, h_out, o = self.h_tok.numpy(), self.h_out.numpy(), out.numpy()
+                for i in range(n):
+                    eng.graph_stream.replay()
+                    stream.synchronize()
+                    callback(self.h_out)
+                    o[:, i] = h_out
+                    h_tok[:] = h_out
+                return out
             for i in range(n):
                 eng.tok.copy_(self.h_tok, non_blocking=True)        # H2D: the token the host feeds
                 tok = eng.step()

@@ -247,38 +247,60 @@ __global__ void __launch_bounds__(kGroup * 32) decode_attn_fused_kernel(
     qv[2] = __uint_as_float(r.y << 16) * scale;
     qv[3] = __uint_as_float(r.y & 0xFFFF0000u) * scale;
   }
+  // The walk is latency-bound (a few KB per CTA), so it is organised for memory-level parallelism: a block of 32 cache
+  // positions per trip, lane j owns position jb + j for q.K (its whole 256-byte K row: 16 independent 16-byte loads, no
+  // shuffles), the V rows of the block (one coalesced 8-byte load per lane per position) are requested BEFORE the scores
+  // are reduced, and P.V broadcasts the probabilities lane by lane.  One DRAM round trip per 32 positions instead of
+  // one per 4.
+  __shared__ __align__(16) float q_s[kGroup][hd];
+  *reinterpret_cast<float4*>(&q_s[warp][lane * 4]) = make_float4(qv[0], qv[1], qv[2], qv[3]);
+  __syncwarp();
   float m = -INFINITY, l = 0.f, acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int j = j0; j < j1; j += 4) {
-    // four positions per trip: the loads and the four reductions are independent
-    uint2 kr[4], vr[4];
-    float sc[4];
+  for (int jb = j0; jb < j1; jb += 32) {
+    const int cnt = min(32, j1 - jb);
+    const bool valid = lane < cnt;
+    uint4 kk[16];
+    {
+      const uint4* krow = reinterpret_cast<const uint4*>(kb - lane * 4 + (int64_t)(jb + (valid ? lane : 0)) * hd);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int jj = min(j + u, j1 - 1);
-      kr[u] = *reinterpret_cast<const uint2*>(kb + (int64_t)jj * hd);
-      vr[u] = *reinterpret_cast<const uint2*>(vb + (int64_t)jj * hd);
+      for (int i = 0; i < 16; ++i) kk[i] = krow[i];
     }
+    uint2 vr[32];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      sc[u] = qv[0] * __uint_as_float(kr[u].x << 16) + qv[1] * __uint_as_float(kr[u].x & 0xFFFF0000u) +
-              qv[2] * __uint_as_float(kr[u].y << 16) + qv[3] * __uint_as_float(kr[u].y & 0xFFFF0000u);
+    for (int jj = 0; jj < 32; ++jj)
+      vr[jj] = jj < cnt ? *reinterpret_cast<const uint2*>(vb + (int64_t)(jb + jj) * hd) : make_uint2(0u, 0u);
+    float sc = 0.f;
 #pragma unroll
-    for (int o = 16; o; o >>= 1)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) sc[u] += __shfl_xor_sync(0xffffffffu, sc[u], o);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (j + u >= j1) break;
-      const float m_new = fmaxf(m, sc[u]);
-      const float corr = __expf(m - m_new);
-      const float p = __expf(sc[u] - m_new);
-      l = l * corr + p;
-      acc[0] = acc[0] * corr + p * __uint_as_float(vr[u].x << 16);
-      acc[1] = acc[1] * corr + p * __uint_as_float(vr[u].x & 0xFFFF0000u);
-      acc[2] = acc[2] * corr + p * __uint_as_float(vr[u].y << 16);
-      acc[3] = acc[3] * corr + p * __uint_as_float(vr[u].y & 0xFFFF0000u);
-      m = m_new;
+    for (int i = 0; i < 16; ++i) {
+      const float4 qa = *reinterpret_cast<const float4*>(&q_s[warp][8 * i]);
+      const float4 qb = *reinterpret_cast<const float4*>(&q_s[warp][8 * i + 4]);
+      sc += qa.x * __uint_as_float(kk[i].x << 16) + qa.y * __uint_as_float(kk[i].x & 0xFFFF0000u) +
+            qa.z * __uint_as_float(kk[i].y << 16) + qa.w * __uint_as_float(kk[i].y & 0xFFFF0000u) +
+            qb.x * __uint_as_float(kk[i].z << 16) + qb.y * __uint_as_float(kk[i].z & 0xFFFF0000u) +
+            qb.z * __uint_as_float(kk[i].w << 16) + qb.w * __uint_as_float(kk[i].w & 0xFFFF0000u);
     }
+    if (!valid) sc = -INFINITY;
+    float mb = sc;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, o));
+    const float m_new = fmaxf(m, mb);  // finite: the block holds at least one position
+    const float corr = __expf(m - m_new);
+    const float pj = valid ? __expf(sc - m_new) : 0.f;
+    float ps = pj;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
+    l = l * corr + ps;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[e] *= corr;
+#pragma unroll
+    for (int jj = 0; jj < 32; ++jj) {
+      const float pw = __shfl_sync(0xffffffffu, pj, jj);  // 0 beyond cnt
+      acc[0] += pw * __uint_as_float(vr[jj].x << 16);
+      acc[1] += pw * __uint_as_float(vr[jj].x & 0xFFFF0000u);
+      acc[2] += pw * __uint_as_float(vr[jj].y << 16);
+      acc[3] += pw * __uint_as_float(vr[jj].y & 0xFFFF0000u);
+    }
+    m = m_new;
   }
   if (n_split == 1) {
     const float inv = 1.f / l;
@@ -308,15 +330,40 @@ __global__ void __launch_bounds__(kGroup * 32) decode_attn_fused_kernel(
   __threadfence();
   // merge the n_split partials of this warp's q head
   const int64_t bh = (int64_t)b * H + h;
-  float mm = -INFINITY;
-  for (int s = 0; s < n_split; ++s) mm = fmaxf(mm, __ldcg(part_ml + (bh * n_split + s) * 2));
   float ll = 0.f, a[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int s = 0; s < n_split; ++s) {
-    const float ms = __ldcg(part_ml + (bh * n_split + s) * 2), ls = __ldcg(part_ml + (bh * n_split + s) * 2 + 1);
+  if (n_split <= 32) {
+    // lane s owns split s's (m, l): one coalesced load, the maximum and the normaliser are warp reductions, the weights
+    // exp(m_s - max) are computed once in parallel; the accumulation loop is then independent loads + broadcasts
+    float ms = -INFINITY, ls = 0.f;
+    if (lane < n_split) {
+      const float2 ml = __ldcg(reinterpret_cast<const float2*>(part_ml + (bh * n_split + lane) * 2));
+      ms = ml.x;
+      ls = ml.y;
+    }
+    float mm = ms;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mm = fmaxf(mm, __shfl_xor_sync(0xffffffffu, mm, o));
     const float w = (ls > 0.f) ? __expf(ms - mm) : 0.f;
-    const float4 po = __ldcg(reinterpret_cast<const float4*>(part_o + (bh * n_split + s) * hd + lane * 4));
-    ll += ls * w;
-    a[0] += po.x * w; a[1] += po.y * w; a[2] += po.z * w; a[3] += po.w * w;
+    ll = ls * w;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
+    const float4* pp = reinterpret_cast<const float4*>(part_o + bh * n_split * hd + lane * 4);
+#pragma unroll 8
+    for (int s = 0; s < n_split; ++s) {
+      const float4 po = __ldcg(pp + s * (hd / 4));
+      const float ws = __shfl_sync(0xffffffffu, w, s);
+      a[0] += po.x * ws; a[1] += po.y * ws; a[2] += po.z * ws; a[3] += po.w * ws;
+    }
+  } else {
+    float mm = -INFINITY;
+    for (int s = 0; s < n_split; ++s) mm = fmaxf(mm, __ldcg(part_ml + (bh * n_split + s) * 2));
+    for (int s = 0; s < n_split; ++s) {
+      const float ms = __ldcg(part_ml + (bh * n_split + s) * 2), ls = __ldcg(part_ml + (bh * n_split + s) * 2 + 1);
+      const float w = (ls > 0.f) ? __expf(ms - mm) : 0.f;
+      const float4 po = __ldcg(reinterpret_cast<const float4*>(part_o + (bh * n_split + s) * hd + lane * 4));
+      ll += ls * w;
+      a[0] += po.x * w; a[1] += po.y * w; a[2] += po.z * w; a[3] += po.w * w;
+    }
   }
   const float inv = 1.f / ll;
   uint2 o;

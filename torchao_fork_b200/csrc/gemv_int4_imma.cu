@@ -379,9 +379,10 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
         }
       }
     }
-    named_bar_sync(1, kCT);
   }
-  named_bar_sync(2, kIThreads);  // the producer has initialised the mbarriers (long ago)
+  // one barrier closes the staging (limbs, group sums, row scale visible to every consumer and to the epilogue warp) and
+  // meets the producer, which initialised the mbarriers long ago
+  named_bar_sync(2, kIThreads);
 
   // ---- main loop: warp w owns k-tiles 2 w, 2 w + 1 (= group w) of every stage ----
   const uint32_t ring_u = smem_u32(ring);

@@ -192,11 +192,98 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
   const int g = lane >> 2, c = lane & 3;
   const int tid = threadIdx.x;  // 0 .. 511
   constexpr int kCT = k8Consumers * 32;
+  constexpr int kHold = 4;            // chunks a thread keeps in registers between the two staging passes
+  const int chunks_per_row = KT * 8;  // 16-byte chunks of 8 elements over Kp
+  const int n_iter = (chunks_per_row + kCT - 1) / kCT;
+  // Fast path (M = 1, Kp <= 16384): every thread owns <= 4 chunks, all of their loads are issued at once, the normalised
+  // bf16 values stay in registers between the two passes, every warp reduces the row statistics itself, and the norm
+  // weights (independent of the previous kernel, a DRAM miss) are fetched BEFORE the dependency wait.
+  const bool hold = p.M == 1 && n_iter <= kHold;
+  uint4 xr[kHold], wn4[kHold];
+#pragma unroll
+  for (int i = 0; i < kHold; ++i) xr[i] = wn4[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (hold && p.norm_w != nullptr) {
+#pragma unroll
+    for (int i = 0; i < kHold; ++i) {
+      const int ci = i * kCT + tid;
+      if ((int64_t)ci * 8 < p.Kx) wn4[i] = __ldg(reinterpret_cast<const uint4*>(p.norm_w + (int64_t)ci * 8));
+    }
+  }
   grid_dependency_wait();
 
   // ---- stage the activations: x (* norm_w) -> per-row power-of-two scaling -> fp16; per-64-k correction sums ----
-  const int chunks_per_row = KT * 8;  // 16-byte chunks of 8 elements over Kp
-  {
+  if (hold) {
+    float ss = 0.f, amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < kHold; ++i) {
+      const int ci = i * kCT + tid;
+      if ((int64_t)ci * 8 < p.Kx) xr[i] = *reinterpret_cast<const uint4*>(p.x + (int64_t)ci * 8);
+    }
+#pragma unroll
+    for (int i = 0; i < kHold; ++i) {
+      float f[8];
+      unpack8(xr[i], f);
+      if (p.norm_w != nullptr) {
+        float wn[8];
+        unpack8(wn4[i], wn);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          ss = fmaf(f[e], f[e], ss);
+          f[e] = bf16r(f[e] * wn[e]);
+        }
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
+        xr[i] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
+    }
+    ss = warp_sum8(ss);
+    amax = warp_max8(amax);
+    if (lane == 0) {
+      part[warp * 2] = ss;
+      part[warp * 2 + 1] = amax;
+    }
+    named_bar_sync(1, kCT);
+    float t = 0.f;
+    amax = 0.f;
+    if (lane < k8Consumers) {
+      t = part[lane * 2];
+      amax = part[lane * 2 + 1];
+    }
+    t = warp_sum8(t);
+    amax = warp_max8(amax);
+    int e = 0;
+    if (amax > 0.f) e = (int)((__float_as_uint(amax) >> 23) & 0xFF) - 127 - 13;
+    e = max(-100, min(100, e));
+    const float dn = __uint_as_float((uint32_t)(127 - e) << 23);
+    if (warp == 0 && lane == 0) {
+      const float up = __uint_as_float((uint32_t)(e + 127) << 23);
+      row_scale[0] = (p.norm_w != nullptr) ? up * rsqrtf(t / (float)p.Kx + p.eps) : up;  // read by the epilogue warp
+    }
+#pragma unroll
+    for (int it = 0; it < kHold; ++it) {
+      if (it < n_iter) {
+        const int ci = it * kCT + tid;
+        float xs = 0.f;
+        if (ci < chunks_per_row) {
+          float f[8];
+          unpack8(xr[it], f);
+          const __half2 h0 = __floats2half2_rn(f[0] * dn, f[1] * dn), h1 = __floats2half2_rn(f[2] * dn, f[3] * dn);
+          const __half2 h2 = __floats2half2_rn(f[4] * dn, f[5] * dn), h3 = __floats2half2_rn(f[6] * dn, f[7] * dn);
+          *reinterpret_cast<uint4*>(x_s + (size_t)ci * 16) =
+              make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                         *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+          const float2 a0 = __half22float2(h0), a1 = __half22float2(h1), a2 = __half22float2(h2), a3 = __half22float2(h3);
+          xs = ((a0.x + a0.y) + (a1.x + a1.y)) + ((a2.x + a2.y) + (a3.x + a3.y));
+        }
+#pragma unroll
+        for (int o = 4; o; o >>= 1) xs += __shfl_xor_sync(0xffffffffu, xs, o);
+        if (ci < chunks_per_row && (ci & 7) == 0) C_s[(ci >> 3) * 8 * MT] = -1152.f * xs;
+      }
+    }
+  } else {
     for (int m = 0; m < p.M; ++m) {
       float ss = 0.f, amax = 0.f;
       for (int ci = tid; ci < chunks_per_row; ci += kCT) {
@@ -271,9 +358,10 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
         if (ci < chunks_per_row && (ci & 7) == 0) C_s[(ci >> 3) * 8 * MT + m] = -1152.f * xs;
       }
     }
-    named_bar_sync(1, kCT);
   }
-  named_bar_sync(2, k8Threads);  // the producer has initialised the mbarriers (long ago)
+  // one barrier closes the staging (activations, correction sums, row scales visible to every consumer and to the epilogue
+  // warp) and meets the producer, which initialised the mbarriers long ago
+  named_bar_sync(2, k8Threads);
 
   // ---- main loop: warp w owns k-tile w of every stage ----
   constexpr uint32_t CS = 8 * MT * 4;  // bytes of one segment's record
