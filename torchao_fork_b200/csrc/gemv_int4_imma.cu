@@ -523,7 +523,11 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
     cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
     sms = v > 0 ? v : kNumSMs;
   }
-  const int max_grid = sms * (pl.smem <= 113 * 1024 ? 2 : 1);
+  // AO_B200_IMMA_CTAS: CTAs of ONE launch per SM.  2 (default) = more warps per launch; 1 leaves the second slot to the NEXT
+  // kernel of the PDL chain, whose producer then prefetches its weights while this launch is still running.
+  static const int ctas = []() { const char* e = std::getenv("AO_B200_IMMA_CTAS"); const int v = e ? std::atoi(e) : 2; return v < 1 ? 1 : (v > 2 ? 2 : v); }();
+  static const int one_below = []() { const char* e = std::getenv("AO_B200_IMMA_CTAS1_BELOW"); return e ? std::atoi(e) : 0; }();
+  const int max_grid = sms * (pl.smem <= 113 * 1024 ? (p.n_strips <= one_below ? 1 : ctas) : 1);
   // balanced waves: every CTA gets the same number of strips (+-1 at most on the last few), e.g. 1792 strips on 296 slots
   // -> 256 CTAs x 7 instead of 16 CTAs with a 7th strip while 280 idle
   int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
