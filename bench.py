@@ -165,11 +165,13 @@ def cpu_reference(workload, steps, warmup, budget_s=25.0):
         if time.perf_counter() - t_start > budget_s:
             break
     t_block = statistics.median(times)
+    path_name = ("Int4CPULayout path (_weight_int4pack_mm_for_cpu)" if spec["quant"] == "int4"
+                 else "Int8WeightOnlyConfig PlainLayout path (mm(x, int8.to(bf16)) * scale on CPU)")
     block_w = sum(n * k for n, k in shapes)
     t_token = t_block * (cfg.n_layer + cfg.vocab_size * D / block_w)
     return {"value": 1.0 / t_token, "unit": "tok/s", "cores": cores, "kind": kind,
             "sample": f"{len(times)} timed passes over the 5 quantized linears of 1 of {cfg.n_layer} transformer blocks "
-                      f"at M=1 through the reference's Int4CPULayout path (median {t_block * 1e3:.2f} ms/block); token time = "
+                      f"at M=1 through the reference's {path_name} (median {t_block * 1e3:.2f} ms/block); token time = "
                       f"{cfg.n_layer} blocks + output projection scaled by weight count; attention/norms/sampling excluded; "
                       f"reference quantize_ of the block took {t_quant:.1f} s",
             "ms_per_token": t_token * 1e3}
