@@ -44,7 +44,7 @@ def test_model_args_match_reference_table():
 
 @cuda
 @pytest.mark.parametrize("quant", ["int4", "int8"])
-@pytest.mark.parametrize("batch", [1, 4])
+@pytest.mark.parametrize("batch", [1, 4, 32])
 def test_engine_step_matches_eager_forward(quant, batch):
     m = _tiny(quant)
     gen = Generator(m, batch, 64, temperature=0.0, top_k=None)

@@ -115,7 +115,8 @@ class _Linear:
         elif self.kind == "int8":
             _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, self.k, x.stride(0), self.packed.data_ptr(),
                                          self.scale.data_ptr(), self.np_, self.kp, y.data_ptr(), self.n, y.stride(0),
-                                         None, 0, stream), "int8_mm")
+                                         _ptr(ws) if m > 16 else None, 0 if (ws is None or m <= 16) else ws.numel(), stream),
+                       "int8_mm")
         else:
             torch.mm(x, self.w.t(), out=y)
 
@@ -128,12 +129,13 @@ class DecodeEngine:
         cfg = model.config
         assert model.freqs_cis is not None and model.max_batch_size >= batch_size, "call model.setup_caches first"
         assert cfg.head_dim == 128, "decode attention kernel is specialised for head_dim 128"
-        assert batch_size <= 16, "the decode path covers M <= 16"
+        assert batch_size <= 64, "the decode engine covers batch sizes up to 64 (M > 16 runs the prefill GEMM per linear)"
         self.model, self.cfg, self.B = model, cfg, batch_size
         self.temperature, self.top_k = temperature, top_k
         self.tp = tp  # tensor-parallel context (tp.py) or None
         dev = model.tok_embeddings.weight.device
         if tp is not None and tp.world_size > 1:
+            assert batch_size <= 16, "the tensor-parallel exchange buffers are sized for B <= 16"
             tp.enable_peer_exchange(16 * cfg.dim)  # h / delta are [B <= 16][dim]
         self.device = dev
         bf = dict(dtype=torch.bfloat16, device=dev)
