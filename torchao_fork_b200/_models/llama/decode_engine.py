@@ -102,7 +102,7 @@ class _Linear:
             "int4_gemv_fused")
 
     def fused_fits(self, m):
-        return self.kind in ("int4", "int8") and m * (2 * self.kp + 16) <= 150 * 1024
+        return self.kind in ("int4", "int8") and m <= 16 and m * (2 * self.kp + 16) <= 150 * 1024
 
     def launch(self, x: torch.Tensor, y: torch.Tensor, ws: Optional[torch.Tensor], stream: int):
         m = x.shape[0]
@@ -115,7 +115,7 @@ class _Linear:
         elif self.kind == "int8":
             _lib.check(L.ao_b200_int8_mm(x.data_ptr(), m, self.k, x.stride(0), self.packed.data_ptr(),
                                          self.scale.data_ptr(), self.np_, self.kp, y.data_ptr(), self.n, y.stride(0),
-                                         _ptr(ws) if m > 16 else None, 0 if (ws is None or m <= 16) else ws.numel(), stream),
+                                         _ptr(ws), 0 if ws is None else ws.numel(), stream),
                        "int8_mm")
         else:
             torch.mm(x, self.w.t(), out=y)

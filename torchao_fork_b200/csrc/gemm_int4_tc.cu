@@ -62,7 +62,9 @@ struct GemmTcParams {
   const __nv_bfloat16* xt;   // permuted activations [Mpad/NT][Kp/64][8 chunks][NT][8]
   __nv_bfloat16* y;          // [M][ldy]
   int M, KT, stages, tmem_cols, cluster, vec_store;
-  int64_t Mpad, N_out, ldy;
+  int kt_per_split;          // split-K (grid.z): this many 64-k tiles per split, a multiple of the weight-ring slice
+  float* part;               // split-K: fp32 partial sums [splits][Mpad][Np] (null: one split, bf16 output written directly)
+  int64_t Mpad, N_out, ldy, Np;
 };
 
 // ---- activations -> chunk-major, k-permuted copy ------------------------------------------------------------------
@@ -168,7 +170,10 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
   constexpr int kSlotTiles = kGmWSlotBytes / (8 * kTileB);    // k-tiles per weight-ring slot: 4 (int4) / 2 (int8)
   constexpr uint32_t kXStage = NT * 128;
   constexpr uint32_t kChunk = NT * 16;  // bytes between consecutive 8-k chunks of the B tile (descriptor LBO)
-  const int stages = p.stages, KT = p.KT;
+  const int stages = p.stages, KTa = p.KT;
+  // split-K: this CTA covers k-tiles [kt_lo, kt_lo + KT) of the row block (the whole K when grid.z == 1)
+  const int kt_lo = blockIdx.z * p.kt_per_split;
+  const int KT = min(p.kt_per_split, KTa - kt_lo);
   uint64_t* wfull = reinterpret_cast<uint64_t*>(gm_smem);
   uint64_t* wempty = wfull + kGmWSlots;
   uint64_t* xfull = wempty + kGmWSlots;
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
   if (warp == kGmProducerWarp) {
     // ---- TMA producer, activations: one multicast copy (this CTA's share of the stage) per 64-k tile ----------------
     const uint32_t share = kXStage / CL;
-    const uint8_t* xsrc = reinterpret_cast<const uint8_t*>(p.xt) + (int64_t)mt * KT * kXStage + crank * share;
+    const uint8_t* xsrc = reinterpret_cast<const uint8_t*>(p.xt) + ((int64_t)mt * KTa + kt_lo) * kXStage + crank * share;
     for (int it = 0; it < KT; ++it) {
       GM_TRACE(0, it);
       const int slot = it % stages;
@@ -257,12 +262,12 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     const int g = lane >> 2;
     constexpr int GG = kI8 ? 64 : G;  // (int8: no per-group parameters; GG only keeps the int4 index math well-formed)
     constexpr int kGroupsPerTile = GG >= 64 ? 1 : 64 / GG;
-    const int n_groups = KT * 64 / GG;
+    const int n_groups = KTa * 64 / GG;
     const uint32_t* szp = kI8 ? nullptr : p.sz + ((int64_t)(nb * 8 + strip) * n_groups) * 16 + g;
     const uint32_t taddr0 = tb + ((uint32_t)(32 * qd + 16 * (dq >> 2)) << 16) + NT;
     uint32_t szn[kGroupsPerTile][2];
     if constexpr (!kI8) {
-      const int64_t grp = GG >= 64 ? (int64_t)set * 64 / GG : (int64_t)set * kGroupsPerTile;
+      const int64_t grp = GG >= 64 ? (int64_t)(kt_lo + set) * 64 / GG : (int64_t)(kt_lo + set) * kGroupsPerTile;
 #pragma unroll
       for (int h = 0; h < kGroupsPerTile; ++h) {
         szn[h][0] = __ldg(szp + (grp + h) * 16);
@@ -281,7 +286,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
             z2[h][r] = __byte_perm(szn[h][r], 0, 0x3232);
           }
         if (it + 2 < KT) {
-          const int64_t grp = GG >= 64 ? (int64_t)(it + 2) * 64 / GG : (int64_t)(it + 2) * kGroupsPerTile;
+          const int64_t grp = GG >= 64 ? (int64_t)(kt_lo + it + 2) * 64 / GG : (int64_t)(kt_lo + it + 2) * kGroupsPerTile;
 #pragma unroll
           for (int h = 0; h < kGroupsPerTile; ++h) {
             szn[h][0] = __ldg(szp + (grp + h) * 16);
@@ -336,7 +341,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
       // ---- TMA producer, weights (this warp has nothing else to do until the accumulator is final): slice wc = k-tiles
       // 4 wc .. 4 wc + 3 of the row block, 8 copies of 2 KB, into ring slot wc % kGmWSlots as soon as the dequant
       // warps have released it.  Kept off the activation producer: a bulk copy costs its issuing warp ~130 clocks.
-      const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), 0, KT) * kTileB;
+      const uint8_t* wsrc = p.packed + tile_slot((int64_t)nb * 8 + (lane & 7), kt_lo, KTa) * kTileB;
       for (int wc = 0; wc * kSlotTiles < KT; ++wc) {
         const int ws = wc % kGmWSlots, t0 = wc * kSlotTiles;
         if (wc >= kGmWSlots) mbar_wait(&wempty[ws], ((wc / kGmWSlots) - 1) & 1);
@@ -354,9 +359,29 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
     mbar_wait(d_full, 0);
     gm_fence_after();
     GM_TRACE(1, 0);
+    const int nl = 32 * warp + lane;
+    if (p.part != nullptr) {
+      // split-K: this split's fp32 partial sums straight from tensor memory (thread = weight row: a warp's 32 rows are one
+      // 128-byte line per activation row); split_reduce_kernel sums the splits and applies the output rounding
+      float* dst = p.part + ((int64_t)blockIdx.z * p.Mpad + (int64_t)mt * NT) * p.Np + (int64_t)nb * 128 + nl;
+#pragma unroll 1
+      for (int cc = 0; cc < NT / 32; ++cc) {
+        uint32_t d[32];
+        gm_ld_32x32b_x32(tb + ((uint32_t)(32 * warp) << 16) + 32 * cc, d);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if ((int64_t)mt * NT + 32 * cc < p.M) {
+          float* q = dst + (int64_t)(32 * cc) * p.Np;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            *q = __uint_as_float(d[j]);
+            q += p.Np;
+          }
+        }
+      }
+      gm_fence_before();
+    } else {
     constexpr uint32_t kPitch = 128 * 2 + 16;
     const uint32_t tile_u = wring_u;
-    const int nl = 32 * warp + lane;
     float sc8 = 1.f;
     if constexpr (kI8) {
       const int64_t n = (int64_t)nb * 128 + nl;
@@ -396,6 +421,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
       }
     }
     GM_TRACE(2, 0);
+    }
   }
   __syncthreads();
   gm_cluster_sync();  // peers may still be arriving on this CTA's barriers
@@ -405,19 +431,66 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
   }
 }
 
+// ---- split-K epilogue: y = bf16( sum over splits ) ; int8: y = bf16( bf16(sum) * scale[n] ) ------------------------------
+__global__ void __launch_bounds__(256) split_reduce_kernel(const float* __restrict__ part, int splits, int64_t Mpad, int64_t Np,
+                                                           int64_t M, int64_t N_out, const __nv_bfloat16* __restrict__ scale8,
+                                                           __nv_bfloat16* __restrict__ y, int64_t ldy) {
+  const int64_t n4 = (N_out + 3) / 4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M * n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = i / n4, n = (i - m * n4) * 4;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int sp = 0; sp < splits; ++sp) {  // fixed order: deterministic
+      const float4 v = *reinterpret_cast<const float4*>(part + ((int64_t)sp * Mpad + m) * Np + n);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    const float r[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (n + e >= N_out) break;
+      const float v = scale8 ? bf16r(r[e]) * __bfloat162float(scale8[n + e]) : r[e];
+      y[m * ldy + n + e] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
 // ---- host ---------------------------------------------------------------------------------------------------------
 static int gm_tile_rows(int64_t M) { return M <= 64 ? 64 : (M <= 128 ? 128 : 256); }
 
-// bytes of the permuted-activation staging buffer the GEMM needs for M rows (0: shape not handled by this kernel)
+// split-K plan: when (row blocks x prompt tiles) leaves most of the 148 SMs idle (small M and / or small N), the K range
+// is cut into `splits` pieces of `kt_per` 64-k tiles (a multiple of 4, >= 16), each piece its own CTA (grid.z).  Pure
+// function of the shape, so the workspace size is too.
+static void gm_split_plan(int64_t M, int64_t Np, int64_t Kp, int& splits, int& kt_per) {
+  const int NT = gm_tile_rows(M);
+  const int64_t ctas = (Np / 128) * ((M + NT - 1) / NT);
+  const int KT = (int)(Kp / 64);
+  splits = 1;
+  kt_per = KT;
+  static const int enable = []() { const char* e = std::getenv("AO_B200_GEMM_SPLITK"); return e ? std::atoi(e) : 1; }();
+  // measured (profiles/r01b_gemm_splitk.jsonl): pays for long K and few prompt rows (4096 x 14336, M = 32: 84 -> 45 us);
+  // at K = 4096 the extra reduce launch costs more than the idle SMs, at M = 512 the partial sums are 25 MB
+  if (!enable || ctas >= 112 || KT < 128 || M > 128) return;
+  int want = (int)((148 + ctas - 1) / ctas);           // enough CTAs for one wave
+  if (want > 8) want = 8;
+  if (want > KT / 16) want = KT / 16;                   // at least 1024 k per split
+  if (want < 2) return;
+  kt_per = ((KT + want - 1) / want + 3) / 4 * 4;
+  splits = (KT + kt_per - 1) / kt_per;
+  if (splits < 2) { splits = 1; kt_per = KT; }
+}
+
+// bytes of the workspace the GEMM needs for M rows: the permuted-activation staging copy + (split-K) the fp32 partial
+// sums (0: shape not handled by this kernel)
 int64_t int4_gemm_tc_workspace_bytes(int64_t M, int64_t Np, int64_t Kp) {
   if (Np % 128 != 0 || Kp % 64 != 0 || M <= 0) return 0;
   const int NT = gm_tile_rows(M);
   const int64_t Mpad = (M + NT - 1) / NT * NT;
-  return Mpad * Kp * 2;
+  int splits, kt_per;
+  gm_split_plan(M, Np, Kp, splits, kt_per);
+  return Mpad * Kp * 2 + (splits > 1 ? (int64_t)splits * Mpad * Np * 4 : 0);
 }
 
 template <int G, int NT>
-static int launch_gemm_tc(GemmTcParams& p, int64_t Np, cudaStream_t s) {
+static int launch_gemm_tc(GemmTcParams& p, int64_t Np, int splits, cudaStream_t s) {
   constexpr size_t kStageBytes = NT * 128;
   constexpr size_t kFixed = kGmHeader + kGmWSlots * kGmWSlotBytes;
   static int max_smem = -1;
@@ -430,7 +503,7 @@ static int launch_gemm_tc(GemmTcParams& p, int64_t Np, cudaStream_t s) {
   const int max_by_tmem = (512 - NT) / 32;
   if (stages > max_by_tmem) stages = max_by_tmem;
   if (stages > kGmMaxStages) stages = kGmMaxStages;
-  if (stages > p.KT) stages = p.KT;
+  if (stages > p.kt_per_split) stages = p.kt_per_split;
   if (stages < 1) return AO_B200_ERR_UNSUPPORTED;
   p.stages = stages;
   int cols = 32;
@@ -452,7 +525,7 @@ static int launch_gemm_tc(GemmTcParams& p, int64_t Np, cudaStream_t s) {
   }();
   p.cluster = (n_blocks % 4 == 0 && max_cl >= 4) ? 4 : ((n_blocks % 2 == 0 && max_cl >= 2) ? 2 : 1);
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)n_blocks, (unsigned)(p.Mpad / NT));
+  cfg.gridDim = dim3((unsigned)n_blocks, (unsigned)(p.Mpad / NT), (unsigned)splits);
   cfg.blockDim = dim3(kGmThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
@@ -486,18 +559,24 @@ static int gemm_tc_any(const void* x, int64_t M, int64_t Kx, int64_t ldx, const 
   p.Mpad = (M + NT - 1) / NT * NT;
   p.N_out = N_out;
   p.ldy = ldy;
+  p.Np = Np;
   p.vec_store = (ldy % 8 == 0 && ao_aligned(y, 16)) ? 1 : 0;
   if (p.Mpad / NT > 65535) return AO_B200_ERR_UNSUPPORTED;
+  int splits = 1;
+  gm_split_plan(M, Np, Kp, splits, p.kt_per_split);
+  p.part = splits > 1 ? reinterpret_cast<float*>(static_cast<char*>(workspace) + p.Mpad * Kp * 2) : nullptr;
   const int64_t items = p.Mpad * p.KT;
   x_permute_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), M, Kx, ldx, p.Mpad, p.KT, NT,
                                                                    static_cast<__nv_bfloat16*>(workspace));
   if (cudaGetLastError() != cudaSuccess) return AO_B200_ERR_CUDA;
-#define AO_GM(GG)                                                        \
-  switch (NT) {                                                          \
-    case 64: return launch_gemm_tc<GG, 64>(p, Np, s);                    \
-    case 128: return launch_gemm_tc<GG, 128>(p, Np, s);                  \
-    default: return launch_gemm_tc<GG, 256>(p, Np, s);                   \
-  }
+  int rc = AO_B200_ERR_UNSUPPORTED;
+#define AO_GM(GG)                                                              \
+  switch (NT) {                                                                \
+    case 64: rc = launch_gemm_tc<GG, 64>(p, Np, splits, s); break;             \
+    case 128: rc = launch_gemm_tc<GG, 128>(p, Np, splits, s); break;           \
+    default: rc = launch_gemm_tc<GG, 256>(p, Np, splits, s); break;            \
+  }                                                                            \
+  break;
   switch (G) {
     case 0: AO_GM(0)
     case 32: AO_GM(32)
@@ -506,7 +585,12 @@ static int gemm_tc_any(const void* x, int64_t M, int64_t Kx, int64_t ldx, const 
     case 256: AO_GM(256)
   }
 #undef AO_GM
-  return AO_B200_ERR_UNSUPPORTED;
+  if (rc != AO_B200_OK || splits == 1) return rc;
+  const int64_t red_items = M * ((N_out + 3) / 4);
+  const int64_t blocks = (red_items + 255) / 256;
+  split_reduce_kernel<<<(unsigned)(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, s>>>(p.part, splits, p.Mpad, Np, M, N_out, p.scale8,
+                                                                                  p.y, ldy);
+  return ao_launch_status();
 }
 
 int int4_gemm_tc(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np, int64_t Kp,
