@@ -20,15 +20,19 @@ __global__ void __launch_bounds__(256) int8_quantize_kernel(const __nv_bfloat16*
     float mn = INFINITY, mx = -INFINITY;
     const bool vec = (K % 8 == 0) && (ldw % 8 == 0) && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
     if (vec) {
+      // packed bf16x2 min / max (comparisons only: exact), one instruction per two weights
+      uint32_t mn2 = 0x7F807F80u, mx2 = 0xFF80FF80u;
       for (int64_t i = threadIdx.x; i < K / 8; i += blockDim.x) {
-        float f[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(p) + i), f);
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + i);
+        const uint32_t r[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          mn = fminf(mn, f[e]);
-          mx = fmaxf(mx, f[e]);
+        for (int e = 0; e < 4; ++e) {
+          asm("min.bf16x2 %0, %0, %1;" : "+r"(mn2) : "r"(r[e]));
+          asm("max.bf16x2 %0, %0, %1;" : "+r"(mx2) : "r"(r[e]));
         }
       }
+      mn = fminf(__uint_as_float(mn2 << 16), __uint_as_float(mn2 & 0xFFFF0000u));
+      mx = fmaxf(__uint_as_float(mx2 << 16), __uint_as_float(mx2 & 0xFFFF0000u));
     } else {
       for (int64_t i = threadIdx.x; i < K; i += blockDim.x) {
         const float v = __bfloat162float(p[i]);
@@ -61,16 +65,27 @@ __global__ void __launch_bounds__(256) int8_quantize_kernel(const __nv_bfloat16*
     const float inv = s_inv;
     int8_t* qo = q + row * K;
     if (vec) {
+      // bf16(w * inv) is ONE packed multiply (the fp32 product of two bf16 values is exact, so the reference's
+      // compute-in-fp32-then-round is a single rounding = mul.rn.bf16x2); clamp in bf16x2 (commutes with rint at the
+      // integer bounds); rint = add 1.5 * 2^23, whose low mantissa byte is then the two's-complement int8
+      const uint32_t ib = float_to_bf16_bits(inv), inv2 = ib | (ib << 16);
+      constexpr float kMagic = 12582912.0f;
       for (int64_t i = threadIdx.x; i < K / 8; i += blockDim.x) {
-        float f[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(p) + i), f);
-        uint32_t o[2] = {0, 0};
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + i);
+        const uint32_t r[4] = {v.x, v.y, v.z, v.w};
+        uint32_t u[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float r = fminf(fmaxf(rintf(bf16r(f[e] * inv)), -128.f), 127.f);
-          o[e >> 2] |= (static_cast<uint32_t>(static_cast<int>(r)) & 0xFFu) << (8 * (e & 3));
+        for (int e = 0; e < 4; ++e) {
+          uint32_t t2;
+          asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(t2) : "r"(r[e]), "r"(inv2));
+          asm("min.bf16x2 %0, %0, %1;" : "+r"(t2) : "r"(0x42FE42FEu));  // 127.0
+          asm("max.bf16x2 %0, %0, %1;" : "+r"(t2) : "r"(0xC300C300u));  // -128.0
+          u[2 * e] = __float_as_uint(__uint_as_float(t2 << 16) + kMagic);
+          u[2 * e + 1] = __float_as_uint(__uint_as_float(t2 & 0xFFFF0000u) + kMagic);
         }
-        *reinterpret_cast<uint2*>(qo + i * 8) = make_uint2(o[0], o[1]);
+        const uint32_t o0 = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
+        const uint32_t o1 = __byte_perm(__byte_perm(u[4], u[5], 0x0040), __byte_perm(u[6], u[7], 0x0040), 0x5410);
+        *reinterpret_cast<uint2*>(qo + i * 8) = make_uint2(o0, o1);
       }
     } else {
       for (int64_t i = threadIdx.x; i < K; i += blockDim.x) {
@@ -128,9 +143,13 @@ __global__ void __launch_bounds__(256) int8_unpack_kernel(const uint4* __restric
       const int64_t row = 16 * s + g + 8 * (j & 1), k0 = 64 * kt + 32 * h + 8 * c + 4 * (j >> 1);
       if (row >= N) continue;
       const uint32_t t = w[j] ^ 0x80808080u;
+      if (k0 + 4 <= K && (K & 3) == 0) {
+        *reinterpret_cast<uint32_t*>(q + row * K + k0) = t;
+      } else {
 #pragma unroll
-      for (int e = 0; e < 4; ++e)
-        if (k0 + e < K) q[row * K + k0 + e] = (int8_t)((t >> (8 * e)) & 0xFFu);
+        for (int e = 0; e < 4; ++e)
+          if (k0 + e < K) q[row * K + k0 + e] = (int8_t)((t >> (8 * e)) & 0xFFu);
+      }
     }
   }
 }
@@ -252,7 +271,7 @@ extern "C" int ao_b200_int8_pack(const int8_t* q, int64_t N, int64_t K, int64_t 
 
 extern "C" int ao_b200_int8_unpack(const void* packed, int64_t Np, int64_t Kp, int64_t N, int64_t K, int8_t* q, void* stream) {
   AO_CHECK_ARG(q && packed && N > 0 && K > 0 && Np >= N && Kp >= K && Np % 16 == 0 && Kp % 64 == 0);
-  AO_CHECK_ARG(ao_aligned(packed, 16));
+  AO_CHECK_ARG(ao_aligned(packed, 16) && ((K & 3) != 0 || ao_aligned(q, 4)));
   const int64_t total = (Np / 16) * (Kp / 64) * 64;
   const int64_t blocks = (total + 255) / 256;
   ao::int8_unpack_kernel<<<(unsigned)(blocks < 148 * 32 ? blocks : 148 * 32), 256, 0, static_cast<cudaStream_t>(stream)>>>(

@@ -29,6 +29,65 @@ __device__ __forceinline__ uint32_t tinygemm_quant1(float w, float min_val, floa
   return static_cast<uint32_t>(r);
 }
 
+// ---- fast exact path of the fused kernel -------------------------------------------------------------------------
+// The per-element work of _quantize_affine_tinygemm is  q = clamp(rint(bf16(bf16(w - min_val) / scale)), 0, 15).  Done
+// naively it is ~22 instructions per weight, four of them on the quarter-rate conversion pipe (two bf16 roundings,
+// rint, float->int) plus an IEEE division: the kernel ran at 13-20 % of the HBM roofline, instruction-bound.  Here:
+//   * min / max and the subtraction stay in packed bf16x2 (HMNMX2 / HADD2.BF16 round exactly like the reference's
+//     fp32-compute-then-round, and take one instruction per TWO weights);
+//   * the division is a * (1/s) + one Newton step with a reciprocal computed once per group.  Both operands carry 8
+//     significant bits, so the true quotient is either exactly representable in fp32 (then the residual is exact and
+//     the step returns it exactly) or at least 2^-18 (relative) away from any bf16 rounding boundary, while the step's
+//     error is < 2^-22: bf16(quotient) is the reference's value in every case;
+//   * rint is an add of 1.5 * 2^23 (round-to-nearest-even in the FMA pipe), the nibbles are assembled with FMAs
+//     (q * 16^slot, exact below 2^16) and converted to integer once per four weights.
+struct QFast {
+  float s, rs;        // scale and its reciprocal
+  uint32_t minv2;     // (min_val, min_val) as bf16x2
+};
+__device__ __forceinline__ uint32_t bf2_min(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("min.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_max(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_sub(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ float fast_quot(float a, const QFast& p) {
+  const float x0 = a * p.rs;
+  const float r = fmaf(-p.s, x0, a);
+  return fmaf(r, p.rs, x0);
+}
+// 8 weights (4 bf16x2 registers: element pairs (0,1) (2,3) (4,5) (6,7)) -> one packed word, nibble slots
+// [k0,k0+2,k0+4,k0+6,k0+1,k0+3,k0+5,k0+7]: even elements fill the low 16 bits, odd elements the high 16 bits
+__device__ __forceinline__ uint32_t quant_word_fast(const uint4& raw, const QFast& p) {
+  const uint32_t w2[4] = {raw.x, raw.y, raw.z, raw.w};
+  constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23
+  constexpr uint32_t k15 = 0x41704170u;  // (15.0, 15.0) bf16x2
+  float lo = 0.f, hi = 0.f, wgt = 1.f;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t a2 = bf2_sub(w2[j], p.minv2);                                  // bf16(w - min_val)
+    const float q0 = fast_quot(__uint_as_float(a2 << 16), p), q1 = fast_quot(__uint_as_float(a2 & 0xFFFF0000u), p);
+    uint32_t t2;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(t2) : "f"(q1), "f"(q0));            // bf16(a / scale)
+    t2 = bf2_max(bf2_min(t2, k15), 0u);                                           // clamp commutes with rint at 0 and 15
+    const float r0 = (__uint_as_float(t2 << 16) + kMagic) - kMagic;               // rint, ties to even
+    const float r1 = (__uint_as_float(t2 & 0xFFFF0000u) + kMagic) - kMagic;
+    lo = fmaf(r0, wgt, lo);
+    hi = fmaf(r1, wgt, hi);
+    wgt *= 16.f;
+  }
+  return static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+}
+
 // ---------------------------------------------------------------------------------------
 // Fused quantize + pack into the super-tile layout (include/ao_b200.h).  One warp owns a unit = 16 rows x UK columns, UK = max(G, 64):
 // it loads the unit's tiles in the strip layout's own lane order (so the packed words fall
@@ -62,54 +121,52 @@ __global__ void __launch_bounds__(256) int4_quantize_pack_kernel(
         raw[t][j] = (row < N && k0 < K) ? ldg128(w + row * ldw + k0) : make_uint4(0, 0, 0, 0);
       }
     }
-    // min / max per (row slot r = j&1, group gi)
-    float mn[2][NG], mx[2][NG];
+    // min / max per (row slot r = j&1, group gi), in packed bf16x2 (exact: comparisons only)
+    uint32_t mn2[2][NG], mx2[2][NG];
 #pragma unroll
     for (int r = 0; r < 2; ++r)
 #pragma unroll
       for (int gi = 0; gi < NG; ++gi) {
-        mn[r][gi] = INFINITY;
-        mx[r][gi] = -INFINITY;
+        mn2[r][gi] = 0x7F807F80u;  // (+inf, +inf)
+        mx2[r][gi] = 0xFF80FF80u;  // (-inf, -inf)
       }
 #pragma unroll
     for (int t = 0; t < T; ++t)
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float f[8];
-        unpack8(raw[t][j], f);
         const int gi = (NG == 2) ? (j >> 1) : 0;
+        const uint32_t v[4] = {raw[t][j].x, raw[t][j].y, raw[t][j].z, raw[t][j].w};
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          mn[j & 1][gi] = fminf(mn[j & 1][gi], f[i]);
-          mx[j & 1][gi] = fmaxf(mx[j & 1][gi], f[i]);
+        for (int i = 0; i < 4; ++i) {
+          mn2[j & 1][gi] = bf2_min(mn2[j & 1][gi], v[i]);
+          mx2[j & 1][gi] = bf2_max(mx2[j & 1][gi], v[i]);
         }
       }
     QParams qp[2][NG];
+    QFast qf[2][NG];
 #pragma unroll
     for (int r = 0; r < 2; ++r)
 #pragma unroll
       for (int gi = 0; gi < NG; ++gi) {
-        float a = mn[r][gi], b = mx[r][gi];
-        a = fminf(a, __shfl_xor_sync(0xffffffffu, a, 1));
-        a = fminf(a, __shfl_xor_sync(0xffffffffu, a, 2));
-        b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, 1));
-        b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, 2));
+        uint32_t a2 = mn2[r][gi], b2 = mx2[r][gi];
+        a2 = bf2_min(a2, __shfl_xor_sync(0xffffffffu, a2, 1));
+        a2 = bf2_min(a2, __shfl_xor_sync(0xffffffffu, a2, 2));
+        b2 = bf2_max(b2, __shfl_xor_sync(0xffffffffu, b2, 1));
+        b2 = bf2_max(b2, __shfl_xor_sync(0xffffffffu, b2, 2));
+        const float a = fminf(__uint_as_float(a2 << 16), __uint_as_float(a2 & 0xFFFF0000u));
+        const float b = fmaxf(__uint_as_float(b2 << 16), __uint_as_float(b2 & 0xFFFF0000u));
         qp[r][gi] = tinygemm_qparams(a, b, eps, div_mode);
+        qf[r][gi].s = qp[r][gi].scale;
+        qf[r][gi].rs = __frcp_rn(qp[r][gi].scale);
+        const uint32_t mb = float_to_bf16_bits(qp[r][gi].min_val);
+        qf[r][gi].minv2 = mb | (mb << 16);
       }
     // quantize + pack
 #pragma unroll
     for (int t = 0; t < T; ++t) {
       uint32_t words[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float f[8];
-        unpack8(raw[t][j], f);
-        const QParams p = qp[j & 1][(NG == 2) ? (j >> 1) : 0];
-        uint32_t word = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) word |= tinygemm_quant1(f[i], p.min_val, p.scale) << (4 * nib_slot(i));
-        words[j] = word;
-      }
+      for (int j = 0; j < 4; ++j) words[j] = quant_word_fast(raw[t][j], qf[j & 1][(NG == 2) ? (j >> 1) : 0]);
       const int64_t kt = uk * T + t;
       packed[tile_slot(strip, kt, Kp / 64) * 32 + lane] = make_uint4(words[0], words[1], words[2], words[3]);
     }
