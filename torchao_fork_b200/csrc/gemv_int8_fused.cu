@@ -284,36 +284,50 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
       }
     }
   } else {
-    for (int m = 0; m < p.M; ++m) {
-      float ss = 0.f, amax = 0.f;
+    // rows in batches of four: the four activation loads of a thread are in flight together (one exposed L2 round trip
+    // per batch instead of one per row)
+    for (int m0 = 0; m0 < p.M; m0 += 4) {
+      float ss4[4] = {0.f, 0.f, 0.f, 0.f}, am4[4] = {0.f, 0.f, 0.f, 0.f};
       for (int ci = tid; ci < chunks_per_row; ci += kCT) {
         const int64_t k0 = (int64_t)ci * 8;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (k0 < p.Kx) v = *reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0);
-        float f[8];
-        unpack8(v, f);
-        if (p.norm_w != nullptr && k0 < p.Kx) {
-          float wn[8];
-          unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
+        uint4 v4[4];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            ss = fmaf(f[e], f[e], ss);
-            f[e] = bf16r(f[e] * wn[e]);
-          }
-          uint32_t o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
-          v = make_uint4(o[0], o[1], o[2], o[3]);
+        for (int j = 0; j < 4; ++j) {
+          v4[j] = make_uint4(0, 0, 0, 0);
+          if (m0 + j < p.M && k0 < p.Kx) v4[j] = *reinterpret_cast<const uint4*>(p.x + (int64_t)(m0 + j) * p.ldx + k0);
         }
+        float wn[8];
+        const bool normed = p.norm_w != nullptr && k0 < p.Kx;
+        if (normed) unpack8(__ldg(reinterpret_cast<const uint4*>(p.norm_w + k0)), wn);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
-        *reinterpret_cast<uint4*>(x_s + (size_t)m * p.x_row_bytes + (size_t)ci * 16) = v;
+        for (int j = 0; j < 4; ++j) {
+          if (m0 + j >= p.M) break;
+          uint4 v = v4[j];
+          float f[8];
+          unpack8(v, f);
+          if (normed) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              ss4[j] = fmaf(f[e], f[e], ss4[j]);
+              f[e] = bf16r(f[e] * wn[e]);
+            }
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
+            v = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+#pragma unroll
+          for (int e = 0; e < 8; ++e) am4[j] = fmaxf(am4[j], fabsf(f[e]));
+          *reinterpret_cast<uint4*>(x_s + (size_t)(m0 + j) * p.x_row_bytes + (size_t)ci * 16) = v;
+        }
       }
-      ss = warp_sum8(ss);
-      amax = warp_max8(amax);
-      if (lane == 0) {
-        part[(m * k8Consumers + warp) * 2] = ss;
-        part[(m * k8Consumers + warp) * 2 + 1] = amax;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float ss = warp_sum8(ss4[j]), amax = warp_max8(am4[j]);
+        if (lane == 0 && m0 + j < p.M) {
+          part[((m0 + j) * k8Consumers + warp) * 2] = ss;
+          part[((m0 + j) * k8Consumers + warp) * 2 + 1] = amax;
+        }
       }
     }
     named_bar_sync(1, kCT);
