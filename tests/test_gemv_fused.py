@@ -30,7 +30,8 @@ def _quant(n, k, gs, seed):
     return packed, sz, (q - 8.0) * s + z
 
 
-SHAPES = [(4096, 4096), (1280, 8192), (512, 3584), (4096, 14336), (384, 1024)]
+# the last two are the K of the row-parallel wo / w2 shards of Llama-3-8B at TP = 8 (one partial stage, idle consumer warps)
+SHAPES = [(4096, 4096), (1280, 8192), (512, 3584), (4096, 14336), (384, 1024), (4096, 512), (4096, 1792)]
 
 
 @pytest.mark.parametrize("shape", SHAPES, ids=str)

@@ -45,7 +45,7 @@ def test_pack_matches_oracle_and_round_trips(shape):
     assert torch.equal(T.b200_int8_unpack(packed, n, k), q)
 
 
-SHAPES = [(4096, 4096), (1280, 8192), (512, 3584), (4096, 14336), (384, 1024), (1000, 4096 + 16)]
+SHAPES = [(4096, 4096), (1280, 8192), (512, 3584), (4096, 14336), (384, 1024), (1000, 4096 + 16), (4096, 512), (4096, 1792)]
 
 
 @pytest.mark.parametrize("shape", SHAPES, ids=str)
