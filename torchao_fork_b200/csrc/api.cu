@@ -55,12 +55,13 @@ struct Tunables {
     if (stages > 16) stages = 16;
     const char* pd = std::getenv("AO_B200_PDL");
     pdl = pd ? std::atoi(pd) : 1;
-    // tcgen05 / tensor-memory decode GEMV: 0 never, 1 wherever it applies, 2 (default) for large weights only — its
-    // steady-state rate is higher (5.2 vs 4.6 TB/s) but its per-launch cost is ~3 us more (no co-residency with its
-    // neighbours in a PDL chain: it takes the whole SM's shared and tensor memory)
+    // tcgen05 / tensor-memory decode GEMV: 0 never, 1 wherever it applies (before the integer-MMA kernel), 2 (default)
+    // for large weights that the integer-MMA kernel does not take (2 < M <= 5).  Against the fp16 mma.sync kernel its
+    // steady-state rate is higher (5.2 vs 4.6 TB/s) at ~3 us more per launch; the integer-MMA kernel beats it at every
+    // size (57344 x 8192, M = 1: 44.0 vs 51.7 us, profiles/r01c_gemv_70b_imma_vs_tc.jsonl)
     const char* tc = std::getenv("AO_B200_GEMV_TC");
     gemv_tc = tc ? std::atoi(tc) : 2;
-    // integer-MMA decode GEMV (M <= 2, G = 128; gemv_int4_imma.cu): 1 (default) wherever it applies, 0 never
+    // integer-MMA decode GEMV (M <= 2; gemv_int4_imma.cu): 1 (default) wherever it applies, 0 never
     const char* im = std::getenv("AO_B200_GEMV_IMMA");
     gemv_imma = im ? std::atoi(im) : 1;
   }
@@ -101,18 +102,23 @@ extern "C" int ao_b200_int4_mm(const void* x, int64_t M, int64_t Kx, int64_t ldx
   for (int64_t m0 = 0; m0 < M; m0 += 16) {
     const int64_t mc = (M - m0) < 16 ? (M - m0) : 16;
     int e = AO_B200_ERR_WORKSPACE;
-    if ((tunables().gemv_tc == 1 || (tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20)) && mc <= 5) {
-      e = ao::int4_gemv_tc(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out, ldy,
-                           nullptr, 0.f, nullptr, 0, 0, workspace, workspace_bytes, tunables().pdl != 0, s);
-      if (e == AO_B200_OK) continue;
-      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+    const bool tc_large = tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20;
+    for (int pass = 0; pass < 2; ++pass) {
+      // pass 0: tensor-memory kernel when forced; integer-MMA kernel; pass 1: tensor-memory kernel for large weights
+      if (((pass == 0 && tunables().gemv_tc == 1) || (pass == 1 && tc_large)) && mc <= 5) {
+        e = ao::int4_gemv_tc(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out,
+                             ldy, nullptr, 0.f, nullptr, 0, 0, workspace, workspace_bytes, tunables().pdl != 0, s);
+        if (e == AO_B200_OK) break;
+        if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+      }
+      if (pass == 0 && tunables().gemv_imma && mc <= 2) {
+        e = ao::int4_gemv_imma(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out,
+                               ldy, nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
+        if (e == AO_B200_OK) break;
+        if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+      }
     }
-    if (tunables().gemv_imma && mc <= 2 && group_size == 128) {
-      e = ao::int4_gemv_imma(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy, N_out, ldy,
-                             nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
-      if (e == AO_B200_OK) continue;
-      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
-    }
+    if (e == AO_B200_OK) continue;
     if (tunables().gemv_version == 3) {
       e = ao::int4_gemv_fused(xb + m0 * ldx, mc, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, yb + m0 * ldy,
                               N_out, ldy, nullptr, 0.f, nullptr, 0, 0, tunables().stages, tunables().pdl != 0, s);
@@ -142,18 +148,21 @@ extern "C" int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, int
   AO_CHECK_ARG(!norm_weight || ao_aligned(norm_weight, 16));
   if (!(group_size == 32 || group_size == 64 || group_size == 128 || group_size == 256)) return AO_B200_ERR_UNSUPPORTED;
   AO_CHECK_ARG(Kp % group_size == 0);
-  if (tunables().gemv_tc == 1 || (tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20)) {
-    // tensor-memory kernel (M <= 5, Np % 128 == 0, activations + >= 3 ring stages must fit); else the mma.sync kernel
-    const int e = ao::int4_gemv_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
-                                   norm_eps, residual, ld_res, epilogue, workspace, workspace_bytes, tunables().pdl != 0,
-                                   static_cast<cudaStream_t>(stream));
-    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
-  }
-  if (tunables().gemv_imma && M <= 2 && group_size == 128) {
-    const int e = ao::int4_gemv_imma(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
-                                     norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,
+  const bool tc_large = tunables().gemv_tc == 2 && Np * Kp >= (int64_t)192 << 20;
+  for (int pass = 0; pass < 2; ++pass) {
+    if ((pass == 0 && tunables().gemv_tc == 1) || (pass == 1 && tc_large)) {
+      // tensor-memory kernel (M <= 5, Np % 128 == 0, activations + >= 3 ring stages must fit); else the mma.sync kernels
+      const int e = ao::int4_gemv_tc(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
+                                     norm_eps, residual, ld_res, epilogue, workspace, workspace_bytes, tunables().pdl != 0,
                                      static_cast<cudaStream_t>(stream));
-    if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+    }
+    if (pass == 0 && tunables().gemv_imma && M <= 2) {
+      const int e = ao::int4_gemv_imma(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
+                                       norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,
+                                       static_cast<cudaStream_t>(stream));
+      if (e != AO_B200_ERR_WORKSPACE && e != AO_B200_ERR_UNSUPPORTED) return e;
+    }
   }
   return ao::int4_gemv_fused(x, M, Kx, ldx, packed, scale_and_zero, Np, Kp, group_size, y, N_out, ldy, norm_weight,
                              norm_eps, residual, ld_res, epilogue, tunables().stages, tunables().pdl != 0,

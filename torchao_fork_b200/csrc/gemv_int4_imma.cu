@@ -1,4 +1,4 @@
-// int4 weight-only linear, decode path for M <= 2 and G = 128: the integer-tensor-core sibling of gemv_int4_fused.cu.
+// int4 weight-only linear, decode path for M <= 2 (every group size): the integer-tensor-core sibling of gemv_int4_fused.cu.
 //
 // Same skeleton (strip-parallel, one 16 KB bulk copy + one scale/zero copy per stage into a shared-memory ring, 16
 // consumer warps, producer warp, epilogue warp, PDL, RMSNorm prologue, residual / SiLU*mul epilogues), but the inner
@@ -9,10 +9,11 @@
 //   * the activation row is staged ONCE per CTA as 23-bit fixed point (per-row power-of-two scale, exact for every bf16
 //     value within 2^-15 of the row's maximum) split into three balanced int8 limbs, and the limbs ride in three of the
 //     eight MMA columns (M = 2: six), so the three partial products cost nothing extra;
-//   * int32 accumulation over a 128-k group is exact; the accumulators start at the integer image of 1.5 * 2^23, so
-//     int -> float is one subtraction; the affine dequant is applied per group on the accumulator in fp32,
-//         y[col] += s_g * acc_g[col] + (z_g - 8 s_g) * S_g[col],   S_g[col] = sum of the limb over the group,
-//     and the limbs are recombined (65536 a + 256 b + c) once per strip in the epilogue warp.
+//   * int32 accumulation over a segment (min(G, 128) k of one group) is exact; the accumulators start at the integer image
+//     of 1.5 * 2^23, so int -> float is one subtraction; the affine dequant is applied per segment on the accumulator in fp32,
+//         y[col] += s_g * acc[col] + (z_g - 8 s_g) * S[col],   S[col] = sum of the limb over the segment,
+//     and the limbs are recombined (65536 a + 256 b + c) once per strip in the epilogue warp.  A warp's share of a stage
+//     is 128 k: one segment at G >= 128 (G = 256: two warps share a group's scale / zero), two at G = 64, four at G = 32.
 // Arithmetic: fp32-dequant semantics, like gemv_int4_fused.cu; the products are exact integers.
 #include <cstdlib>
 
@@ -25,22 +26,28 @@ constexpr int kIThreads = (kIConsumers + 2) * 32;
 constexpr int kIRedBufs = 2;
 constexpr int kIStageTiles = 32;                       // 64-k tiles per stage: 2 per consumer warp = one 128-k group
 constexpr int kIStageW = kIStageTiles * 512;           // 16 KB of packed weights
-constexpr int kIStageSZ = (kIStageTiles / 2) * 64;     // 16 groups x 16 rows x (scale | zero << 16)
-constexpr int kIStageBytes = kIStageW + kIStageSZ;
+template <int G>
+struct IGeom {
+  static constexpr int kSegK = G < 128 ? G : 128;        // k covered by one accumulator fix-up
+  static constexpr int kNSeg = 128 / kSegK;              // segments in a warp's 128 k of a stage
+  static constexpr int kSegLanes = kSegK / 8;            // 8-element chunks (= staging lanes) per segment
+  static constexpr int kStageSZ = (kIStageTiles * 64 / G) * 64;  // groups of a stage x 16 rows x (scale | zero << 16)
+  static constexpr int kStageBytes = kIStageW + kStageSZ;
+};
 constexpr uint32_t kIMagicI = 0x4B400000u;             // bits of 1.5 * 2^23: int adds land in the mantissa (ulp 1)
 constexpr float kIMagicF = 12582912.0f;
 
 struct GemvIParams {
   const uint8_t* packed;          // strip-major [Np/16][Kp/64][512 B]
-  const uint32_t* sz;             // strip-major [Np/16][Kp/128][16] (scale | zero << 16)
+  const uint32_t* sz;             // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
   const __nv_bfloat16* x;
   const __nv_bfloat16* norm_w;
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;
   int M, stages, epilogue, hold;
-  int KT;                         // Kp / 64 (even: Kp % 128 == 0)
+  int KT;                         // Kp / 64 (Kp % max(G, 128) == 0)
   int64_t Kx, ldx, N_out, ldy, ld_res;
-  int n_strips, strips_base, strips_rem;
+  int n_strips, strips_base, strips_rem;  // CTA b owns strips [b base + min(b, rem), ...)
   float eps;
   uint32_t limb_row_bytes;        // Kp + 32 (row stride = 32 mod 128: the limb rows of one load sit in different banks)
   uint32_t off_x, off_S, off_red, off_misc;
@@ -70,11 +77,17 @@ __device__ __forceinline__ uint2 lds64u(uint32_t a) {
   return v;
 }
 
+// NH > 0: M = 1 and every thread owns <= NH 8-element chunks of the activation row (register-held staging); NH = 0: the
+// general two-pass staging.  One instantiation per case: the staging code runs once per launch, instruction-cache cold,
+// so what is not needed is not compiled in.
+template <int G, int NH>
 __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const GemvIParams p) {
+  using GE = IGeom<G>;
+  constexpr int kIStageBytes = GE::kStageBytes;
   extern __shared__ __align__(128) uint8_t smem_i[];
   uint8_t* ring = smem_i;
   uint8_t* x_s = smem_i + p.off_x;                             // [3 M limb rows][limb_row_bytes] int8, k permuted per 8
-  float* S_s = reinterpret_cast<float*>(smem_i + p.off_S);     // [Kp/128][8 cols]: limb sums of the group
+  float* S_s = reinterpret_cast<float*>(smem_i + p.off_S);     // [Kp/kSegK][8 cols]: limb sums of the segment
   float* red = reinterpret_cast<float*>(smem_i + p.off_red);   // [2][16 warps][32][4]
   float* part = reinterpret_cast<float*>(smem_i + p.off_misc); // [2 rows][16 warps][2 = {sum sq, amax}]
   float* row_scale = part + 2 * kIConsumers * 2;               // [2]: 2^-e (* rsqrt(mean sq + eps))
@@ -89,7 +102,6 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   const int b = blockIdx.x;
   const int s0 = b * p.strips_base + min(b, p.strips_rem), s1 = s0 + p.strips_base + (b < p.strips_rem ? 1 : 0);
   const int KT = p.KT;
-  const int n_chunks = (KT + kIStageTiles - 1) / kIStageTiles;
 
   grid_launch_dependents();
 
@@ -111,17 +123,17 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
     if (lane == 0) {
       int slot = 0;
       uint32_t par = 1;
-      const int n_groups = KT / 2;
+      const int n_groups = KT * 64 / G;
       for (int strip = s0; strip < s1; ++strip) {
         const uint8_t* wrow = p.packed + (int64_t)strip * KT * 512;
         const uint32_t* srow = p.sz + (int64_t)strip * n_groups * 16;
-        for (int ch = 0; ch < n_chunks; ++ch) {
-          const int kt0 = ch * kIStageTiles;
+        for (int kt0 = 0; kt0 < KT; kt0 += kIStageTiles) {
           const int cnt = min(kIStageTiles, KT - kt0);
           uint8_t* dst = ring + (size_t)slot * kIStageBytes;
           mbar_wait(&empty[slot], par);
-          mbar_arrive_expect_tx(&full[slot], (uint32_t)(cnt * 512 + (cnt / 2) * 64));
-          bulk_g2s(dst + kIStageW, srow + (int64_t)(kt0 / 2) * 16, (uint32_t)((cnt / 2) * 64), &full[slot]);
+          const uint32_t sz_bytes = (uint32_t)(cnt * 64 / G) * 64u;
+          mbar_arrive_expect_tx(&full[slot], (uint32_t)(cnt * 512) + sz_bytes);
+          bulk_g2s(dst + kIStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, &full[slot]);
           bulk_g2s(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), &full[slot]);
           if (++slot == stages) {
             slot = 0;
@@ -162,8 +174,7 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
       t.z = __shfl_down_sync(0xffffffffu, v.z, 1);
       t.w = __shfl_down_sync(0xffffffffu, v.w, 1);
       const int m = c;
-      if (m >= p.M || m > 1) continue;
-      float r0, r1;
+      float r0, r1;  // lanes c = 0, 1: rows g, g + 8 of activation row c (other lanes: don't care)
       if (m == 0) {
         r0 = fmaf(65536.f, v.x, fmaf(256.f, v.y, t.x));
         r1 = fmaf(65536.f, v.z, fmaf(256.f, v.w, t.z));
@@ -171,6 +182,7 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
         r0 = fmaf(65536.f, v.y, fmaf(256.f, t.x, t.y));
         r1 = fmaf(65536.f, v.w, fmaf(256.f, t.z, t.w));
       }
+      if (m >= p.M || m > 1) continue;
       const float rsc = row_scale[m];
       const float v0 = r0 * rsc, v1 = r1 * rsc;
       if (p.epilogue == 2) {
@@ -199,13 +211,13 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   const int g = lane >> 2, c = lane & 3;
   const int tid = threadIdx.x;  // 0 .. 511
   constexpr int kCT = kIConsumers * 32;
-  constexpr int kHold = 4;            // chunks a thread keeps in registers between the two staging passes
+  constexpr int kHold = NH > 0 ? NH : 1;  // chunks a thread keeps in registers between the two staging passes
   const int chunks_per_row = KT * 8;  // 8-element chunks over Kp
   const int n_iter = (chunks_per_row + kCT - 1) / kCT;
   // Fast path (M = 1, Kp <= 16384): every thread owns <= 4 chunks; all of their loads are issued at once and the
   // normalised bf16 values stay in registers between the two passes.  The norm weights do not depend on the previous
   // kernel, so they are fetched BEFORE the dependency wait (they are a DRAM miss: read once per token).
-  const bool hold = p.hold != 0 && p.M == 1 && n_iter <= kHold;
+  constexpr bool hold = NH > 0;  // host: p.M == 1 && n_iter <= NH
   uint4 xr[kHold], wn4[kHold];
 #pragma unroll
   for (int i = 0; i < kHold; ++i) xr[i] = wn4[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -234,7 +246,7 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
     }
   };
   {
-    if (hold) {
+    if constexpr (hold) {
       float ss = 0.f, amax = 0.f;
 #pragma unroll
       for (int i = 0; i < kHold; ++i) {
@@ -341,19 +353,19 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
         *reinterpret_cast<uint2*>(rows + p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[1][0], lw[1][1]);
         *reinterpret_cast<uint2*>(rows + 2 * p.limb_row_bytes + (size_t)ci * 8) = make_uint2(lw[2][0], lw[2][1]);
       }
-      // a 128-k group = 16 consecutive chunks = 16 consecutive lanes (kCT % 16 == 0)
+      // a segment = kSegLanes consecutive chunks = consecutive lanes (kCT % 16 == 0)
 #pragma unroll
-      for (int o = 8; o; o >>= 1) {
+      for (int o = GE::kSegLanes / 2; o; o >>= 1) {
         sl0 += __shfl_xor_sync(0xffffffffu, sl0, o);
         sl1 += __shfl_xor_sync(0xffffffffu, sl1, o);
         sl2 += __shfl_xor_sync(0xffffffffu, sl2, o);
       }
-      if (valid && (ci & 15) == 0) {
-        float* S = S_s + (ci >> 4) * 8 + 3 * m;
+      if (valid && (ci % GE::kSegLanes) == 0) {
+        float* S = S_s + (ci / GE::kSegLanes) * 8 + 3 * m;
         S[0] = (float)sl0; S[1] = (float)sl1; S[2] = (float)sl2;
       }
     };
-    if (hold) {
+    if constexpr (hold) {
 #pragma unroll
       for (int it = 0; it < kHold; ++it) {
         if (it < n_iter) {
@@ -384,11 +396,11 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   // meets the producer, which initialised the mbarriers long ago
   named_bar_sync(2, kIThreads);
 
-  // ---- main loop: warp w owns k-tiles 2 w, 2 w + 1 (= group w) of every stage ----
+  // ---- main loop: warp w owns k-tiles 2 w, 2 w + 1 (128 k) of every stage ----
   const uint32_t ring_u = smem_u32(ring);
   uint32_t w_off = (uint32_t)warp * 1024u + (uint32_t)lane * 16u;
-  uint32_t sz_off = (uint32_t)kIStageW + (uint32_t)warp * 64u + (uint32_t)g * 4u;
-  uint32_t S_u0 = smem_u32(S_s) + (uint32_t)warp * 32u + (uint32_t)c * 8u;
+  uint32_t sz_off = (uint32_t)kIStageW + (uint32_t)(G >= 128 ? warp * 128 / G : warp * GE::kNSeg) * 64u + (uint32_t)g * 4u;
+  uint32_t S_u0 = smem_u32(S_s) + (uint32_t)(warp * GE::kNSeg) * 32u + (uint32_t)c * 8u;
   const bool x_on = g < 3 * p.M;  // MMA column g = (activation row g / 3, limb g % 3)
   uint32_t x_u0 = smem_u32(x_s) + (uint32_t)min(g, 3 * p.M - 1) * p.limb_row_bytes + (uint32_t)warp * 128u + (uint32_t)c * 8u;
   asm volatile("" : "+r"(w_off), "+r"(sz_off), "+r"(S_u0), "+r"(x_u0));
@@ -399,35 +411,57 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   for (int strip = s0; strip < s1; ++strip) {
     float yacc[4] = {0.f, 0.f, 0.f, 0.f};
     uint32_t xo = 0, S_u = S_u0;
-    for (int ch = 0; ch < n_chunks; ++ch) {
+    for (int kt0 = 0; kt0 < KT; kt0 += kIStageTiles) {
       mbar_wait(&full[slot], par);
-      if (2 * warp < KT - ch * kIStageTiles) {
+      if (2 * warp < KT - kt0) {
         const uint4 wa = lds128(stage_u + w_off), wb = lds128(stage_u + w_off + 512u);
         uint2 xb[4];
 #pragma unroll
         for (int h = 0; h < 4; ++h) xb[h] = x_on ? lds64u(x_u0 + xo + 32u * h) : make_uint2(0u, 0u);
-        const uint32_t p0 = lds32(stage_u + sz_off), p1 = lds32(stage_u + sz_off + 32u);
-        const float2 S = lds64f(S_u);
-        int a0[4] = {(int)kIMagicI, (int)kIMagicI, (int)kIMagicI, (int)kIMagicI}, a1[4] = {0, 0, 0, 0};
         constexpr uint32_t kM = 0x0f0f0f0fu;
         // half h: words (row g, row g + 8); low nibbles = k (k0, k0+4, k0+1, k0+5), high nibbles = (k0+2, k0+6, k0+3, k0+7)
-        imma_16832(a0, wa.x & kM, wa.y & kM, (wa.x >> 4) & kM, (wa.y >> 4) & kM, xb[0].x, xb[0].y);
-        imma_16832(a1, wa.z & kM, wa.w & kM, (wa.z >> 4) & kM, (wa.w >> 4) & kM, xb[1].x, xb[1].y);
-        imma_16832(a0, wb.x & kM, wb.y & kM, (wb.x >> 4) & kM, (wb.y >> 4) & kM, xb[2].x, xb[2].y);
-        imma_16832(a1, wb.z & kM, wb.w & kM, (wb.z >> 4) & kM, (wb.w >> 4) & kM, xb[3].x, xb[3].y);
-        const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
-        const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0 & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1 & 0xFFFF0000u));
-        const float f0 = __int_as_float(a0[0] + a1[0]) - kIMagicF, f1 = __int_as_float(a0[1] + a1[1]) - kIMagicF;
-        const float f2 = __int_as_float(a0[2] + a1[2]) - kIMagicF, f3 = __int_as_float(a0[3] + a1[3]) - kIMagicF;
-        yacc[0] = fmaf(sc0, f0, fmaf(zz0, S.x, yacc[0]));
-        yacc[1] = fmaf(sc0, f1, fmaf(zz0, S.y, yacc[1]));
-        yacc[2] = fmaf(sc1, f2, fmaf(zz1, S.x, yacc[2]));
-        yacc[3] = fmaf(sc1, f3, fmaf(zz1, S.y, yacc[3]));
+        const uint32_t wl[4][2] = {{wa.x, wa.y}, {wa.z, wa.w}, {wb.x, wb.y}, {wb.z, wb.w}};
+        if constexpr (GE::kNSeg == 1) {
+          const uint32_t p0 = lds32(stage_u + sz_off), p1 = lds32(stage_u + sz_off + 32u);
+          const float2 S = lds64f(S_u);
+          int a0[4] = {(int)kIMagicI, (int)kIMagicI, (int)kIMagicI, (int)kIMagicI}, a1[4] = {0, 0, 0, 0};
+          imma_16832(a0, wl[0][0] & kM, wl[0][1] & kM, (wl[0][0] >> 4) & kM, (wl[0][1] >> 4) & kM, xb[0].x, xb[0].y);
+          imma_16832(a1, wl[1][0] & kM, wl[1][1] & kM, (wl[1][0] >> 4) & kM, (wl[1][1] >> 4) & kM, xb[1].x, xb[1].y);
+          imma_16832(a0, wl[2][0] & kM, wl[2][1] & kM, (wl[2][0] >> 4) & kM, (wl[2][1] >> 4) & kM, xb[2].x, xb[2].y);
+          imma_16832(a1, wl[3][0] & kM, wl[3][1] & kM, (wl[3][0] >> 4) & kM, (wl[3][1] >> 4) & kM, xb[3].x, xb[3].y);
+          const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
+          const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0 & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1 & 0xFFFF0000u));
+          const float f0 = __int_as_float(a0[0] + a1[0]) - kIMagicF, f1 = __int_as_float(a0[1] + a1[1]) - kIMagicF;
+          const float f2 = __int_as_float(a0[2] + a1[2]) - kIMagicF, f3 = __int_as_float(a0[3] + a1[3]) - kIMagicF;
+          yacc[0] = fmaf(sc0, f0, fmaf(zz0, S.x, yacc[0]));
+          yacc[1] = fmaf(sc0, f1, fmaf(zz0, S.y, yacc[1]));
+          yacc[2] = fmaf(sc1, f2, fmaf(zz1, S.x, yacc[2]));
+          yacc[3] = fmaf(sc1, f3, fmaf(zz1, S.y, yacc[3]));
+        } else {
+          constexpr int kHS = 4 / GE::kNSeg;  // 32-k halves per segment
+#pragma unroll
+          for (int sg = 0; sg < GE::kNSeg; ++sg) {
+            const uint32_t p0 = lds32(stage_u + sz_off + 64u * sg), p1 = lds32(stage_u + sz_off + 64u * sg + 32u);
+            const float2 S = lds64f(S_u + 32u * sg);
+            int a[4] = {(int)kIMagicI, (int)kIMagicI, (int)kIMagicI, (int)kIMagicI};
+#pragma unroll
+            for (int hh = 0; hh < kHS; ++hh) {
+              const int h = sg * kHS + hh;
+              imma_16832(a, wl[h][0] & kM, wl[h][1] & kM, (wl[h][0] >> 4) & kM, (wl[h][1] >> 4) & kM, xb[h].x, xb[h].y);
+            }
+            const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
+            const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0 & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1 & 0xFFFF0000u));
+            yacc[0] = fmaf(sc0, __int_as_float(a[0]) - kIMagicF, fmaf(zz0, S.x, yacc[0]));
+            yacc[1] = fmaf(sc0, __int_as_float(a[1]) - kIMagicF, fmaf(zz0, S.y, yacc[1]));
+            yacc[2] = fmaf(sc1, __int_as_float(a[2]) - kIMagicF, fmaf(zz1, S.x, yacc[2]));
+            yacc[3] = fmaf(sc1, __int_as_float(a[3]) - kIMagicF, fmaf(zz1, S.y, yacc[3]));
+          }
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
       xo += kIStageTiles * 64u;
-      S_u += (kIStageTiles / 2) * 32u;
+      S_u += (kIStageTiles * 64 / GE::kSegK) * 32u;
       stage_u += kIStageBytes;
       if (++slot == stages) {
         slot = 0;
@@ -454,18 +488,20 @@ struct PlanI {
   uint32_t off_x, off_S, off_red, off_misc, limb_row_bytes;
 };
 
-static bool plan_imma(int M, int64_t Kp, int max_stages, PlanI& pl) {
+static bool plan_imma(int M, int64_t Kp, int G, int max_stages, PlanI& pl) {
+  const int seg_k = G < 128 ? G : 128;
+  const size_t kIStageBytes = (size_t)kIStageW + (size_t)(kIStageTiles * 64 / G) * 64;
   pl.limb_row_bytes = (uint32_t)(Kp + 32);
   const size_t x_bytes = ((size_t)3 * M * pl.limb_row_bytes + 127) / 128 * 128;
-  const size_t S_bytes = ((size_t)(Kp / 128) * 32 + 127) / 128 * 128;
+  const size_t S_bytes = ((size_t)(Kp / seg_k) * 32 + 127) / 128 * 128;
   const size_t red_bytes = (size_t)kIRedBufs * kIConsumers * 128 * 4;
   const size_t misc = (2 * kIConsumers * 2 + 4) * 4 + (2 * 16 + 2 * kIRedBufs) * 8 + 64;
   const size_t fixed = x_bytes + S_bytes + red_bytes + misc;
   const size_t two_per_sm = 113 * 1024, one_per_sm = 226 * 1024;
   int st = 0;
-  if (fixed + 4 * (size_t)kIStageBytes <= two_per_sm) {
+  if (fixed + 4 * kIStageBytes <= two_per_sm) {
     st = (int)((two_per_sm - fixed) / kIStageBytes);
-  } else if (fixed + 3 * (size_t)kIStageBytes <= one_per_sm) {
+  } else if (fixed + 3 * kIStageBytes <= one_per_sm) {
     st = (int)((one_per_sm - fixed) / kIStageBytes);
   } else {
     return false;
@@ -482,11 +518,11 @@ static bool plan_imma(int M, int64_t Kp, int max_stages, PlanI& pl) {
   return true;
 }
 
-// M <= 2, G == 128.  Returns AO_B200_ERR_UNSUPPORTED / AO_B200_ERR_WORKSPACE when the shape is not for this kernel.
+// M <= 2, G in {32, 64, 128, 256}.  Returns AO_B200_ERR_UNSUPPORTED / AO_B200_ERR_WORKSPACE when the shape is not for this kernel.
 int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void* packed, const void* sz, int64_t Np,
                    int64_t Kp, int G, void* y, int64_t N_out, int64_t ldy, const void* norm_w, float eps,
                    const void* residual, int64_t ld_res, int epilogue, int max_stages, bool pdl, cudaStream_t s) {
-  if (M > 2 || G != 128 || Kp % 128 != 0) return AO_B200_ERR_UNSUPPORTED;
+  if (M > 2 || (G != 32 && G != 64 && G != 128 && G != 256) || Kp % (G > 128 ? G : 128) != 0) return AO_B200_ERR_UNSUPPORTED;
   (void)Np;
   GemvIParams p;
   p.packed = static_cast<const uint8_t*>(packed);
@@ -506,15 +542,26 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
   p.n_strips = (int)((N_out + 15) / 16);
   p.eps = eps;
   PlanI pl;
-  if (!plan_imma((int)M, Kp, max_stages, pl)) return AO_B200_ERR_WORKSPACE;
+  if (!plan_imma((int)M, Kp, G, max_stages, pl)) return AO_B200_ERR_WORKSPACE;
   p.stages = pl.stages;
   p.limb_row_bytes = pl.limb_row_bytes;
   p.off_x = pl.off_x; p.off_S = pl.off_S; p.off_red = pl.off_red; p.off_misc = pl.off_misc;
-  static bool attr_done = false;
-  if (!attr_done) {
-    if (cudaFuncSetAttribute(int4_gemv_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+  using KernelFn = void (*)(const GemvIParams);
+  static const KernelFn kernels[4][4] = {
+      {int4_gemv_imma_kernel<32, 0>, int4_gemv_imma_kernel<32, 1>, int4_gemv_imma_kernel<32, 2>, int4_gemv_imma_kernel<32, 4>},
+      {int4_gemv_imma_kernel<64, 0>, int4_gemv_imma_kernel<64, 1>, int4_gemv_imma_kernel<64, 2>, int4_gemv_imma_kernel<64, 4>},
+      {int4_gemv_imma_kernel<128, 0>, int4_gemv_imma_kernel<128, 1>, int4_gemv_imma_kernel<128, 2>, int4_gemv_imma_kernel<128, 4>},
+      {int4_gemv_imma_kernel<256, 0>, int4_gemv_imma_kernel<256, 1>, int4_gemv_imma_kernel<256, 2>, int4_gemv_imma_kernel<256, 4>}};
+  const int gi = G == 32 ? 0 : (G == 64 ? 1 : (G == 128 ? 2 : 3));
+  // register-held staging: M = 1 and <= 4 chunks of 8 activations per consumer thread (Kp <= 16384)
+  const int n_iter = (p.KT * 8 + kIConsumers * 32 - 1) / (kIConsumers * 32);
+  const int hi = (p.hold != 0 && M == 1 && n_iter <= 4) ? (n_iter <= 1 ? 1 : (n_iter <= 2 ? 2 : 3)) : 0;
+  const KernelFn kern = kernels[gi][hi];
+  static bool attr_done[4][4] = {};
+  if (!attr_done[gi][hi]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
       return AO_B200_ERR_CUDA;
-    attr_done = true;
+    attr_done[gi][hi] = true;
   }
   static int sms = 0;
   if (sms == 0) {
@@ -528,14 +575,15 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
   static const int ctas = []() { const char* e = std::getenv("AO_B200_IMMA_CTAS"); const int v = e ? std::atoi(e) : 2; return v < 1 ? 1 : (v > 2 ? 2 : v); }();
   static const int one_below = []() { const char* e = std::getenv("AO_B200_IMMA_CTAS1_BELOW"); return e ? std::atoi(e) : 0; }();
   const int max_grid = sms * (pl.smem <= 113 * 1024 ? (p.n_strips <= one_below ? 1 : ctas) : 1);
-  // balanced waves: every CTA gets the same number of strips (+-1 at most on the last few), e.g. 1792 strips on 296 slots
-  // -> 256 CTAs x 7 instead of 16 CTAs with a 7th strip while 280 idle
   int grid = p.n_strips < max_grid ? p.n_strips : max_grid;
   {
+    // balanced waves (off by default: slower in the decode step): every CTA gets the same number of strips
     static const bool balance = []() { const char* e = std::getenv("AO_B200_BALANCE"); return e ? std::atoi(e) != 0 : false; }();
     const int per = (p.n_strips + grid - 1) / grid;
     if (balance) grid = (p.n_strips + per - 1) / per;
   }
+  // (Splitting strips along K between CTAs — 256-k units, parked partial sums + tickets — was tried and removed: wherever
+  // it applied the launch got 3 - 4 us slower, more than the balance won; profiles/r01c_imma_splitk_ab.txt.)
   p.strips_base = p.n_strips / grid;
   p.strips_rem = p.n_strips % grid;
   cudaLaunchConfig_t cfg{};
@@ -548,7 +596,7 @@ int int4_gemv_imma(const void* x, int64_t M, int64_t Kx, int64_t ldx, const void
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  if (cudaLaunchKernelEx(&cfg, int4_gemv_imma_kernel, p) != cudaSuccess) return AO_B200_ERR_CUDA;
+  if (cudaLaunchKernelEx(&cfg, kern, p) != cudaSuccess) return AO_B200_ERR_CUDA;
   return ao_launch_status();
 }
 
