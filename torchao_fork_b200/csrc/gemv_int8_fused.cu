@@ -68,7 +68,10 @@ __device__ __forceinline__ void mma8_f16_16816(float (&d)[4], uint32_t a0, uint3
 __device__ __forceinline__ uint32_t u8_f16_lo(uint32_t w) { return __byte_perm(w, 0x64646464u, 0x4140); }
 __device__ __forceinline__ uint32_t u8_f16_hi(uint32_t w) { return __byte_perm(w, 0x64646464u, 0x4342); }
 
-template <int MT>
+// NH > 0: M = 1 and every consumer thread owns <= NH chunks of the activation row (register-held staging); NH = 0: the
+// general staging.  One instantiation per case — the staging code runs once per launch with a cold instruction cache, so
+// code that a launch does not need is not compiled into its kernel (profiles/r01c_imma_code_size_ab.txt).
+template <int MT, int NH>
 __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_kernel(const Gemv8Params p) {
   extern __shared__ __align__(128) uint8_t smem8[];
   uint8_t* ring = smem8;
@@ -192,13 +195,13 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
   const int g = lane >> 2, c = lane & 3;
   const int tid = threadIdx.x;  // 0 .. 511
   constexpr int kCT = k8Consumers * 32;
-  constexpr int kHold = 4;            // chunks a thread keeps in registers between the two staging passes
+  constexpr int kHold = NH > 0 ? NH : 1;  // chunks a thread keeps in registers between the two staging passes
   const int chunks_per_row = KT * 8;  // 16-byte chunks of 8 elements over Kp
   const int n_iter = (chunks_per_row + kCT - 1) / kCT;
   // Fast path (M = 1, Kp <= 16384): every thread owns <= 4 chunks, all of their loads are issued at once, the normalised
   // bf16 values stay in registers between the two passes, every warp reduces the row statistics itself, and the norm
   // weights (independent of the previous kernel, a DRAM miss) are fetched BEFORE the dependency wait.
-  const bool hold = p.M == 1 && n_iter <= kHold;
+  constexpr bool hold = NH > 0;  // host: p.M == 1 && n_iter <= NH
   uint4 xr[kHold], wn4[kHold];
 #pragma unroll
   for (int i = 0; i < kHold; ++i) xr[i] = wn4[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
   grid_dependency_wait();
 
   // ---- stage the activations: x (* norm_w) -> per-row power-of-two scaling -> fp16; per-64-k correction sums ----
-  if (hold) {
+  if constexpr (hold) {
     float ss = 0.f, amax = 0.f;
 #pragma unroll
     for (int i = 0; i < kHold; ++i) {
@@ -497,11 +500,11 @@ static int sm_count8() {
   return n;
 }
 
-template <int MT>
+template <int MT, int NH>
 static int launch8(Gemv8Params& p, const Plan8& pl, bool pdl, cudaStream_t s) {
   static bool attr_done = false;
   if (!attr_done) {
-    if (cudaFuncSetAttribute(int8_gemv_fused_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
+    if (cudaFuncSetAttribute(int8_gemv_fused_kernel<MT, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess)
       return AO_B200_ERR_CUDA;
     attr_done = true;
   }
@@ -526,7 +529,7 @@ static int launch8(Gemv8Params& p, const Plan8& pl, bool pdl, cudaStream_t s) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  if (cudaLaunchKernelEx(&cfg, int8_gemv_fused_kernel<MT>, p) != cudaSuccess) return AO_B200_ERR_CUDA;
+  if (cudaLaunchKernelEx(&cfg, int8_gemv_fused_kernel<MT, NH>, p) != cudaSuccess) return AO_B200_ERR_CUDA;
   return ao_launch_status();
 }
 
@@ -554,7 +557,13 @@ int int8_gemv_fused(const void* x, int64_t M, int64_t Kx, int64_t ldx, const voi
   p.stages = pl.stages;
   p.x_row_bytes = pl.x_row_bytes;
   p.off_x = pl.off_x; p.off_C = pl.off_C; p.off_red = pl.off_red; p.off_misc = pl.off_misc;
-  return MT == 1 ? launch8<1>(p, pl, pdl, s) : launch8<2>(p, pl, pdl, s);
+  if (MT == 2) return launch8<2, 0>(p, pl, pdl, s);
+  // register-held staging: M = 1 and <= 4 chunks of 8 activations per consumer thread (Kp <= 16384)
+  const int n_iter = (p.KT * 8 + k8Consumers * 32 - 1) / (k8Consumers * 32);
+  if (M == 1 && n_iter <= 1) return launch8<1, 1>(p, pl, pdl, s);
+  if (M == 1 && n_iter <= 2) return launch8<1, 2>(p, pl, pdl, s);
+  if (M == 1 && n_iter <= 4) return launch8<1, 4>(p, pl, pdl, s);
+  return launch8<1, 0>(p, pl, pdl, s);
 }
 
 }  // namespace ao
