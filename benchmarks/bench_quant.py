@@ -60,6 +60,28 @@ def ref_eager_int8(w):  # quant_primitives.py:1537-1565, :453-456
     return scale, q
 
 
+def ref_eager_hqq(w, gs):  # quant_primitives.py:1915-1973, 2035-2090 restated with torch ops (fp32), as the reference runs it
+    W = w.float().reshape(-1, gs)
+    mn, mx = W.min(dim=1, keepdim=True)[0], W.max(dim=1, keepdim=True)[0]
+    scale = (15 / (mx - mn)).clamp(max=2e4)
+    zero = torch.round(-mn * scale)
+    beta, best = 10.0, 1e4
+    for _ in range(20):
+        Wq = torch.round(W * scale + zero).clamp(0, 15)
+        Wr = (Wq - zero) / scale
+        d = W - Wr
+        We = torch.sign(d) * torch.relu(d.abs() - (1.0 / beta) * d.abs().pow(-0.3))
+        zero = torch.mean(Wq - (W - We) * scale, dim=1, keepdim=True)
+        beta *= 1.01
+        err = float((W - Wr).abs().mean())
+        if err < best:
+            best = err
+        else:
+            break
+    q = torch.round(W * scale + zero).clamp(0, 15).to(torch.int32).reshape(w.shape)
+    return q, (1.0 / scale).to(torch.bfloat16), ((8 - zero) / scale).to(torch.bfloat16)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shapes", nargs="*", default=["4096,4096", "28672,4096", "4096,14336"])
@@ -93,6 +115,9 @@ def main():
         packed, sz = T.b200_int4_quantize_pack(w, gs, 1e-6, True)
         rec("int4_unpack", lambda: T.b200_int4_unpack(packed), n * k // 2 + 4 * n * k)
         rec("int4_dequantize", lambda: T.b200_int4_dequantize(packed, sz, gs), n * k // 2 + (k // gs) * n * 4 + 2 * n * k)
+        if n * k <= 4096 * 14336:  # a solver iteration reads the weight once: (iterations + 2) * 2NK + 4NK written
+            rec("int4_hqq_quantize (<= 20 iterations + init + finalize)", lambda: T.b200_int4_hqq_quantize(w, gs),
+                22 * 2 * n * k + 4 * n * k, lambda: ref_eager_hqq(w, gs))
         rec("int8_quantize", lambda: T.b200_int8_quantize(w, 1.1920929e-07, True), 2 * n * k + n * k + 2 * n,
             lambda: ref_eager_int8(w))
         q8, _ = T.b200_int8_quantize(w, 1.1920929e-07, True)

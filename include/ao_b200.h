@@ -154,6 +154,24 @@ AO_B200_API int ao_b200_int4_gemv_fused(const void* x, int64_t M, int64_t Kx, in
 AO_B200_API int ao_b200_int8_quantize(const void* w, int64_t N, int64_t K, int64_t ldw, float eps, int div_mode,
                           int8_t* q, void* scale, void* stream);
 
+/* HQQ qparam search for Int4WeightOnlyConfig(use_hqq=True): replaces _choose_qparams_and_quantize_affine_hqq
+ * (quant_primitives.py:1998-2111, optimizer :1915-1973, format conversion :1981-1995; caller
+ * affine_quantized_tensor.py:252-288).  w bf16, contiguous, viewed as [n_groups][group_size]; scale / zero fp32
+ * [n_groups] are the solver's state (hqq convention  W ~ (q - zero) / scale).
+ *   init:     scale = min(15 / (max - min), 2e4), zero = round(-min * scale)
+ *   step:     one proximal iteration (zero updated in place); err_partial[ao_b200_hqq_blocks(n_groups)] receives the
+ *             per-block sums of |W - W_r|: the caller divides their sum by the element count and applies the reference's
+ *             global early stop (stop at the first iteration whose mean error does not improve), multiplying beta by
+ *             kappa between iterations
+ *   finalize: q int32 [n_groups][group_size] in 0..15, scale_out = bf16(1 / scale), zero_out = bf16((8 - zero) / scale):
+ *             the tinygemm convention  w' = (q - 8) * scale_out + zero_out, ready for ao_b200_int4_pack. */
+AO_B200_API int64_t ao_b200_hqq_blocks(int64_t n_groups);
+AO_B200_API int ao_b200_hqq_init(const void* w, int64_t n_groups, int group_size, float* scale, float* zero, void* stream);
+AO_B200_API int ao_b200_hqq_step(const void* w, int64_t n_groups, int group_size, const float* scale, float* zero,
+                                 double beta, double lp_norm, float* err_partial, void* stream);
+AO_B200_API int ao_b200_hqq_finalize(const void* w, int64_t n_groups, int group_size, const float* scale, const float* zero,
+                                     int32_t* q, void* scale_out, void* zero_out, void* stream);
+
 /* strip-major int8 layout (this library's format): uint8 [Np/16][Kp/64][2][32][16], BIASED bytes u = q + 128.
  *   strip s (16 rows) x k-tile kt (64 k) = 1024 contiguous bytes = two 32-k halves of 512 bytes; inside a half lane
  *   l = (g = l>>2, c = l&3) owns 16 bytes = 4 words; word j holds row 16 s + g + 8 (j&1), k0 = 64 kt + 32 h + 8 c + 4 (j>>1),

@@ -407,6 +407,51 @@ def unpack_int8_b200(packed):
     return (u6.reshape(s_ * 16, kt_ * 64).astype(np.int16) - 128).astype(np.int8)
 
 
+# --------------------------------------------------------------------------
+# HQQ (use_hqq=True): half-quadratic qparam search, then the same packed format
+# --------------------------------------------------------------------------
+def hqq_quantize(w, group_size, nbits=4, lp_norm=0.7, beta=10.0, kappa=1.01, iters=20):
+    """quant_primitives.py:1998-2111 (_choose_qparams_and_quantize_affine_hqq, axis=1, optimize=True,
+    raw_output=False, compute_dtype=bf16) with optimize_weights_proximal_legacy (:1915-1973) on its fp32 (CPU) path and
+    _convert_to_affinequantized_format (:1981-1995).  ``w``: bf16-valued fp32 (N, K).  Returns q uint8 (N, K),
+    scale / zero as bf16-valued fp32 (N, K/G) in the tinygemm convention  w' = (q - 8) * scale + zero.
+
+    Parity status of THIS function: pinned to tests/golden/hqq_*.npz within a tolerance, not bit-for-bit — the
+    reference's iteration uses torch's vectorised fp32 ``mean`` / ``pow`` whose last-ulp behaviour numpy does not
+    reproduce; the scale (a pure min / max quantity) IS bit-exact, the optimised zero agrees to a bf16 ulp on almost every
+    group and q is identical on > 99.9 % of the weights (tests/test_oracle_golden.py states the bounds)."""
+    w = np.ascontiguousarray(w, dtype=F32)
+    n, k = w.shape
+    W = w.reshape(-1, group_size)
+    max_v = F32(2 ** nbits - 1)
+    mn = W.min(axis=1, keepdims=True)
+    mx = W.max(axis=1, keepdims=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        scale = np.minimum(max_v / (mx - mn), F32(2e4)).astype(F32)  # .clamp(max=2e4): inf (constant group) -> 2e4
+    zero = np.rint(-mn * scale).astype(F32)
+    best = 1e4
+    for _ in range(iters):
+        Wq = np.clip(np.rint(W * scale + zero), 0, max_v).astype(F32)
+        Wr = ((Wq - zero) / scale).astype(F32)
+        d = (W - Wr).astype(F32)
+        ad = np.abs(d)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            shr = ad - F32(1.0 / beta) * np.power(ad, F32(lp_norm - 1)).astype(F32)
+        We = (np.sign(d) * np.maximum(shr, F32(0))).astype(F32)  # |d| = 0: pow = inf, relu(-inf) = 0, sign = 0
+        We[ad == 0] = 0
+        zero = np.mean(Wq - (W - We) * scale, axis=1, keepdims=True, dtype=F32)
+        beta *= kappa
+        err = float(np.mean(np.abs(W - Wr), dtype=F32))
+        if err < best:
+            best = err
+        else:
+            break
+    q = np.clip(np.rint(W * scale + zero), 0, max_v).astype(np.uint8).reshape(n, k)
+    s_inv = (F32(1.0) / scale).astype(F32)
+    zero_ao = ((F32(2 ** (nbits - 1)) - zero) * s_inv).astype(F32)
+    return q, bf16_round(s_inv).reshape(n, -1), bf16_round(zero_ao).reshape(n, -1)
+
+
 def sqnr_db(ref, x):
     """Reference: torchao/quantization/utils.py:51-55 compute_error."""
     ref = ref.astype(np.float64)

@@ -150,3 +150,47 @@ def test_int8_b200_layout_round_trip_and_word_contract():
     word = p[s, kt].reshape(2, 32, 4, 4)[h, 4 * g + c, j]
     row, k0 = 16 * s + g + 8 * (j & 1), 64 * kt + 32 * h + 8 * c + 4 * (j >> 1)
     assert np.array_equal(word.astype(np.int16) - 128, q[row, k0:k0 + 4].astype(np.int16))
+
+
+# ------------------------------------------------------------------------------------------------
+# HQQ: tolerance-pinned, see the docstring of ao_oracle.hqq_quantize
+# ------------------------------------------------------------------------------------------------
+HQQ = sorted(glob.glob(os.path.join(GOLDEN, "hqq_*.npz")))
+
+
+def hqq_agreement(q, s, z, g):
+    """(fraction of identical q, max |dq|, scale bit-exact?, fraction of groups whose zero is within one bf16 ulp or
+    1/128 of the group's scale of the golden zero)"""
+    gq, gs_, gz = g["q"], o.from_bits(g["scale"]), o.from_bits(g["zero"])
+    dz = np.abs(z - gz)
+    tol = np.maximum(np.abs(gz), np.abs(gs_)) * 2.0 ** -7
+    return ((q == gq).mean(), int(np.abs(q.astype(np.int32) - gq.astype(np.int32)).max()),
+            np.array_equal(o.to_bits(s), g["scale"]), (dz <= tol).mean())
+
+
+def test_hqq_golden_present():
+    assert len(HQQ) >= 4
+
+
+@pytest.mark.parametrize("path", HQQ, ids=os.path.basename)
+def test_hqq_oracle_matches_reference_within_tolerance(path):
+    g = np.load(path)
+    q, s, z = o.hqq_quantize(o.from_bits(g["w"]), int(g["group_size"]))
+    same_q, max_dq, scale_exact, zero_ok = hqq_agreement(q, s, z, g)
+    assert scale_exact                      # 1 / (15 / (max - min)) has no iteration in it
+    assert same_q >= 0.999 and max_dq <= 1  # a zero one ulp off moves a weight sitting on a rounding boundary by one step
+    assert zero_ok >= 0.99
+
+
+def test_hqq_lowers_the_lp_error_of_heavy_tailed_groups():
+    # what the solver is for: || W - dequant ||_p^p with p = 0.7 must not be worse than min / max (tinygemm) qparams
+    g = np.load(os.path.join(GOLDEN, "hqq_heavy_24x512_g256.npz"))
+    gs = int(g["group_size"])
+    w = o.from_bits(g["w"])
+    q, s, z = o.hqq_quantize(w, gs)
+    s0, z0 = o.choose_qparams_tinygemm(w, gs)
+    q0 = o.quantize_tinygemm(w, s0, z0, gs)
+    rep = lambda a: np.repeat(a, gs, axis=1)
+    e_hqq = np.abs(w - ((q.astype(np.float32) - 8) * rep(s) + rep(z))) ** 0.7
+    e_mm = np.abs(w - ((q0.astype(np.float32) - 8) * rep(s0) + rep(z0))) ** 0.7
+    assert e_hqq.mean() < e_mm.mean()

@@ -31,6 +31,10 @@ SIGNATURES = {
     "ao_b200_int8_pack": [_vp, _i64, _i64, _i64, _i64, _vp, _vp],
     "ao_b200_int8_unpack": [_vp, _i64, _i64, _i64, _i64, _vp, _vp],
     "ao_b200_int8_mm_workspace_bytes": [_i64, _i64, _i64],
+    "ao_b200_hqq_blocks": [_i64],
+    "ao_b200_hqq_init": [_vp, _i64, _i32, _vp, _vp, _vp],
+    "ao_b200_hqq_step": [_vp, _i64, _i32, _vp, _vp, ctypes.c_double, ctypes.c_double, _vp, _vp],
+    "ao_b200_hqq_finalize": [_vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp],
     "ao_b200_int8_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp],
     "ao_b200_int8_gemv_fused": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _f32, _vp, _i64, _i32,
                                 _vp],
@@ -52,7 +56,7 @@ SIGNATURES = {
     "ao_b200_tp_allreduce_add": [_vp, _vp, _i64, ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i64, _vp],
 }
 _RESTYPES = {"ao_b200_error_string": ctypes.c_char_p, "ao_b200_int4_mm_workspace_bytes": _i64,
-             "ao_b200_int8_mm_workspace_bytes": _i64,
+             "ao_b200_int8_mm_workspace_bytes": _i64, "ao_b200_hqq_blocks": _i64,
              "ao_b200_decode_attention_workspace_bytes": _i64,
              "ao_b200_decode_attention_fused_workspace_bytes": _i64, "ao_b200_tp_buffer_bytes": _i64}
 

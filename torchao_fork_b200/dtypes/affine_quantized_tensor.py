@@ -111,8 +111,6 @@ class AffineQuantizedTensor(torch.Tensor):
 
         if zero_point_domain is None:
             raise ValueError("please use ZeroPointDomain.NONE instead of None")
-        if use_hqq:
-            raise NotImplementedError("use_hqq=True is a 'next' row of the B200 path (SURVEY.md §8 N1)")
         if custom_scale is not None or custom_zero_point is not None:
             raise NotImplementedError("custom scale/zero_point are outside the B200 hot path")
         if not input_float.is_cuda:
@@ -133,11 +131,21 @@ class AffineQuantizedTensor(torch.Tensor):
                     "FLOAT zero-point domain, preserve_zero=False, block_size (1, G)")
             if zero_point_dtype not in (None, torch.bfloat16) or scale_dtype not in (None, torch.bfloat16):
                 raise NotImplementedError("tinygemm qparams are bfloat16")
+            if use_hqq:
+                # reference: affine_quantized_tensor.py:252-288 -> _choose_qparams_and_quantize_affine_hqq with
+                # nbits = log2(quant_max + 1), axis = 1, group_size = max(block_size), raw_output = False
+                q, scale, zero = torch.ops.torchao.b200_int4_hqq_quantize(
+                    input_float if input_float.dtype is torch.bfloat16 else input_float.to(torch.bfloat16), int(block_size[1]))
+                tensor_impl = TensorCoreTiledAQTTensorImpl.from_plain(q, scale, zero, _layout)
+                return cls(tensor_impl, block_size, original_shape, quant_min, quant_max, zero_point_domain,
+                           dtype=input_float.dtype)
             tensor_impl = TensorCoreTiledAQTTensorImpl.from_hp(
                 input_float, int(block_size[1]), 1e-6 if eps is None else float(eps), _layout)
             return cls(tensor_impl, block_size, original_shape, quant_min, quant_max, zero_point_domain,
                        dtype=input_float.dtype)
 
+        if use_hqq:
+            raise NotImplementedError("use_hqq=True on B200 is implemented for TensorCoreTiledLayout (Int4WeightOnlyConfig)")
         if isinstance(_layout, PlainLayout):
             int8 = (mapping_type is MappingType.SYMMETRIC and target_dtype == torch.int8 and (qmin, qmax) == (-128, 127)
                     and zero_point_domain is ZeroPointDomain.INT and len(block_size) == 2 and block_size[0] == 1)

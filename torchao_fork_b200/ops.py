@@ -24,6 +24,7 @@ _SCHEMAS = {
     "b200_int4_choose_qparams": "(Tensor w, int group_size, float eps, bool cuda_div_semantics) -> (Tensor, Tensor)",
     "b200_int4_quantize": "(Tensor w, Tensor scale, Tensor zero, int group_size) -> Tensor",
     "b200_int4_pack": "(Tensor int_data) -> Tensor",
+    "b200_int4_hqq_quantize": "(Tensor w, int group_size) -> (Tensor, Tensor, Tensor)",
     "b200_int4_unpack": "(Tensor packed_w) -> Tensor",
     "b200_int4_dequantize": "(Tensor packed_w, Tensor scales_and_zeros, int group_size) -> Tensor",
     "b200_tinygemm_pack": "(Tensor int_data, int inner_k_tiles) -> Tensor",
@@ -242,6 +243,53 @@ def _int4_quantize_cuda(w: Tensor, scale: Tensor, zero: Tensor, group_size: int)
         _lib.check(_lib.lib().ao_b200_int4_quantize(w.data_ptr(), n, k, k, group_size, scale.data_ptr(),
                                                     zero.data_ptr(), q.data_ptr(), _stream(w)), "int4_quantize")
     return q
+
+
+# HQQ solver constants: optimize_weights_proximal_legacy's opt_params (quant_primitives.py:1924-1930)
+HQQ_LP_NORM, HQQ_BETA, HQQ_KAPPA, HQQ_ITERS = 0.7, 1e1, 1.01, 20
+
+
+@register_custom_op("torchao::b200_int4_hqq_quantize")
+def _(w: Tensor, group_size: int):
+    shape = (w.size(0), w.size(1) // group_size)
+    return (torch.empty(w.shape, dtype=torch.int32, device=w.device),
+            torch.empty(shape, dtype=torch.bfloat16, device=w.device),
+            torch.empty(shape, dtype=torch.bfloat16, device=w.device))
+
+
+@_impl_cuda("b200_int4_hqq_quantize")
+def _int4_hqq_quantize_cuda(w: Tensor, group_size: int):
+    """`_choose_qparams_and_quantize_affine_hqq(w, nbits=4, group_size, axis=1, compute_dtype=bf16, raw_output=False)`
+    (quant_primitives.py:1998-2111): q int32 (N, K) in 0..15, scale / zero bf16 (N, K/G) in the tinygemm convention.
+    One kernel per solver iteration; the reference's early stop is a mean over the whole tensor, so the host reads one
+    float per iteration (a one-off cost at quantization time, <= 20 iterations)."""
+    _w_checks(w, group_size)
+    w = w.contiguous()
+    n, k = w.shape
+    n_groups = n * (k // group_size)
+    L = _lib.lib()
+    scale = torch.empty(n_groups, dtype=torch.float32, device=w.device)
+    zero = torch.empty_like(scale)
+    err = torch.empty(int(L.ao_b200_hqq_blocks(n_groups)), dtype=torch.float32, device=w.device)
+    q = torch.empty((n, k), dtype=torch.int32, device=w.device)
+    scale_out = torch.empty((n, k // group_size), dtype=torch.bfloat16, device=w.device)
+    zero_out = torch.empty_like(scale_out)
+    with torch.cuda.device(w.device):
+        st = _stream(w)
+        _lib.check(L.ao_b200_hqq_init(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(), st), "hqq_init")
+        beta, best = HQQ_BETA, 1e4
+        for _ in range(HQQ_ITERS):
+            _lib.check(L.ao_b200_hqq_step(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(), beta,
+                                          HQQ_LP_NORM, err.data_ptr(), st), "hqq_step")
+            beta *= HQQ_KAPPA
+            current = float(err.sum(dtype=torch.float64)) / (n * k)
+            if current < best:  # early_stop=True (:1968-1972): the zero of the non-improving iteration is kept
+                best = current
+            else:
+                break
+        _lib.check(L.ao_b200_hqq_finalize(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(),
+                                          q.data_ptr(), scale_out.data_ptr(), zero_out.data_ptr(), st), "hqq_finalize")
+    return q, scale_out, zero_out
 
 
 @register_custom_op("torchao::b200_int4_pack")
