@@ -22,6 +22,10 @@ import sys
 import threading
 import time
 
+# stdout carries ONE JSON line: keep NCCL's version banner (printed to stdout when NCCL_DEBUG=VERSION) out of it
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
