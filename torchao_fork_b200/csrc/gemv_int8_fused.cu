@@ -71,6 +71,12 @@ __device__ __forceinline__ uint32_t u8_f16_hi(uint32_t w) { return __byte_perm(w
 // NH > 0: M = 1 and every consumer thread owns <= NH chunks of the activation row (register-held staging); NH = 0: the
 // general staging.  One instantiation per case — the staging code runs once per launch with a cold instruction cache, so
 // code that a launch does not need is not compiled into its kernel (profiles/r01c_imma_code_size_ab.txt).
+__device__ __forceinline__ uint32_t mul_bf16x2_8(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+
 template <int MT, int NH>
 __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_kernel(const Gemv8Params p) {
   extern __shared__ __align__(128) uint8_t smem8[];
@@ -225,20 +231,16 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
 #pragma unroll
     for (int i = 0; i < kHold; ++i) {
       float f[8];
-      unpack8(xr[i], f);
       if (p.norm_w != nullptr) {
-        float wn[8];
-        unpack8(wn4[i], wn);
+        unpack8(xr[i], f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          ss = fmaf(f[e], f[e], ss);
-          f[e] = bf16r(f[e] * wn[e]);
-        }
-        uint32_t o[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) o[e] = float_to_bf16_bits(f[2 * e]) | (float_to_bf16_bits(f[2 * e + 1]) << 16);
-        xr[i] = make_uint4(o[0], o[1], o[2], o[3]);
+        for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
+        // bf16(x * w): the fp32 product of two bf16 is exact, so one packed bf16x2 multiply IS the reference's
+        // compute-in-fp32-then-round (and leaves the values packed for the second pass)
+        xr[i] = make_uint4(mul_bf16x2_8(xr[i].x, wn4[i].x), mul_bf16x2_8(xr[i].y, wn4[i].y), mul_bf16x2_8(xr[i].z, wn4[i].z),
+                           mul_bf16x2_8(xr[i].w, wn4[i].w));
       }
+      unpack8(xr[i], f);
 #pragma unroll
       for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
     }
