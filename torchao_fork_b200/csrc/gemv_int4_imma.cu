@@ -163,12 +163,16 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
       const uint32_t use = (uint32_t)(li / kIRedBufs);
       const float* rb = red + (size_t)rbuf * (kIConsumers * 128);
       mbar_wait(&red_full[rbuf], use & 1u);
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      // 16 warps' partial sums, added in warp order with packed fp32x2 adds (half the instructions of the scalar chain)
+      uint64_t vlo = 0ull, vhi = 0ull;
 #pragma unroll
       for (int w = 0; w < kIConsumers; ++w) {
-        const float4 t = *reinterpret_cast<const float4*>(rb + (w * 32 + lane) * 4);
-        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+        const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(rb + (w * 32 + lane) * 4);
+        asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vlo) : "l"(t.x));
+        asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vhi) : "l"(t.y));
       }
+      const float4 v = make_float4(__uint_as_float((uint32_t)vlo), __uint_as_float((uint32_t)(vlo >> 32)),
+                                   __uint_as_float((uint32_t)vhi), __uint_as_float((uint32_t)(vhi >> 32)));
       __syncwarp();
       if (lane == 0) mbar_arrive(&red_free[rbuf]);
       // limb recombination: columns (3 m, 3 m + 1, 3 m + 2) = limbs (2^16, 2^8, 2^0) of activation row m; lane (g, c)
@@ -301,9 +305,10 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
     }
     named_bar_sync(1, kCT);
     // every warp reduces the 16 partials of every row itself (no second hand-over through shared memory)
-    float up_m[2];
+    float up_m[2] = {1.f, 1.f};
+    constexpr int kRows = hold ? 1 : 2;  // the register-held path is M = 1
 #pragma unroll
-    for (int m = 0; m < 2; ++m) {
+    for (int m = 0; m < kRows; ++m) {
       float t = 0.f, amax = 0.f;
       if (m < p.M && lane < kIConsumers) {
         t = part[(m * kIConsumers + lane) * 2];
