@@ -157,13 +157,16 @@ __global__ void __launch_bounds__(k8Threads, (MT == 1 ? 2 : 1)) int8_gemv_fused_
       float4 sum[MT];
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt) {
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        // warp order, packed fp32x2 adds: the same sums with half the instructions on the launch's tail
+        uint64_t slo = 0ull, shi = 0ull;
 #pragma unroll
         for (int w = 0; w < k8Consumers; ++w) {
-          const float4 v = *reinterpret_cast<const float4*>(rb + ((w * MT + mt) * 32 + lane) * 4);
-          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+          const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(rb + ((w * MT + mt) * 32 + lane) * 4);
+          asm("add.rn.f32x2 %0, %0, %1;" : "+l"(slo) : "l"(v.x));
+          asm("add.rn.f32x2 %0, %0, %1;" : "+l"(shi) : "l"(v.y));
         }
-        sum[mt] = s;
+        sum[mt] = make_float4(__uint_as_float((uint32_t)slo), __uint_as_float((uint32_t)(slo >> 32)),
+                              __uint_as_float((uint32_t)shi), __uint_as_float((uint32_t)(shi >> 32)));
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&red_free[rbuf]);
