@@ -265,6 +265,63 @@ AO_B200_API int ao_b200_tp_status(const void* own_buf, int* status_out /* 0 ok, 
 AO_B200_API int ao_b200_tp_allreduce_add(const void* partial, void* h, int64_t n, void* const* bufs, int rank, int world,
                                          int64_t max_elems, void* stream);
 
+/* ---- one decode step as ONE persistent launch (csrc/decode_mega.cu) --------------------------------------------------
+ * decode_one_token (torchao/_models/llama/generate.py:111-117) -> Transformer.forward for one token
+ * (torchao/_models/llama/model.py:342-360: embedding, n_layer x TransformerBlock.forward :405-408 [RMSNorm :498-503, wqkv,
+ * RoPE :547-559, KVCache.update :175-192, GQA attention :465-470, wo, residual, RMSNorm, w2(silu(w1 x) * w3 x) :486,
+ * residual], final norm + output) with int4 weight-only linears (Int4WeightOnlyConfig, any supported group size), batch 1.
+ * One cooperative launch of n_cta CTAs (one per SM) replaces the 161 launches per token of the per-projection path: the
+ * weight stream never drains between projections.  The launch leaves bf16 logits[vocab] in `logits`, appends the
+ * token's k / v to the caches at *pos, then sets *pos += 1 (device side: one captured graph serves every token).
+ *
+ * ao_b200_mega_model is filled by the HOST (plain struct, host memory); every pointer inside is a device pointer on the
+ * current device except `layers` (host array of n_layer entries).  Weights are strip-major int4 + strip-major
+ * scale_and_zero (see above); w13 = w1 / w3 rows interleaved 8 / 8 per 16-row strip (the SiLU*mul pairing of
+ * ao_b200_int4_gemv_fused epilogue 2).  Caches bf16 [n_kv_head][max_seq][128]; freqs bf16 [>= max_seq][64][2].
+ * Caller-owned device buffers:
+ *   plan    ao_b200_decode_mega_plan_bytes(m) bytes, filled once by ao_b200_decode_mega_setup (synchronises `stream`:
+ *           set-up time only, not capturable);
+ *   state   ao_b200_decode_mega_state_bytes() bytes, ZEROED once: [u64 arrival counter][u32 launches][u32 status];
+ *           status != 0 after a launch = a wait inside the kernel timed out (timeout_ms, default 2000): the outputs of
+ *           that launch are garbage and state + xchg must be zeroed again before the next one;
+ *   xchg[rank]  ao_b200_decode_mega_xchg_bytes(m) bytes, ZEROED once: the activation packets {2 bf16 | 32-bit tag};
+ *           world > 1 (tensor parallel: wqkv / w13 / output column shards, wo / w2 row shards, n_head / n_kv_head / inter /
+ *           vocab are the LOCAL sizes): xchg[r] = rank r's region as mapped into this process (CUDA IPC, like
+ *           ao_b200_tp_alloc / ao_b200_tp_open); the wo / w2 partial sums are pushed into every peer's region from the
+ *           GEMV epilogue and summed in rank order by the consumers of the next projection — no separate all-reduce
+ *           launch.  All ranks must launch the same sequence of steps.
+ * ao_b200_decode_mega_step is CUDA-graph-capturable (cooperative kernel node). */
+typedef struct ao_b200_mega_layer {
+  const void* wqkv_packed; const void* wqkv_sz;
+  const void* wo_packed; const void* wo_sz;
+  const void* w13_packed; const void* w13_sz;
+  const void* w2_packed; const void* w2_sz;
+  const void* attn_norm; const void* ffn_norm;   /* bf16 [dim] */
+  void* k_cache; void* v_cache;
+} ao_b200_mega_layer;
+
+typedef struct ao_b200_mega_model {
+  int32_t n_layer, dim, n_head, n_kv_head, head_dim, inter, vocab, group_size, max_seq;
+  int32_t world, rank, n_cta, timeout_ms, attn_blocks_per_cta;  /* attn_blocks_per_cta: 16-position blocks per CTA before the sequence is split (0 = default 32) */
+  float eps;
+  int32_t reserved;
+  const ao_b200_mega_layer* layers;   /* HOST array [n_layer] */
+  const void* out_packed; const void* out_sz; const void* out_norm;
+  const void* emb;                    /* bf16 [full vocab][dim] */
+  const void* freqs;
+  const int64_t* tok;                 /* the token to feed */
+  int32_t* pos;                       /* its position; incremented by the launch */
+  void* logits;                       /* bf16 [vocab] */
+  void* state;
+  void* xchg[8];
+} ao_b200_mega_model;
+
+AO_B200_API int64_t ao_b200_decode_mega_plan_bytes(const ao_b200_mega_model* m);
+AO_B200_API int64_t ao_b200_decode_mega_xchg_bytes(const ao_b200_mega_model* m);
+AO_B200_API int64_t ao_b200_decode_mega_state_bytes(void);
+AO_B200_API int ao_b200_decode_mega_setup(const ao_b200_mega_model* m, void* plan_dev, int64_t plan_bytes, void* stream);
+AO_B200_API int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void* plan_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

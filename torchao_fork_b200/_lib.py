@@ -10,6 +10,26 @@ LIB_PATH = os.path.join(_HERE, "lib", "libao_b200.so")
 
 _vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
 
+
+
+class MegaLayer(ctypes.Structure):
+    """ao_b200_mega_layer (include/ao_b200.h)"""
+    _fields_ = [(n, _vp) for n in ("wqkv_packed", "wqkv_sz", "wo_packed", "wo_sz", "w13_packed", "w13_sz", "w2_packed",
+                                   "w2_sz", "attn_norm", "ffn_norm", "k_cache", "v_cache")]
+
+
+class MegaModel(ctypes.Structure):
+    """ao_b200_mega_model (include/ao_b200.h)"""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("n_layer", "dim", "n_head", "n_kv_head", "head_dim", "inter", "vocab",
+                                               "group_size", "max_seq", "world", "rank", "n_cta", "timeout_ms",
+                                               "attn_blocks_per_cta")]
+                + [("eps", _f32), ("reserved", ctypes.c_int32), ("layers", ctypes.POINTER(MegaLayer))]
+                + [(n, _vp) for n in ("out_packed", "out_sz", "out_norm", "emb", "freqs", "tok", "pos", "logits", "state")]
+                + [("xchg", _vp * 8)])
+
+
+_mp = ctypes.POINTER(MegaModel)
+
 # name -> argtypes (all return int unless listed in _RESTYPES)
 SIGNATURES = {
     "ao_b200_error_string": [_i32],
@@ -54,11 +74,18 @@ SIGNATURES = {
     "ao_b200_tp_free": [_vp],
     "ao_b200_tp_status": [_vp, ctypes.POINTER(ctypes.c_int)],
     "ao_b200_tp_allreduce_add": [_vp, _vp, _i64, ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i64, _vp],
+    "ao_b200_decode_mega_plan_bytes": [_mp],
+    "ao_b200_decode_mega_xchg_bytes": [_mp],
+    "ao_b200_decode_mega_state_bytes": [],
+    "ao_b200_decode_mega_setup": [_mp, _vp, _i64, _vp],
+    "ao_b200_decode_mega_step": [_mp, _vp, _vp],
 }
 _RESTYPES = {"ao_b200_error_string": ctypes.c_char_p, "ao_b200_int4_mm_workspace_bytes": _i64,
              "ao_b200_int8_mm_workspace_bytes": _i64, "ao_b200_hqq_blocks": _i64,
              "ao_b200_decode_attention_workspace_bytes": _i64,
-             "ao_b200_decode_attention_fused_workspace_bytes": _i64, "ao_b200_tp_buffer_bytes": _i64}
+             "ao_b200_decode_attention_fused_workspace_bytes": _i64, "ao_b200_tp_buffer_bytes": _i64,
+             "ao_b200_decode_mega_plan_bytes": _i64, "ao_b200_decode_mega_xchg_bytes": _i64,
+             "ao_b200_decode_mega_state_bytes": _i64}
 
 DIV_IEEE, DIV_RECIP = 0, 1
 

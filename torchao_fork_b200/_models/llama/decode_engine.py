@@ -125,7 +125,7 @@ class DecodeEngine:
     """decode_one_token (generate.py:111-117) + sample (generate.py:79-100) for a fixed batch size."""
 
     def __init__(self, model: Transformer, batch_size: int = 1, temperature: float = 0.8,
-                 top_k: Optional[int] = 200, tp=None, fused: bool = True):
+                 top_k: Optional[int] = 200, tp=None, fused: bool = True, mega: Optional[bool] = None):
         cfg = model.config
         assert model.freqs_cis is not None and model.max_batch_size >= batch_size, "call model.setup_caches first"
         assert cfg.head_dim == 128, "decode attention kernel is specialised for head_dim 128"
@@ -197,6 +197,81 @@ class DecodeEngine:
         self.graph = None
         self.graph_stream = None
         self.launches_per_step = 0
+        self._host_pos = 0   # host mirror of *pos (set_state / step): decoding past the caches raises instead of corrupting them
+        # one persistent launch per token (csrc/decode_mega.cu): batch 1, every linear int4 with one group size
+        can_mega = (batch_size == 1 and self.fused and tp is None
+                    and all(l[k] is not None and l[k].kind == "int4" for l in self.layers for k in ("wqkv", "wo", "w13", "w2"))
+                    and self.output.kind == "int4"
+                    and len({l[k].group_size for l in self.layers for k in ("wqkv", "wo", "w13", "w2")} | {self.output.group_size}) == 1
+                    and D % 128 == 0 and self.I % 128 == 0 and self.H // self.Hkv <= 8)
+        if mega is None:
+            mega = can_mega and os.environ.get("AO_B200_MEGA", "1") != "0"
+        assert not mega or can_mega, "the persistent decode kernel needs batch 1 and int4 weight-only linears everywhere"
+        self.mega = bool(mega)
+        if self.mega:
+            self._setup_mega()
+
+    # ------------------------------------------------------------------ one persistent launch per token
+    def _setup_mega(self, attn_blocks_per_cta: int = 0, timeout_ms: int = 2000):
+        import ctypes
+        L = _lib.lib()
+        dev = self.device
+        nl = len(self.layers)
+        arr = (_lib.MegaLayer * nl)()
+        for i, l in enumerate(self.layers):
+            a = arr[i]
+            a.wqkv_packed, a.wqkv_sz = l["wqkv"].packed.data_ptr(), l["wqkv"].sz.data_ptr()
+            a.wo_packed, a.wo_sz = l["wo"].packed.data_ptr(), l["wo"].sz.data_ptr()
+            a.w13_packed, a.w13_sz = l["w13"].packed.data_ptr(), l["w13"].sz.data_ptr()
+            a.w2_packed, a.w2_sz = l["w2"].packed.data_ptr(), l["w2"].sz.data_ptr()
+            a.attn_norm, a.ffn_norm = l["attn_norm"].data_ptr(), l["ffn_norm"].data_ptr()
+            a.k_cache, a.v_cache = l["k_cache"].data_ptr(), l["v_cache"].data_ptr()
+        m = _lib.MegaModel()
+        m.n_layer, m.dim, m.n_head, m.n_kv_head, m.head_dim = nl, self.cfg.dim, self.H, self.Hkv, self.hd
+        m.inter, m.vocab, m.group_size, m.max_seq = self.I, self.output.n, self.output.group_size, self.S
+        m.world, m.rank = 1, 0
+        m.n_cta = torch.cuda.get_device_properties(dev).multi_processor_count
+        if os.environ.get("AO_B200_MEGA_CTAS"):
+            m.n_cta = int(os.environ["AO_B200_MEGA_CTAS"])
+        m.timeout_ms, m.attn_blocks_per_cta = timeout_ms, attn_blocks_per_cta
+        m.eps = self.eps
+        m.layers = ctypes.cast(arr, ctypes.POINTER(_lib.MegaLayer))
+        m.out_packed, m.out_sz, m.out_norm = self.output.packed.data_ptr(), self.output.sz.data_ptr(), self.out_norm.data_ptr()
+        m.emb, m.freqs = self.emb.data_ptr(), self.freqs.data_ptr()
+        assert self.freqs.dtype == torch.bfloat16 and self.freqs.is_contiguous() and self.freqs.shape[0] >= self.S
+        self.next_tok = self.tok   # the sampled token IS the token fed to the next launch
+        m.tok, m.pos, m.logits = self.tok.data_ptr(), self.pos.data_ptr(), self.logits.data_ptr()
+        self._mega_state = torch.zeros(int(L.ao_b200_decode_mega_state_bytes()), dtype=torch.uint8, device=dev)
+        m.state = self._mega_state.data_ptr()
+        self._mega_layers, self._mega_model = arr, m   # keep the host structs alive
+        xb = int(L.ao_b200_decode_mega_xchg_bytes(ctypes.byref(m)))
+        assert xb > 0, "ao_b200_decode_mega: unsupported model shape"
+        self._mega_xchg = torch.zeros(xb, dtype=torch.uint8, device=dev)
+        m.xchg[0] = self._mega_xchg.data_ptr()
+        pb = int(L.ao_b200_decode_mega_plan_bytes(ctypes.byref(m)))
+        assert pb > 0, "ao_b200_decode_mega: unsupported model shape"
+        self._mega_plan = torch.zeros(pb, dtype=torch.uint8, device=dev)
+        torch.cuda.synchronize(dev)
+        _lib.check(L.ao_b200_decode_mega_setup(ctypes.byref(m), self._mega_plan.data_ptr(), pb,
+                                               torch.cuda.current_stream(dev).cuda_stream), "decode_mega_setup")
+
+    def mega_status(self) -> int:
+        """Sticky status word of the persistent kernel (0 = fine; non-zero = a wait inside it timed out)."""
+        return int(self._mega_state[12:16].view(torch.int32).item()) if self.mega else 0
+
+    def check_status(self):
+        st = self.mega_status()
+        if st:
+            raise RuntimeError(f"ao_b200_decode_mega: a wait inside the kernel timed out (status {st:#x}); "
+                               "outputs since then are invalid — rebuild the engine")
+
+    def _launch_step_mega(self):
+        import ctypes
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(_lib.lib().ao_b200_decode_mega_step(ctypes.byref(self._mega_model), self._mega_plan.data_ptr(), st),
+                   "decode_mega_step")
+        self._sample(self.logits)
+        self.launches_per_step = 2 + (1 if self.temperature != 0.0 else 0)
 
     # ------------------------------------------------------------------ one step, eager launches
     def _mm(self, lin, x, y, stream):
@@ -240,6 +315,8 @@ class DecodeEngine:
         self.pos.add_(1)
 
     def _launch_step(self):
+        if self.mega:
+            return self._launch_step_mega()
         if self.fused:
             return self._launch_step_fused()
         L = _lib.lib()
@@ -352,12 +429,19 @@ class DecodeEngine:
 
     def set_state(self, tokens: torch.Tensor, pos: int):
         """tokens int [B] = the token to feed next; pos = its position in the sequence."""
+        if not 0 <= pos < self.S:
+            raise ValueError(f"position {pos} outside the KV cache (max_seq_length {self.S})")
         self.tok.copy_(tokens.reshape(-1).to(torch.int64))
         self.pos.fill_(pos)
+        self._host_pos = pos
 
     def step(self) -> torch.Tensor:
         """Runs one decode step; returns the device buffer holding the sampled tokens [B] (overwritten by
         the next step).  The sampled token is already fed back for the following step."""
+        if self._host_pos >= self.S:
+            raise RuntimeError(f"decode step at position {self._host_pos} would run past the KV cache "
+                               f"(max_seq_length {self.S}); the reference's KVCache.update raises here too")
+        self._host_pos += 1
         if self.graph is not None:
             self.graph.replay()
         else:

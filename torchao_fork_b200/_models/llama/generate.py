@@ -90,6 +90,9 @@ class Generator:
         reads the sampled token back into pinned host memory (result on the host); otherwise the tokens
         stay on the device (result on the device), as in the reference."""
         eng, B, dev = self.engine, self.batch_size, self.engine.device
+        if eng._host_pos + n > eng.S:
+            raise RuntimeError(f"decoding {n} tokens from position {eng._host_pos} would run past the KV cache "
+                               f"(max_seq_length {eng.S})")
         if stream_to_host:
             out = torch.empty(B, n, dtype=torch.int64)
             self.h_tok.copy_(eng.tok)
@@ -99,12 +102,14 @@ class Generator:
             if eng.graph_stream is not None:
                 # one replay = H2D of the fed token + the step + D2H of the sampled token (memcpy nodes in the graph)
                 h_tok, h_out, o = self.h_tok.numpy(), self.h_out.numpy(), out.numpy()
+                eng._host_pos += n
                 for i in range(n):
                     eng.graph_stream.replay()
                     stream.synchronize()
                     callback(self.h_out)
                     o[:, i] = h_out
                     h_tok[:] = h_out
+                eng.check_status()
                 return out
             for i in range(n):
                 eng.tok.copy_(self.h_tok, non_blocking=True)        # H2D: the token the host feeds
@@ -119,6 +124,7 @@ class Generator:
         for i in range(n):
             out[:, i].copy_(eng.step())
             callback(out[:, i])
+        eng.check_status()
         return out
 
 
