@@ -1,0 +1,90 @@
+"""Where a persistent decode step spends its time: per-phase clock stamps of every CTA (decode_mega.cu `trace`).
+
+    python benchmarks/mega_trace.py [--workload llama3-8b-int4] [--pos 100] [--layers N] [--out gpurun_out/mega_trace.json]
+
+Stamps (clock64 of the CTA's SM, so only differences inside a CTA are meaningful): 0 phase entered (previous main loop
+done), 1 arrival counter satisfied, 6 statistics pass + barrier done, 2 staging done, 3 main loop done, 4 outputs
+published, 5 producer issued the phase's last stage.  Reported per phase kind, averaged over layers (layer 0 skipped),
+in microseconds at --mhz: [mean, max, min] over the CTAs."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="llama3-8b-int4")
+    ap.add_argument("--pos", type=int, default=100)
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--mhz", type=float, default=1965.0)
+    ap.add_argument("--layers", type=int, default=0, help="override n_layer (short ncu runs)")
+    args = ap.parse_args()
+    from torchao_fork_b200._models.llama import Generator
+    from torchao_fork_b200._models.llama.model import transformer_configs
+    spec = bench.WORKLOADS[args.workload]
+    if args.layers:
+        transformer_configs[spec["model"]]["n_layer"] = args.layers
+    model, cfg = bench.build_model(spec, torch.device("cuda"))
+    gen = Generator(model, 1, args.pos + 64, temperature=0.8, top_k=200, use_graph=False)
+    eng = gen.engine
+    assert eng.mega
+    eng._setup_mega(trace=True)
+    eng.set_state(torch.tensor([1], device="cuda"), args.pos)
+    for _ in range(5):
+        eng.step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    eng.step()
+    e1.record()
+    torch.cuda.synchronize()
+    eng.check_status()
+    step_us = e0.elapsed_time(e1) * 1e3
+    tr = eng._mega_trace.cpu().numpy().astype("float64") / args.mhz   # us, [cta][phase][8]
+    n_cta, n_ph, _ = tr.shape
+    nl = (n_ph - 1) // 5
+    names = ["wqkv", "attn", "wo", "w13", "w2"]
+    rep = {"step_us_with_sampling": step_us, "n_cta": n_cta, "phases": {}}
+    rep["kernel_us_mean_over_ctas"] = float((tr[:, n_ph - 1, 3] - tr[:, 0, 0]).mean())
+
+    def mmm(x):
+        return [round(float(x.mean()), 2), round(float(x.max()), 2), round(float(x.min()), 2)]
+
+    def summarize(idx, gemv):
+        d = {"wait": mmm(tr[:, idx, 1] - tr[:, idx, 0])}
+        if gemv:
+            d["sweep_stats"] = mmm(tr[:, idx, 6] - tr[:, idx, 1])
+            d["limbs"] = mmm(tr[:, idx, 2] - tr[:, idx, 6])
+            d["main"] = mmm(tr[:, idx, 3] - tr[:, idx, 2])
+            d["publish_after_main"] = mmm(tr[:, idx, 4] - tr[:, idx, 3])
+            d["producer_lead"] = mmm(tr[:, idx, 3] - tr[:, idx, 5])
+            d["total"] = mmm(tr[:, idx, 3] - tr[:, idx, 0])
+        else:
+            act = (tr[:, idx, 4] - tr[:, idx, 1])
+            d["attn"] = mmm(act)
+            d["total"] = mmm(tr[:, idx, 4] - tr[:, idx, 0])
+        return d
+
+    for k, nm in enumerate(names):
+        acc = {}
+        for l in range(1 if nl > 1 else 0, nl):
+            for kk, v in summarize(5 * l + k, nm != "attn").items():
+                acc.setdefault(kk, []).append(v)
+        rep["phases"][nm] = {kk: [round(sum(x[j] for x in v) / len(v), 2) for j in range(3)] for kk, v in acc.items()}
+    rep["phases"]["output"] = summarize(n_ph - 1, True)
+    rep["layer_us"] = round(sum(rep["phases"][nm]["total"][0] for nm in names), 2)
+    print(json.dumps({k: v for k, v in rep.items() if k != "phases"}))
+    for nm, d in rep["phases"].items():
+        print(nm, json.dumps(d))
+    if args.out:
+        open(args.out, "w").write(json.dumps(rep, indent=1))
+
+
+if __name__ == "__main__":
+    main()

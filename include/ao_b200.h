@@ -314,6 +314,7 @@ typedef struct ao_b200_mega_model {
   void* logits;                       /* bf16 [vocab] */
   void* state;
   void* xchg[8];
+  void* trace;                        /* NULL, or u64 [n_cta][5 n_layer + 1][8]: per-phase clock64 stamps of every CTA (profiling) */
 } ao_b200_mega_model;
 
 AO_B200_API int64_t ao_b200_decode_mega_plan_bytes(const ao_b200_mega_model* m);

@@ -25,7 +25,7 @@ class MegaModel(ctypes.Structure):
                                                "attn_blocks_per_cta")]
                 + [("eps", _f32), ("reserved", ctypes.c_int32), ("layers", ctypes.POINTER(MegaLayer))]
                 + [(n, _vp) for n in ("out_packed", "out_sz", "out_norm", "emb", "freqs", "tok", "pos", "logits", "state")]
-                + [("xchg", _vp * 8)])
+                + [("xchg", _vp * 8), ("trace", _vp)])
 
 
 _mp = ctypes.POINTER(MegaModel)

@@ -212,7 +212,7 @@ class DecodeEngine:
             self._setup_mega()
 
     # ------------------------------------------------------------------ one persistent launch per token
-    def _setup_mega(self, attn_blocks_per_cta: int = 0, timeout_ms: int = 2000):
+    def _setup_mega(self, attn_blocks_per_cta: int = 0, timeout_ms: int = 2000, trace: bool = False):
         import ctypes
         L = _lib.lib()
         dev = self.device
@@ -250,6 +250,10 @@ class DecodeEngine:
         m.xchg[0] = self._mega_xchg.data_ptr()
         pb = int(L.ao_b200_decode_mega_plan_bytes(ctypes.byref(m)))
         assert pb > 0, "ao_b200_decode_mega: unsupported model shape"
+        self._mega_trace = None
+        if trace:  # per-CTA, per-phase clock stamps (benchmarks/mega_trace.py)
+            self._mega_trace = torch.zeros(m.n_cta, 5 * nl + 1, 8, dtype=torch.int64, device=dev)
+            m.trace = self._mega_trace.data_ptr()
         self._mega_plan = torch.zeros(pb, dtype=torch.uint8, device=dev)
         torch.cuda.synchronize(dev)
         _lib.check(L.ao_b200_decode_mega_setup(ctypes.byref(m), self._mega_plan.data_ptr(), pb,

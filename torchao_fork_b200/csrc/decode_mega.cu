@@ -88,6 +88,7 @@ struct Params {
   int stages;
   uint32_t off_x, off_S, off_red, off_h, off_misc;
   unsigned long long timeout_ns;
+  unsigned long long* trace;      // optional: [n_cta][n_phases][8] clock64 stamps (benchmarks/mega_trace.py)
 };
 
 // ------------------------------------------------------------------------------------------------ small helpers
@@ -141,6 +142,10 @@ __device__ __forceinline__ uint64_t ld_ctr(const uint64_t* p) {
 }
 __device__ __forceinline__ void red_ctr(uint64_t* p) {
   asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" ::"l"(p) : "memory");
+}
+
+__device__ __forceinline__ void stamp(unsigned long long* trace, int n_phases, int i, int k) {
+  if (trace != nullptr) trace[((size_t)blockIdx.x * n_phases + i) * 8 + k] = (unsigned long long)clock64();
 }
 
 struct Ctx {
@@ -518,6 +523,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
             }
           }
         }
+        stamp(p.trace, n_phases, i, 5);
       }
     }
     return;
@@ -597,7 +603,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
         }
       }
       __syncwarp();
-      if (lane == 0) red_ctr(p.counter);
+      if (lane == 0) {
+        red_ctr(p.counter);
+        stamp(p.trace, n_phases, i, 4);
+      }
       ++gphase;
     }
     if (b == 0 && lane == 0) {  // every CTA read both at its start, long before CTA 0 can get here
@@ -633,6 +642,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
     const __nv_bfloat16* norm_w = ph->norm_w;
     uint4 wn_first = make_uint4(0u, 0u, 0u, 0u);
     if (is_gemv && in_kind == IN_H && tid * 8 < Kx) wn_first = __ldg(reinterpret_cast<const uint4*>(norm_w) + tid);
+    if (tid == 0) stamp(p.trace, n_phases, i, 0);
     if (i > 0) {
       if (tid == 0) wait_counter(p.counter, cnt0 + (uint64_t)i * (uint64_t)n_cta, ctx);
     }
@@ -640,8 +650,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
 
     if (!is_gemv) {
       // ================= attention of the new token (model.py:405-440), one kv head x sequence split per CTA =================
+      if (tid == 0) stamp(p.trace, n_phases, i, 1);
       attention_phase(p, ph, x_s, xq, pos, tag_in, tag_out, ctx);
-      if (tid == 0) red_ctr(p.counter);
+      if (tid == 0) {
+        red_ctr(p.counter);
+        stamp(p.trace, n_phases, i, 4);
+      }
       continue;
     }
 
@@ -651,6 +665,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
     const int n_chunks = Kx >> 3;
     const uint32_t limb_row = (uint32_t)KT * 64u + 32u;
     const uint64_t* in_pk = ph->in_off == kNone ? nullptr : xq + ph->in_off;
+    if (tid == 0) stamp(p.trace, n_phases, i, 1);
     float ss = 0.f;
     uint32_t amax_u = 0u;  // max |.| as bits: an Inf / NaN input shows up as >= 0x7f800000
     if (in_kind == IN_H) {
@@ -709,6 +724,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
       part[warp * 2 + 1] = __uint_as_float(amax_u);
     }
     named_bar_sync(1, kCT);  // B2
+    if (tid == 0) stamp(p.trace, n_phases, i, 6);
     float up, rnorm = 1.f;
     {
       float t = 0.f;
@@ -790,6 +806,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
       }
     }
     named_bar_sync(1, kCT);  // B3: limbs, segment sums and the row scale are in place
+    if (tid == 0) stamp(p.trace, n_phases, i, 2);
 
     // ================= main loop: warp w owns k-tiles 2 w, 2 w + 1 (128 k) of every stage =================
     int s0, s1;
@@ -867,6 +884,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
       __syncwarp();
       if (lane == 0) mbar_arrive(&red_full[rbuf]);
     }
+    if (tid == 0) stamp(p.trace, n_phases, i, 3);
     ++gphase;
   }
 }
@@ -1039,6 +1057,7 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   p.stages = pl.stages;
   p.off_x = pl.off_x; p.off_S = pl.off_S; p.off_red = pl.off_red; p.off_h = pl.off_h; p.off_misc = pl.off_misc;
   p.timeout_ns = (unsigned long long)(m->timeout_ms > 0 ? m->timeout_ms : 2000) * 1000000ull;
+  p.trace = static_cast<unsigned long long*>(m->trace);
   using KernelFn = void (*)(const Params);
   KernelFn kern = nullptr;
   int gi = 0;
