@@ -52,7 +52,8 @@ enum {
   AO_B200_ERR_INVALID_ARG = 1,   /* null pointer, bad shape, misaligned pointer */
   AO_B200_ERR_UNSUPPORTED = 2,   /* group size / M / arch not supported        */
   AO_B200_ERR_CUDA = 3,          /* a CUDA launch failed (cudaGetLastError)    */
-  AO_B200_ERR_WORKSPACE = 4      /* caller-provided workspace too small        */
+  AO_B200_ERR_WORKSPACE = 4,     /* caller-provided workspace too small        */
+  AO_B200_ERR_STATIC_SCRATCH = 5 /* ao_b200_decode_attention_static: needs more than AO_B200_STATIC_SCRATCH_BYTES */
 };
 
 /* how `tensor / python_scalar` is evaluated when restating the reference's eager ops */
@@ -223,6 +224,22 @@ AO_B200_API int64_t ao_b200_decode_attention_workspace_bytes(int B, int H, int n
 AO_B200_API int ao_b200_decode_attention(const void* q, const void* k_cache, const void* v_cache,
                              const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim, int S,
                              float scale, int n_split, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Allocation-free variant of ao_b200_decode_attention.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid allocation).  Same inputs, outputs and arithmetic as ao_b200_decode_attention, but the split partials
+ * (ao_b200_decode_attention_workspace_bytes(B, H, n_split) bytes) live in a file-scope `static __device__` array of
+ * AO_B200_STATIC_SCRATCH_BYTES (1 MiB: B * H * n_split <= 2016) inside the library image — every GPU that loads the
+ * library holds that 1 MiB until exit.  The call makes no cudaMalloc / cudaFree / allocating library call; the array's
+ * device address is resolved once per device with cudaGetSymbolAddress.  Larger problems are REJECTED with
+ * AO_B200_ERR_STATIC_SCRATCH (nothing is launched).  All calls on a device share the one array, which keeps the previous
+ * call's contents (nothing in it has to start at zero: each call writes every partial it later reads): calls that may
+ * overlap on the GPU (different streams, concurrent graphs) RACE on it — serialise them, or use ao_b200_decode_attention
+ * with caller-owned workspaces. */
+#define AO_B200_STATIC_SCRATCH_BYTES (1 << 20)
+AO_B200_API int ao_b200_decode_attention_static(const void* q, const void* k_cache, const void* v_cache,
+                                    const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim, int S,
+                                    float scale, int n_split, void* stream);
 
 /* Attention.forward for ONE new token in one launch (model.py:405-440): RoPE on q and the new k (model.py:547-559),
  * KV append at *input_pos (KVCache.update, model.py:175-192), GQA softmax(q K^T * scale) V over positions 0..pos split

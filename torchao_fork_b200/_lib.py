@@ -62,6 +62,7 @@ SIGNATURES = {
     "ao_b200_rope_kv_append": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "ao_b200_decode_attention_workspace_bytes": [_i32, _i32, _i32],
     "ao_b200_decode_attention": [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp, _i64, _vp],
+    "ao_b200_decode_attention_static": [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp],
     "ao_b200_decode_attention_fused_workspace_bytes": [_i32, _i32, _i32, _i32],
     "ao_b200_decode_attention_fused": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp, _i64,
                                        _vp],

@@ -33,6 +33,7 @@ extern "C" const char* ao_b200_error_string(int code) {
     case AO_B200_ERR_UNSUPPORTED: return "unsupported configuration";
     case AO_B200_ERR_CUDA: return "CUDA launch failed";
     case AO_B200_ERR_WORKSPACE: return "workspace too small";
+    case AO_B200_ERR_STATIC_SCRATCH: return "problem too large for the fixed static scratch (AO_B200_STATIC_SCRATCH_BYTES) of the allocation-free entry point";
   }
   return "unknown error";
 }

@@ -1,9 +1,16 @@
 // Non-GEMM remainder of one Llama decode step: fused residual-add + RMSNorm,
 // RoPE + KV-cache append, GQA decode attention, SiLU*mul.  All read the token position from DEVICE
 // memory so a captured CUDA graph can be replayed for every token.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace ao {
+
+// Scratch of ao_b200_decode_attention_static (bottom of this file): lives in the library image, every GPU that loads
+// the library holds it until exit.  In HOST code this name is only a stand-in for the symbol — the device address
+// comes from cudaGetSymbolAddress (static_scratch_ptr below), never from `&g_attn_static_scratch`.
+static __device__ __align__(256) unsigned char g_attn_static_scratch[AO_B200_STATIC_SCRATCH_BYTES];
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -516,4 +523,43 @@ extern "C" int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64
   silu_mul_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(gate_up),
                                                                       static_cast<__nv_bfloat16*>(out), B, I);
   return ao_launch_status();
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of ao_b200_decode_attention: the split partials live in g_attn_static_scratch.
+// ---------------------------------------------------------------------------------------
+// Device address of the static scratch on the CURRENT device: resolved once per device (cudaGetSymbolAddress with that
+// device current), then cached.  No allocation anywhere on this path.
+static int static_scratch_ptr(void** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static void* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return AO_B200_ERR_CUDA;
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, ao::g_attn_static_scratch) != cudaSuccess || p == nullptr) {
+      cudaGetLastError();
+      return AO_B200_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return AO_B200_OK;
+}
+
+extern "C" int ao_b200_decode_attention_static(const void* q, const void* k_cache, const void* v_cache,
+                                               const int32_t* input_pos, void* out, int B, int H, int Hkv, int head_dim,
+                                               int S, float scale, int n_split, void* stream) {
+  AO_CHECK_ARG(q && k_cache && v_cache && input_pos && out && B > 0 && H > 0 && Hkv > 0 && S > 0 && n_split >= 1);
+  // the partials of every (batch row, head, split) must fit the fixed array: reject, never truncate
+  if (ao_b200_decode_attention_workspace_bytes(B, H, n_split) > (int64_t)AO_B200_STATIC_SCRATCH_BYTES)
+    return AO_B200_ERR_STATIC_SCRATCH;
+  void* scratch = nullptr;
+  const int rc = static_scratch_ptr(&scratch);
+  if (rc != AO_B200_OK) return rc;
+  // every partial slot that the merge reads is written by the split kernel of the same call: nothing has to start at zero
+  return ao_b200_decode_attention(q, k_cache, v_cache, input_pos, out, B, H, Hkv, head_dim, S, scale, n_split, scratch,
+                                  (int64_t)AO_B200_STATIC_SCRATCH_BYTES, stream);
 }
