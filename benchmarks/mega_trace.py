@@ -31,7 +31,7 @@ def main():
     if args.layers:
         transformer_configs[spec["model"]]["n_layer"] = args.layers
     model, cfg = bench.build_model(spec, torch.device("cuda"))
-    gen = Generator(model, 1, args.pos + 64, temperature=0.8, top_k=200, use_graph=False)
+    gen = Generator(model, 1, args.pos + 64, temperature=0.8, top_k=200, use_graph=False, mega=True)
     eng = gen.engine
     assert eng.mega
     eng._setup_mega(trace=True)
@@ -52,6 +52,7 @@ def main():
     names = ["wqkv", "attn", "wo", "w13", "w2"]
     rep = {"step_us_with_sampling": step_us, "n_cta": n_cta, "phases": {}}
     rep["kernel_us_mean_over_ctas"] = float((tr[:, n_ph - 1, 3] - tr[:, 0, 0]).mean())
+    rep["slow_polls_total"] = int(eng._mega_state[16:20].view(torch.int32).item())  # sweeps that ran ahead of their packets (all steps)
 
     def mmm(x):
         return [round(float(x.mean()), 2), round(float(x.max()), 2), round(float(x.min()), 2)]
@@ -59,6 +60,7 @@ def main():
     def summarize(idx, gemv):
         d = {"wait": mmm(tr[:, idx, 1] - tr[:, idx, 0])}
         if gemv:
+            d["first_packets"] = mmm(tr[:, idx, 7] - tr[:, idx, 1])   # thread 0's own sweep loads: one loaded L2 round trip
             d["sweep_stats"] = mmm(tr[:, idx, 6] - tr[:, idx, 1])
             d["limbs"] = mmm(tr[:, idx, 2] - tr[:, idx, 6])
             d["main"] = mmm(tr[:, idx, 3] - tr[:, idx, 2])
@@ -68,6 +70,12 @@ def main():
         else:
             act = (tr[:, idx, 4] - tr[:, idx, 1])
             d["attn"] = mmm(act)
+            on = tr[:, idx, 2] > 0   # CTAs that own a slice of the attention
+            if on.any():
+                d["n_active"] = int(on.sum())
+                d["q_ready"] = mmm((tr[:, idx, 2] - tr[:, idx, 1])[on])      # qkv packets polled, RoPE, q in shared memory
+                d["tiles"] = mmm((tr[:, idx, 3] - tr[:, idx, 2])[on])        # K / V tiles out of the ring
+                d["merge_publish"] = mmm((tr[:, idx, 4] - tr[:, idx, 3])[on])
             d["total"] = mmm(tr[:, idx, 4] - tr[:, idx, 0])
         return d
 
@@ -76,7 +84,8 @@ def main():
         for l in range(1 if nl > 1 else 0, nl):
             for kk, v in summarize(5 * l + k, nm != "attn").items():
                 acc.setdefault(kk, []).append(v)
-        rep["phases"][nm] = {kk: [round(sum(x[j] for x in v) / len(v), 2) for j in range(3)] for kk, v in acc.items()}
+        rep["phases"][nm] = {kk: ([round(sum(x[j] for x in v) / len(v), 2) for j in range(3)] if isinstance(v[0], list) else v[0])
+                             for kk, v in acc.items()}
     rep["phases"]["output"] = summarize(n_ph - 1, True)
     rep["layer_us"] = round(sum(rep["phases"][nm]["total"][0] for nm in names), 2)
     print(json.dumps({k: v for k, v in rep.items() if k != "phases"}))

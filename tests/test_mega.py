@@ -55,7 +55,7 @@ def _fill_caches(m, T, seed=1):
 @pytest.mark.parametrize("group_size", [32, 64, 128, 256])
 def test_mega_step_matches_eager_forward(group_size):
     m = _tiny(group_size)
-    gen = Generator(m, 1, 64, temperature=0.0, top_k=None)
+    gen = Generator(m, 1, 64, temperature=0.0, top_k=None, mega=True)
     eng = gen.engine
     assert eng.mega, "batch-1 int4 decode must run the persistent kernel"
     T = 5
@@ -130,7 +130,7 @@ def test_mega_matches_per_projection_engine_and_graph_replay():
 
 def test_mega_greedy_generation_equals_eager_loop():
     m = _tiny(128, seed=3)
-    gen = Generator(m, 1, 64, temperature=0.0, top_k=None)
+    gen = Generator(m, 1, 64, temperature=0.0, top_k=None, mega=True)
     prompt = torch.randint(0, m.config.vocab_size, (6,))
     out = gen.generate(prompt, 12)
     # eager loop on the same model
@@ -154,7 +154,7 @@ def test_mega_greedy_generation_equals_eager_loop():
 
 def test_mega_sampling_path_and_streaming():
     m = _tiny(128)
-    gen = Generator(m, 1, 64, temperature=0.8, top_k=50)
+    gen = Generator(m, 1, 64, temperature=0.8, top_k=50, mega=True)
     assert gen.engine.mega
     prompt = torch.randint(0, m.config.vocab_size, (6,))
     torch.manual_seed(5)
@@ -169,7 +169,7 @@ def test_mega_nan_activation_propagates():
     """A non-finite hidden state must come out as NaN logits (the reference's bf16 matmul propagates NaN), not as
     finite garbage from the fixed-point staging."""
     m = _tiny(128)
-    gen = Generator(m, 1, 32, temperature=0.0, top_k=None)
+    gen = Generator(m, 1, 32, temperature=0.0, top_k=None, mega=True)
     emb = m.tok_embeddings.weight
     saved = emb[5].clone()
     emb.data[5, 17] = float("nan")
@@ -182,7 +182,7 @@ def test_mega_nan_activation_propagates():
 
 def test_mega_step_past_cache_raises():
     m = _tiny(128)
-    gen = Generator(m, 1, 16, temperature=0.0, top_k=None)
+    gen = Generator(m, 1, 16, temperature=0.0, top_k=None, mega=True)
     eng = gen.engine
     with pytest.raises(ValueError):
         eng.set_state(torch.tensor([1], device="cuda"), 16)
@@ -198,7 +198,7 @@ def test_mega_step_past_cache_raises():
 def test_mega_gqa_group_of_eight_and_odd_layer_count():
     """Llama-3-70B's head ratio (8 q heads per kv head) and a strip count that does not divide the CTA count."""
     m = _tiny(128, n_head=16, n_local_heads=2, dim=2048, intermediate_size=2304, n_layer=3, vocab_size=2000)
-    gen = Generator(m, 1, 64, temperature=0.0, top_k=None)
+    gen = Generator(m, 1, 64, temperature=0.0, top_k=None, mega=True)
     eng = gen.engine
     assert eng.mega
     _fill_caches(m, 9)

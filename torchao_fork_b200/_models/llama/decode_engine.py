@@ -24,6 +24,11 @@ from ...dtypes.layouts import PlainAQTTensorImpl, TensorCoreTiledAQTTensorImpl
 from .model import Transformer
 
 
+# persistent one-launch-per-token kernel (csrc/decode_mega.cu) as the batch-1 int4 default: "1" once it beats the
+# per-projection graph on the bench (profiles/), AO_B200_MEGA overrides
+MEGA_DEFAULT = "0"
+
+
 def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
 
@@ -205,7 +210,7 @@ class DecodeEngine:
                     and len({l[k].group_size for l in self.layers for k in ("wqkv", "wo", "w13", "w2")} | {self.output.group_size}) == 1
                     and D % 128 == 0 and self.I % 128 == 0 and self.H // self.Hkv <= 8)
         if mega is None:
-            mega = can_mega and os.environ.get("AO_B200_MEGA", "1") != "0"
+            mega = can_mega and os.environ.get("AO_B200_MEGA", MEGA_DEFAULT) != "0"
         assert not mega or can_mega, "the persistent decode kernel needs batch 1 and int4 weight-only linears everywhere"
         self.mega = bool(mega)
         if self.mega:

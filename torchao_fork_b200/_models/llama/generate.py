@@ -46,12 +46,12 @@ class Generator:
     """Owns the caches, the DecodeEngine and its CUDA graph for one (model, batch_size, max_seq_length)."""
 
     def __init__(self, model: Transformer, batch_size: int, max_seq_length: int, temperature: float = 0.8,
-                 top_k: Optional[int] = 200, use_graph: bool = True, tp=None):
+                 top_k: Optional[int] = 200, use_graph: bool = True, tp=None, mega: Optional[bool] = None):
         self.model = model
         self.batch_size = batch_size
         dev = model.tok_embeddings.weight.device
         model.setup_caches(batch_size, max_seq_length, device=dev)
-        self.engine = DecodeEngine(model, batch_size, temperature, top_k, tp=tp)
+        self.engine = DecodeEngine(model, batch_size, temperature, top_k, tp=tp, mega=mega)
         if use_graph:
             self.engine.capture()
         self.sampling = dict(temperature=temperature, top_k=top_k)

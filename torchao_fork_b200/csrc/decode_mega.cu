@@ -1,16 +1,17 @@
 // One decode step of the gpt-fast Llama (torchao/_models/llama/model.py:342-486, generate.py:111-117) as ONE persistent,
-// cooperative launch: every SM runs one CTA for the whole token, and the int4 weight stream never drains between
-// projections.
+// cooperative launch: every SM runs one CTA for the whole token, and the weight stream never drains between projections.
 //
 // Why: with one launch per projection (round 1: 161 launches per token) each launch pays a fixed 3.5 - 5 us (dependency
 // resolution, cold instruction cache, activation staging, pipeline fill, drain) around 1.3 - 9.6 us of streaming; the step
 // ran at 0.43 of the HBM roofline.  Here a CTA is
-//   * 1 producer warp that walks the CTA's share of EVERY weight of the model in order (bulk-copy ring in shared memory:
-//     16 KB of nibbles + the groups' scale / zero per stage) and never waits for anything but a free ring slot: while the
-//     consumers exchange activations between two projections, the ring fills with the next projection's weights;
+//   * 1 producer warp that walks the CTA's share of EVERY byte the token streams, in order — the int4 weights of every
+//     projection (16 KB of nibbles + the groups' scale / zero per stage) and, for the CTAs that own a slice of the
+//     attention, the K / V cache rows (32 positions per stage) — through ONE bulk-copy ring in shared memory.  It never
+//     waits for anything but a free ring slot: while the consumers hand activations over between two projections the
+//     ring fills with the next projection's weights, and the K / V rows of a layer are on chip before its q exists;
 //   * 16 consumer warps: integer tensor-core inner product of gemv_int4_imma.cu (nibbles -> bytes, mma.sync m16n8k32
 //     u8 x s8, activations as three balanced int8 limbs of 23-bit fixed point, exact int32 group sums, affine dequant on
-//     the accumulator in fp32) + the attention of the token + the staging of the next projection's activations;
+//     the accumulator in fp32), the attention of the token out of the ring, the staging of the next projection's input;
 //   * 1 epilogue warp: cross-warp sums, limb recombination, SiLU*mul, publishing the outputs.
 //
 // Hand-over between projections (every output element depends on the whole input vector: an all-to-all over the CTAs):
@@ -28,6 +29,10 @@
 //
 // Every wait in the kernel is bounded (globaltimer): on a time-out the CTA raises a sticky status word, stops waiting
 // and runs its remaining control flow without blocking, so a bug or a dead peer ends the launch instead of hanging the GPU.
+//
+// Code organisation: the three roles and the consumer's three jobs (input staging, main loop, attention) are separate
+// NON-inlined functions — each gets the whole register file for its own loop instead of sharing one allocation across a
+// 900-line kernel (the first version kept ring indices in local memory inside the main loop).
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -48,32 +53,55 @@ constexpr int kRedBufs = 2;
 constexpr uint32_t kMagicI = 0x4B400000u;    // bits of 1.5 * 2^23
 constexpr float kMagicF = 12582912.0f;
 constexpr int kMaxWorld = 8;
-constexpr int kHG = 4;                       // q heads per attention pass
-constexpr int kQPad = 136;                   // q row stride in floats (two 64-dim halves, the second shifted by 4 floats)
+constexpr int kAttnPos = 32;                 // cache positions per ring stage: 8 KB of K rows + 8 KB of V rows
 constexpr int kPartStride = 132;             // attention partial: 128 acc + m + l (+ pad)
+constexpr int kHdrBytes = 128;               // shared-memory header (wait context) in front of the ring
 
 enum { PH_GEMV = 0, PH_ATTN = 1 };
 enum { IN_H = 0, IN_PK = 1 };
 enum { OUT_PK = 0, OUT_DELTA = 1, OUT_SILU = 2, OUT_PLAIN = 3 };
 constexpr uint32_t kNone = 0xffffffffu;
 
-struct alignas(16) Phase {
-  const uint8_t* packed;          // strip-major int4 [Np/16][Kp/64][512 B]
-  const uint32_t* sz;             // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
-  const __nv_bfloat16* norm_w;    // IN_H: RMSNorm weight [Kx]
-  __nv_bfloat16* out_plain;       // OUT_PLAIN: bf16 [N_out]
-  __nv_bfloat16* k_cache;         // PH_ATTN: [Hkv][S][128]
-  __nv_bfloat16* v_cache;
-  uint32_t in_off;                // packet offset in the exchange region: IN_PK input, IN_H deltas [world][Kx / 2] (kNone: no delta), ATTN qkv
+// Per-layer pointers (global memory, filled by ao_b200_decode_mega_setup, copied to shared memory at kernel start) and
+// per-kind constants (kernel parameters = constant bank): a phase's description costs no global load on the critical path
+// (the first version read a 96-byte Phase record per phase from global memory: a DRAM miss per phase per SM, because the
+// weight stream evicts it from L2 between tokens).
+struct alignas(16) LayerPtrs {      // 96 bytes
+  const uint8_t* w[4];              // wqkv, wo, w13, w2: strip-major int4 [Np/16][Kp/64][512 B]
+  const uint32_t* sz[4];            // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
+  const __nv_bfloat16* norm[2];     // attention_norm, ffn_norm
+  __nv_bfloat16* kc;                // [Hkv][S][128]
+  __nv_bfloat16* vc;
+};
+enum { K_WQKV = 0, K_ATTN = 1, K_WO = 2, K_W13 = 3, K_W2 = 4, K_OUT = 5, kKinds = 6 };
+struct Kind {
+  uint32_t in_off;                // packet offset in the exchange region: IN_PK input, IN_H deltas [world][Kx / 2], ATTN qkv
   uint32_t out_off;               // packet offset of the output (OUT_DELTA: + rank * N_out / 2 in every peer's region)
   uint32_t aux_off;               // ATTN: split partials
   int type, in_kind, out_kind;
-  int KT, n_strips, N_out, Kx, rot;
+  int KT, n_strips, N_out, Kx, rot_inc;
+};
+// a phase as the roles see it (registers)
+struct Phase {
+  const uint8_t* packed;
+  const uint32_t* sz;
+  const __nv_bfloat16* norm_w;
+  __nv_bfloat16* out_plain;
+  __nv_bfloat16* k_cache;
+  __nv_bfloat16* v_cache;
+  uint32_t in_off, out_off, aux_off;
+  int type, in_kind, out_kind;
+  int KT, n_strips, N_out, Kx, rot_inc;
 };
 
 struct Params {
-  const Phase* phases;
-  int n_phases, n_cta;
+  const LayerPtrs* layers;        // global [n_layer]
+  Kind kinds[kKinds];
+  const uint8_t* out_w;           // the output projection
+  const uint32_t* out_sz;
+  const __nv_bfloat16* out_norm;
+  __nv_bfloat16* logits;
+  int n_layer, n_phases, n_cta;
   uint64_t* xchg[kMaxWorld];      // exchange regions: own at [rank], the peers' as mapped here
   int world, rank;
   const __nv_bfloat16* emb;
@@ -83,13 +111,26 @@ struct Params {
   uint64_t* counter;              // arrivals, monotonic over the life of the state buffer
   uint32_t* step;                 // launches so far
   uint32_t* status;               // sticky error bits
-  int dim, H, Hkv, S, attn_bpc, attn_max_split;
+  int dim, H, Hkv, S, attn_spc, attn_max_split;
   float eps, attn_scale;
   int stages;
-  uint32_t off_x, off_S, off_red, off_h, off_misc;
+  uint32_t off_x, off_S, off_red, off_h, off_misc, off_lay;
   unsigned long long timeout_ns;
   unsigned long long* trace;      // optional: [n_cta][n_phases][8] clock64 stamps (benchmarks/mega_trace.py)
+  int dbg;                        // profiling switches (AO_B200_MEGA_DEBUG): 1 = main loops skip the math (stream only)
 };
+
+// wait context at the start of dynamic shared memory: reachable from every (non-inlined) function without arguments
+struct SCtx {
+  uint32_t abort;                 // this CTA stopped waiting
+  uint32_t pad;
+  uint32_t* status;
+  unsigned long long timeout_ns;
+};
+__device__ __forceinline__ SCtx* sctx() {
+  extern __shared__ __align__(128) uint8_t smem_mega[];
+  return reinterpret_cast<SCtx*>(smem_mega);
+}
 
 // ------------------------------------------------------------------------------------------------ small helpers
 __device__ __forceinline__ float warp_sum(float v) {
@@ -114,26 +155,45 @@ __device__ __forceinline__ uint2 lds64u(uint32_t a) {
   asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
   return v;
 }
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ unsigned long long globaltimer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
+// mbarriers by 32-bit shared-window address
+__device__ __forceinline__ bool bar_try(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void bar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_u(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar) : "memory");
+}
 // packets: single 8-byte accesses that bypass the (incoherent) L1.  `.sys` scope: the exchange regions are also written
 // by NVLink peers; on local memory it costs the same as `.gpu`.
 __device__ __forceinline__ uint64_t ld_pk(const uint64_t* p) {
   uint64_t v;
-  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ ulonglong2 ld_pk2(const uint64_t* p) {
   ulonglong2 v;
-  asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_pk(uint64_t* p, uint32_t data, uint32_t tag) {
   const uint64_t v = (uint64_t)data | ((uint64_t)tag << 32);
-  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ uint64_t ld_ctr(const uint64_t* p) {
   uint64_t v;
@@ -143,93 +203,91 @@ __device__ __forceinline__ uint64_t ld_ctr(const uint64_t* p) {
 __device__ __forceinline__ void red_ctr(uint64_t* p) {
   asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" ::"l"(p) : "memory");
 }
-
 __device__ __forceinline__ void stamp(unsigned long long* trace, int n_phases, int i, int k) {
   if (trace != nullptr) trace[((size_t)blockIdx.x * n_phases + i) * 8 + k] = (unsigned long long)clock64();
 }
 
-struct Ctx {
-  volatile uint32_t* abort_s;   // shared: this CTA stopped waiting
-  uint32_t* status;             // global sticky status
-  unsigned long long timeout_ns;
-};
-__device__ __noinline__ void raise_abort(const Ctx& c, uint32_t code) {
-  *c.abort_s = 1u;
-  atomicOr(c.status, code);
+// ------------------------------------------------------------------------------------------------ bounded waits
+__device__ __noinline__ void raise_abort(uint32_t code) {
+  SCtx* c = sctx();
+  *reinterpret_cast<volatile uint32_t*>(&c->abort) = 1u;
+  atomicOr(c->status, code);
 }
-// bounded mbarrier wait
-__device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parity, const Ctx& c, uint32_t code) {
+__device__ __forceinline__ bool aborted() { return *reinterpret_cast<volatile uint32_t*>(&sctx()->abort) != 0u; }
+
+__device__ __noinline__ void bar_wait_slow(uint32_t bar, uint32_t parity, uint32_t code) {
   const unsigned long long t0 = globaltimer();
+  const unsigned long long lim = sctx()->timeout_ns;
   uint32_t n = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (*c.abort_s) return;
-    if ((++n & 15u) == 0 && globaltimer() - t0 > c.timeout_ns) {
-      raise_abort(c, code);
+  while (!bar_try(bar, parity)) {
+    if (aborted()) return;
+    if ((++n & 15u) == 0 && globaltimer() - t0 > lim) {
+      raise_abort(code);
       return;
     }
   }
 }
-__device__ __forceinline__ void mbar_wait_b(uint64_t* bar, uint32_t parity, const Ctx& c, uint32_t code) {
-  if (mbar_try_wait(bar, parity)) return;
-  mbar_wait_slow(bar, parity, c, code);
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity, uint32_t code) {
+  if (bar_try(bar, parity)) return;
+  bar_wait_slow(bar, parity, code);
 }
-// bounded wait for the arrival counter (one lane per CTA)
-__device__ __noinline__ void wait_counter(const uint64_t* ctr, uint64_t target, const Ctx& c) {
+// the arrival counter (one lane per CTA polls; no back-off: 148 pollers of one line are no load for the L2)
+__device__ __noinline__ void wait_counter(const uint64_t* ctr, uint64_t target) {
   if (ld_ctr(ctr) >= target) return;
   const unsigned long long t0 = globaltimer();
+  const unsigned long long lim = sctx()->timeout_ns;
   uint32_t n = 0;
   for (;;) {
     if (ld_ctr(ctr) >= target) return;
-    if (*c.abort_s) return;
-    __nanosleep(20);
     if ((++n & 63u) == 0) {
-      if (globaltimer() - t0 > c.timeout_ns) {
-        raise_abort(c, 2u);
+      if (aborted()) return;
+      if (globaltimer() - t0 > lim) {
+        raise_abort(2u);
         return;
       }
-      if (*reinterpret_cast<volatile uint32_t*>(c.status) != 0u) {  // somebody else gave up: do not wait for them
-        *c.abort_s = 1u;
+      if (*reinterpret_cast<volatile uint32_t*>(sctx()->status) != 0u) {  // somebody else gave up: do not wait for them
+        *reinterpret_cast<volatile uint32_t*>(&sctx()->abort) = 1u;
         return;
       }
     }
   }
 }
-// bounded wait for one packet
-__device__ __noinline__ uint32_t poll_pk_slow(const uint64_t* p, uint32_t tag, const Ctx& c) {
+// one packet
+__device__ __noinline__ uint32_t poll_pk_slow(const uint64_t* p, uint32_t tag) {
+  atomicAdd(sctx()->status + 1, 1u);  // statistics: how often a sweep ran ahead of its packets (state word 4)
   const unsigned long long t0 = globaltimer();
+  const unsigned long long lim = sctx()->timeout_ns;
   uint32_t n = 0;
   for (;;) {
     const uint64_t v = ld_pk(p);
     if ((uint32_t)(v >> 32) == tag) return (uint32_t)v;
-    if (*c.abort_s) return 0u;
-    if ((++n & 63u) == 0 && globaltimer() - t0 > c.timeout_ns) {
-      raise_abort(c, 4u);
-      return 0u;
+    if ((++n & 63u) == 0) {
+      if (aborted()) return 0u;
+      if (globaltimer() - t0 > lim) {
+        raise_abort(4u);
+        return 0u;
+      }
     }
   }
 }
-__device__ __forceinline__ uint32_t poll_pk(const uint64_t* p, uint32_t tag, const Ctx& c) {
+__device__ __forceinline__ uint32_t poll_pk(const uint64_t* p, uint32_t tag) {
   const uint64_t v = ld_pk(p);
   if ((uint32_t)(v >> 32) == tag) return (uint32_t)v;
-  return poll_pk_slow(p, tag, c);
+  return poll_pk_slow(p, tag);
 }
 // 4 consecutive packets (8 bf16 = one staging chunk); p is 32-byte aligned
-__device__ __forceinline__ uint4 poll_chunk(const uint64_t* p, uint32_t tag, const Ctx& c) {
+__device__ __forceinline__ uint4 poll_chunk(const uint64_t* p, uint32_t tag) {
   const ulonglong2 a = ld_pk2(p), b = ld_pk2(p + 2);
   uint4 r = make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
   const bool ok = ((uint32_t)(a.x >> 32) == tag) & ((uint32_t)(a.y >> 32) == tag) & ((uint32_t)(b.x >> 32) == tag) &
                   ((uint32_t)(b.y >> 32) == tag);
   if (!ok) {
-    r.x = poll_pk_slow(p, tag, c);
-    r.y = poll_pk_slow(p + 1, tag, c);
-    r.z = poll_pk_slow(p + 2, tag, c);
-    r.w = poll_pk_slow(p + 3, tag, c);
+    r.x = poll_pk_slow(p, tag);
+    r.y = poll_pk_slow(p + 1, tag);
+    r.z = poll_pk_slow(p + 2, tag);
+    r.w = poll_pk_slow(p + 3, tag);
   }
   return r;
-}
-__device__ __forceinline__ uint4 load_chunk(const uint64_t* p) {  // packets known to be present
-  const ulonglong2 a = ld_pk2(p), b = ld_pk2(p + 2);
-  return make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
 }
 
 __device__ __forceinline__ void strip_range(int b, int n_cta, int n_strips, int rot, int& s0, int& s1) {
@@ -238,6 +296,27 @@ __device__ __forceinline__ void strip_range(int b, int n_cta, int n_strips, int 
   const int base = n_strips / n_cta, rem = n_strips - base * n_cta;
   s0 = bb * base + min(bb, rem);
   s1 = s0 + base + (bb < rem ? 1 : 0);
+}
+
+// which slice of a layer's attention this CTA owns: (kv head, range of 32-position tiles).  The producer (which streams
+// the K / V rows) and the consumers (which eat them) evaluate the same function.
+struct AttnPart {
+  int active, kvh, split, nsplit, t0, t1, n_t, len;
+};
+__device__ __forceinline__ AttnPart attn_partition(int pos, int S, int Hkv, int spc, int max_split, int b) {
+  AttnPart a;
+  a.len = min(pos + 1, S);                              // positions 0 .. pos (the new token included)
+  a.n_t = (a.len + kAttnPos - 1) / kAttnPos;
+  int ns = min(max_split, (a.n_t + spc - 1) / spc);
+  const int tps = (a.n_t + ns - 1) / ns;                // tiles per split
+  ns = (a.n_t + tps - 1) / tps;
+  a.nsplit = ns;
+  a.active = b < Hkv * ns;
+  a.kvh = b % Hkv;
+  a.split = b / Hkv;
+  a.t0 = a.split * tps;
+  a.t1 = min(a.t0 + tps, a.n_t);
+  return a;
 }
 
 template <int G>
@@ -249,641 +328,927 @@ struct Geom {
   static constexpr int kStageBytes = kStageW + kStageSZ;
 };
 
-// ------------------------------------------------------------------------------------------------ attention phase
-// Attention.forward for the new token (model.py:405-440): one (kv head, sequence split) per CTA, the Gq q heads of the
-// group share every K / V row.  16-position blocks: two lanes per position (64 dims each) for q.K, lane-parallel
-// dims for P.V; the 16 warps' (m, l, acc) are merged through shared memory, splits through {fp32 | tag} packets.
-// Its own function (not inlined): the walk wants the whole register file, the caller's state is parked once per phase.
-__device__ __noinline__ void attention_phase(const Params& p, const Phase* ph, uint8_t* x_s, uint64_t* xq, int pos,
-                                             uint32_t tag_in, uint32_t tag_out, const Ctx& ctx) {
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.x;
+// shared-memory addresses of the barriers, derived from the first one
+struct Bars {
+  uint32_t full, empty, red_full, red_free;
+};
+__device__ __forceinline__ Bars make_bars(uint32_t first, int stages) {
+  Bars b;
+  b.full = first;
+  b.empty = first + 8u * stages;
+  b.red_full = b.empty + 8u * stages;
+  b.red_free = b.red_full + 8u * kRedBufs;
+  return b;
+}
 
-  const int H = p.H, Hkv = p.Hkv, S = p.S;
-  const int Gq = H / Hkv;
-  const int len = min(pos + 1, S);
-  const int nblk = (len + 15) >> 4;
-  int nsplit = min(p.attn_max_split, (nblk + p.attn_bpc - 1) / p.attn_bpc);
-  const int bps = (nblk + nsplit - 1) / nsplit;
-  nsplit = (nblk + bps - 1) / bps;
-  const bool active = b < Hkv * nsplit;
-  if (active) {
-    const int kvh = b % Hkv, split = b / Hkv;
-    const bool owner = split == (nblk - 1) / bps && pos < S;
-    float* q_s = reinterpret_cast<float*>(x_s);                 // [Gq][kQPad]
-    float* part_s = q_s + ((Gq * kQPad + 31) & ~31);            // [16 warps][kHG][kPartStride]
-    __nv_bfloat16* kc = ph->k_cache + (int64_t)kvh * S * 128;
-    __nv_bfloat16* vc = ph->v_cache + (int64_t)kvh * S * 128;
-    const uint64_t* qkv = xq + ph->in_off;
-    for (int idx = tid; idx < (Gq + 2) * 64; idx += kCT) {
-      const int which = idx >> 6, pr = idx & 63;
-      const int elem = which < Gq ? (kvh * Gq + which) * 128 : (which == Gq ? (H + kvh) * 128 : (H + Hkv + kvh) * 128);
-      const uint32_t raw = poll_pk(qkv + (elem >> 1) + pr, tag_in, ctx);
-      uint32_t o = raw;
-      float r0 = 0.f, r1 = 0.f;
-      if (which <= Gq) {
-        const uint32_t cs = __ldg(reinterpret_cast<const uint32_t*>(p.freqs) + (int64_t)min(pos, S - 1) * 64 + pr);
-        const float x0 = __uint_as_float(raw << 16), x1 = __uint_as_float(raw & 0xFFFF0000u);
-        const float cc = __uint_as_float(cs << 16), ss = __uint_as_float(cs & 0xFFFF0000u);
-        r0 = bf16r(x0 * cc - x1 * ss);
-        r1 = bf16r(x1 * cc + x0 * ss);
-        o = float_to_bf16_bits(r0) | (float_to_bf16_bits(r1) << 16);
+// phase i -> its description (constant bank + the layer's pointers in shared memory)
+__device__ __forceinline__ Phase get_phase(const Params& p, int i) {
+  extern __shared__ __align__(128) uint8_t smem_mega[];
+  const LayerPtrs* lay_s = reinterpret_cast<const LayerPtrs*>(smem_mega + p.off_lay);
+  const int layer = i / 5;
+  const int kind = layer == p.n_layer ? (int)K_OUT : i - 5 * layer;
+  const Kind& k = p.kinds[kind];
+  Phase ph;
+  ph.in_off = (i == 0) ? kNone : k.in_off;   // the first projection of the token has no delta to add
+  ph.out_off = k.out_off; ph.aux_off = k.aux_off;
+  ph.type = k.type; ph.in_kind = k.in_kind; ph.out_kind = k.out_kind;
+  ph.KT = k.KT; ph.n_strips = k.n_strips; ph.N_out = k.N_out; ph.Kx = k.Kx; ph.rot_inc = k.rot_inc;
+  ph.packed = nullptr; ph.sz = nullptr; ph.norm_w = nullptr; ph.out_plain = nullptr; ph.k_cache = nullptr; ph.v_cache = nullptr;
+  if (kind == K_OUT) {
+    ph.packed = p.out_w; ph.sz = p.out_sz; ph.norm_w = p.out_norm; ph.out_plain = p.logits;
+  } else if (kind == K_ATTN) {
+    ph.k_cache = lay_s[layer].kc; ph.v_cache = lay_s[layer].vc;
+  } else {
+    const int wi = kind == K_WQKV ? 0 : kind - 1;
+    ph.packed = lay_s[layer].w[wi]; ph.sz = lay_s[layer].sz[wi];
+    if (kind == K_WQKV) ph.norm_w = lay_s[layer].norm[0];
+    if (kind == K_W13) ph.norm_w = lay_s[layer].norm[1];
+  }
+  return ph;
+}
+__device__ __forceinline__ int next_rot(int rot, int inc, int n_cta) {
+  rot += inc;
+  return rot >= n_cta ? rot - n_cta : rot;
+}
+
+// ------------------------------------------------------------------------------------------------ producer warp
+// The CTA's share of every byte of the token, in phase order, through the ring.
+template <int G>
+__device__ __noinline__ void producer_loop(const Params& p, int pos, uint32_t ring_u, uint32_t bar0) {
+  constexpr int kStageBytes = Geom<G>::kStageBytes;
+  const int b = blockIdx.x, n_cta = p.n_cta, stages = p.stages, n_phases = p.n_phases;
+  const Bars bars = make_bars(bar0, stages);
+  int slot = 0, rot = 0;
+  uint32_t par = 1;
+  for (int i = 0; i < n_phases; ++i) {
+    const Phase phv = get_phase(p, i);
+    const Phase* ph = &phv;
+    if (ph->type == PH_GEMV) {
+      const int KT = ph->KT;
+      int s0, s1;
+      strip_range(b, n_cta, ph->n_strips, rot, s0, s1);
+      rot = next_rot(rot, ph->rot_inc, n_cta);
+      const int n_groups = KT * 64 / G;
+      const uint8_t* wrow = ph->packed + (int64_t)s0 * KT * 512;
+      const uint32_t* srow = ph->sz + (int64_t)s0 * n_groups * 16;
+      for (int strip = s0; strip < s1; ++strip) {
+        for (int kt0 = 0; kt0 < KT; kt0 += kStageTiles) {
+          const int cnt = min(kStageTiles, KT - kt0);
+          const uint32_t dst = ring_u + (uint32_t)slot * kStageBytes;
+          bar_wait(bars.empty + 8u * slot, par, 8u);
+          const uint32_t sz_bytes = (uint32_t)(cnt * 64 / G) * 64u;
+          bar_expect_tx(bars.full + 8u * slot, (uint32_t)(cnt * 512) + sz_bytes);
+          bulk_g2s_u(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), bars.full + 8u * slot);
+          bulk_g2s_u(dst + kStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, bars.full + 8u * slot);
+          if (++slot == stages) {
+            slot = 0;
+            par ^= 1u;
+          }
+        }
+        wrow += (int64_t)KT * 512;
+        srow += (int64_t)n_groups * 16;
       }
-      if (which < Gq) {
-        const int d = 2 * pr + (pr >= 32 ? 4 : 0);
-        *reinterpret_cast<float2*>(q_s + which * kQPad + d) = make_float2(r0 * p.attn_scale, r1 * p.attn_scale);
-      } else if (owner) {
-        __nv_bfloat16* dst = (which == Gq ? kc : vc) + (int64_t)pos * 128 + 2 * pr;
-        *reinterpret_cast<uint32_t*>(dst) = o;
+    } else {
+      // K / V rows of this CTA's attention slice: rows [32 t, 32 t + 32) of the kv head, K into the first 8 KB of the
+      // stage, V into the second.  Rows written by EARLIER launches only; the new token's row is patched in by the
+      // consumers (attention_phase).
+      const AttnPart a = attn_partition(pos, p.S, p.Hkv, p.attn_spc, p.attn_max_split, b);
+      if (a.active) {
+        const __nv_bfloat16* kc = ph->k_cache + (int64_t)a.kvh * p.S * 128;
+        const __nv_bfloat16* vc = ph->v_cache + (int64_t)a.kvh * p.S * 128;
+        for (int t = a.t0; t < a.t1; ++t) {
+          const int j0 = t * kAttnPos;
+          const uint32_t bytes = (uint32_t)min(kAttnPos, p.S - j0) * 256u;
+          const uint32_t dst = ring_u + (uint32_t)slot * kStageBytes;
+          bar_wait(bars.empty + 8u * slot, par, 8u);
+          bar_expect_tx(bars.full + 8u * slot, 2u * bytes);
+          bulk_g2s_u(dst, kc + (int64_t)j0 * 128, bytes, bars.full + 8u * slot);
+          bulk_g2s_u(dst + 8192u, vc + (int64_t)j0 * 128, bytes, bars.full + 8u * slot);
+          if (++slot == stages) {
+            slot = 0;
+            par ^= 1u;
+          }
+        }
       }
     }
-    named_bar_sync(1, kCT);  // q in shared memory; the new k / v row is visible to this CTA
-    const int blk_end = min((split + 1) * bps, nblk);
-    const int pj_idx = lane >> 1, half = lane & 1;
-    for (int hp = 0; hp < Gq; hp += kHG) {
-      float m[kHG], l[kHG], acc[kHG][4];
+    stamp(p.trace, n_phases, i, 5);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ epilogue warp
+// Per strip: sum the 16 consumer warps' partials, recombine the limbs, apply the row scale, publish.
+__device__ __noinline__ void epilogue_loop(const Params& p, int pos, uint32_t step, uint32_t red_u, uint32_t bar0,
+                                           const float* row_scale) {
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2, c = lane & 3;
+  const int b = blockIdx.x, n_cta = p.n_cta, n_phases = p.n_phases;
+  const Bars bars = make_bars(bar0, p.stages);
+  const uint32_t tag0 = step * (uint32_t)n_phases;
+  uint64_t* xq = p.xchg[p.rank];
+  uint32_t li = 0;   // strips handed over so far (all phases)
+  int gphase = 0;    // GEMV phases so far
+  int rot = 0;
+  for (int i = 0; i < n_phases; ++i) {
+    const Phase phv = get_phase(p, i);
+    const Phase* ph = &phv;
+    if (ph->type != PH_GEMV) continue;
+    int s0, s1;
+    strip_range(b, n_cta, ph->n_strips, rot, s0, s1);
+    rot = next_rot(rot, ph->rot_inc, n_cta);
+    const int out_kind = ph->out_kind;
+    const int N_out = ph->N_out;
+    const uint32_t tag = tag0 + (uint32_t)i + 1u;
+    const uint32_t out_off = ph->out_off;
+    __nv_bfloat16* out_plain = ph->out_plain;
+    for (int strip = s0; strip < s1; ++strip, ++li) {
+      const uint32_t rbuf = li & 1u;
+      const uint32_t use = li >> 1;
+      const uint32_t rb = red_u + rbuf * (kC * 128 * 4) + (uint32_t)lane * 16u;
+      bar_wait(bars.red_full + 8u * rbuf, use & 1u, 16u);
+      uint64_t vlo = 0ull, vhi = 0ull;
 #pragma unroll
-      for (int h = 0; h < kHG; ++h) {
-        m[h] = -INFINITY;
-        l[h] = 0.f;
-        acc[h][0] = acc[h][1] = acc[h][2] = acc[h][3] = 0.f;
+      for (int w = 0; w < kC; ++w) {
+        const uint4 t = lds128(rb + (uint32_t)w * 512u);
+        const uint64_t tx = (uint64_t)t.x | ((uint64_t)t.y << 32), ty = (uint64_t)t.z | ((uint64_t)t.w << 32);
+        asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vlo) : "l"(tx));
+        asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vhi) : "l"(ty));
       }
-      for (int blk = split * bps + warp; blk < blk_end; blk += kC) {
-        const int j = blk * 16 + pj_idx;
-        const bool valid = j < len;
-        uint4 kk[8];
-        {
-          const uint4* krow = reinterpret_cast<const uint4*>(kc + (int64_t)(valid ? j : blk * 16) * 128 + half * 64);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) kk[q] = krow[q];
+      const float4 v = make_float4(__uint_as_float((uint32_t)vlo), __uint_as_float((uint32_t)(vlo >> 32)),
+                                   __uint_as_float((uint32_t)vhi), __uint_as_float((uint32_t)(vhi >> 32)));
+      __syncwarp();
+      if (lane == 0) bar_arrive(bars.red_free + 8u * rbuf);
+      // limb recombination (M = 1): lane (g, c = 0) holds limbs 0, 1 of rows g (x, y) and g + 8 (z, w); limb 2 sits in
+      // lane (g, c = 1).x / .z
+      const float t2x = __shfl_down_sync(0xffffffffu, v.x, 1), t2z = __shfl_down_sync(0xffffffffu, v.z, 1);
+      const float rsc = row_scale[gphase & 1];
+      const float v0 = fmaf(65536.f, v.x, fmaf(256.f, v.y, t2x)) * rsc;   // row g      (valid on lanes c == 0)
+      const float v1 = fmaf(65536.f, v.z, fmaf(256.f, v.w, t2z)) * rsc;   // row g + 8
+      if (out_kind == OUT_SILU) {
+        // rows g = gate (w1), rows g + 8 = up (w3) of output n = 8 strip + g   (model.py:486)
+        const float gate = bf16r(v0), up = bf16r(v1);
+        const float sg = bf16r(gate / (1.f + __expf(-gate)));
+        const uint32_t o = float_to_bf16_bits(sg * up);
+        const uint32_t on = __shfl_down_sync(0xffffffffu, o, 4);  // row g + 1
+        const int n = 8 * strip + g;
+        if (c == 0 && (g & 1) == 0 && n < N_out) st_pk(xq + out_off + (n >> 1), o | (on << 16), tag);
+      } else if (out_kind == OUT_PLAIN) {
+        const int n0 = 16 * strip + g;
+        if (c == 0) {
+          if (n0 < N_out) out_plain[n0] = __float2bfloat16_rn(v0);
+          if (n0 + 8 < N_out) out_plain[n0 + 8] = __float2bfloat16_rn(v1);
         }
-        float sc[kHG];
-#pragma unroll
-        for (int h = 0; h < kHG; ++h) sc[h] = 0.f;
-        // (asm volatile shared loads: q is block-invariant, and the compiler would otherwise hoist all 64 loads = 256
-        // registers out of the walk)
-        const uint32_t qbase = smem_u32(q_s) + (uint32_t)half * 272u;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float k0 = __uint_as_float(kk[q].x << 16), k1 = __uint_as_float(kk[q].x & 0xFFFF0000u);
-          const float k2 = __uint_as_float(kk[q].y << 16), k3 = __uint_as_float(kk[q].y & 0xFFFF0000u);
-          const float k4 = __uint_as_float(kk[q].z << 16), k5 = __uint_as_float(kk[q].z & 0xFFFF0000u);
-          const float k6 = __uint_as_float(kk[q].w << 16), k7 = __uint_as_float(kk[q].w & 0xFFFF0000u);
-#pragma unroll
-          for (int h = 0; h < kHG; ++h) {
-            const uint32_t qr = qbase + (uint32_t)(min(hp + h, Gq - 1) * kQPad + 8 * q) * 4u;
-            const uint4 qa = lds128(qr), qb = lds128(qr + 16u);
-            sc[h] += __uint_as_float(qa.x) * k0 + __uint_as_float(qa.y) * k1 + __uint_as_float(qa.z) * k2 +
-                     __uint_as_float(qa.w) * k3 + __uint_as_float(qb.x) * k4 + __uint_as_float(qb.y) * k5 +
-                     __uint_as_float(qb.z) * k6 + __uint_as_float(qb.w) * k7;
-          }
-        }
-#pragma unroll
-        for (int h = 0; h < kHG; ++h) {
-          const float s = sc[h] + __shfl_xor_sync(0xffffffffu, sc[h], 1);
-          sc[h] = valid ? s : -INFINITY;
-        }
-        float pj[kHG];
-#pragma unroll
-        for (int h = 0; h < kHG; ++h) {
-          float mb = sc[h];
-#pragma unroll
-          for (int o = 16; o > 1; o >>= 1) mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, o));
-          const float m_new = fmaxf(m[h], mb);  // finite: the block holds at least one position
-          const float corr = __expf(m[h] - m_new);
-          pj[h] = valid ? __expf(sc[h] - m_new) : 0.f;
-          float ps = pj[h];
-#pragma unroll
-          for (int o = 16; o > 1; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
-          l[h] = l[h] * corr + ps;
-          acc[h][0] *= corr; acc[h][1] *= corr; acc[h][2] *= corr; acc[h][3] *= corr;
-          m[h] = m_new;
-        }
-        const int cnt = min(16, len - blk * 16);
-        uint2 vr[16];
-#pragma unroll
-        for (int jj = 0; jj < 16; ++jj)
-          vr[jj] = jj < cnt ? *reinterpret_cast<const uint2*>(vc + (int64_t)(blk * 16 + jj) * 128 + lane * 4)
-                            : make_uint2(0u, 0u);
-#pragma unroll
-        for (int jj = 0; jj < 16; ++jj) {
-          const float v0 = __uint_as_float(vr[jj].x << 16), v1 = __uint_as_float(vr[jj].x & 0xFFFF0000u);
-          const float v2 = __uint_as_float(vr[jj].y << 16), v3 = __uint_as_float(vr[jj].y & 0xFFFF0000u);
-#pragma unroll
-          for (int h = 0; h < kHG; ++h) {
-            const float pw = __shfl_sync(0xffffffffu, pj[h], 2 * jj);
-            acc[h][0] += pw * v0; acc[h][1] += pw * v1; acc[h][2] += pw * v2; acc[h][3] += pw * v3;
-          }
-        }
-      }
-#pragma unroll
-      for (int h = 0; h < kHG; ++h) {
-        float* pp = part_s + (warp * kHG + h) * kPartStride;
-        *reinterpret_cast<float4*>(pp + lane * 4) = make_float4(acc[h][0], acc[h][1], acc[h][2], acc[h][3]);
-        if (lane == 0) {
-          pp[128] = m[h];
-          pp[129] = l[h];
-        }
-      }
-      named_bar_sync(1, kCT);
-      if (warp < kHG && hp + warp < Gq) {
-        // merge the 16 warps' partials of head hp + warp
-        const int head = kvh * Gq + hp + warp;
-        float ms = -INFINITY, ls = 0.f;
-        if (lane < kC) {
-          ms = part_s[(lane * kHG + warp) * kPartStride + 128];
-          ls = part_s[(lane * kHG + warp) * kPartStride + 129];
-        }
-        float mm = ms;
-#pragma unroll
-        for (int o = 16; o; o >>= 1) mm = fmaxf(mm, __shfl_xor_sync(0xffffffffu, mm, o));
-        const float wgt = ls > 0.f ? __expf(ms - mm) : 0.f;
-        float ll = warp_sum(ls * wgt);
-        float a[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int s = 0; s < kC; ++s) {
-          const float ws = __shfl_sync(0xffffffffu, wgt, s);
-          const float4 po = *reinterpret_cast<const float4*>(part_s + (s * kHG + warp) * kPartStride + lane * 4);
-          a[0] += po.x * ws; a[1] += po.y * ws; a[2] += po.z * ws; a[3] += po.w * ws;
-        }
-        if (nsplit > 1) {
-          // partial packets {fp32 | tag}: [head][split][kPartStride]
-          uint64_t* pp = xq + ph->aux_off + ((size_t)head * p.attn_max_split) * kPartStride;
-          if (split > 0) {
-            uint64_t* mine = pp + (size_t)split * kPartStride;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) st_pk(mine + lane * 4 + e, __float_as_uint(a[e]), tag_out);
-            if (lane == 0) st_pk(mine + 128, __float_as_uint(mm), tag_out);
-            if (lane == 1) st_pk(mine + 129, __float_as_uint(ll), tag_out);
-          } else {
-            for (int s = 1; s < nsplit; ++s) {
-              const uint64_t* theirs = pp + (size_t)s * kPartStride;
-              const float m2 = __uint_as_float(poll_pk(theirs + 128, tag_out, ctx));
-              const float l2 = __uint_as_float(poll_pk(theirs + 129, tag_out, ctx));
-              float a2[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) a2[e] = __uint_as_float(poll_pk(theirs + lane * 4 + e, tag_out, ctx));
-              const float mn = fmaxf(mm, m2);
-              const float w1 = __expf(mm - mn), w2 = l2 > 0.f ? __expf(m2 - mn) : 0.f;
-              ll = ll * w1 + l2 * w2;
-#pragma unroll
-              for (int e = 0; e < 4; ++e) a[e] = a[e] * w1 + a2[e] * w2;
-              mm = mn;
+      } else {
+        const uint32_t o0 = float_to_bf16_bits(v0), o1 = float_to_bf16_bits(v1);
+        const uint32_t o0n = __shfl_down_sync(0xffffffffu, o0, 4), o1n = __shfl_down_sync(0xffffffffu, o1, 4);
+        const int n0 = 16 * strip + g;
+        if (c == 0 && (g & 1) == 0) {
+          const uint32_t d0 = o0 | (o0n << 16), d1 = o1 | (o1n << 16);
+          if (out_kind == OUT_PK) {
+            if (n0 < N_out) st_pk(xq + out_off + (n0 >> 1), d0, tag);
+            if (n0 + 8 < N_out) st_pk(xq + out_off + ((n0 + 8) >> 1), d1, tag);
+          } else {  // OUT_DELTA: this rank's slot in every rank's region (own first, then staggered over the peers)
+            const uint32_t off = out_off + (uint32_t)p.rank * (uint32_t)(N_out >> 1);
+            for (int d = 0; d < p.world; ++d) {
+              int r = p.rank + d;
+              if (r >= p.world) r -= p.world;
+              uint64_t* dst = p.xchg[r] + off;
+              if (n0 < N_out) st_pk(dst + (n0 >> 1), d0, tag);
+              if (n0 + 8 < N_out) st_pk(dst + ((n0 + 8) >> 1), d1, tag);
             }
           }
         }
-        if (split == 0) {
-          const float inv = 1.f / ll;
-          const uint32_t o0 = float_to_bf16_bits(a[0] * inv) | (float_to_bf16_bits(a[1] * inv) << 16);
-          const uint32_t o1 = float_to_bf16_bits(a[2] * inv) | (float_to_bf16_bits(a[3] * inv) << 16);
-          uint64_t* dst = xq + ph->out_off + ((head * 128 + lane * 4) >> 1);
-          st_pk(dst, o0, tag_out);
-          st_pk(dst + 1, o1, tag_out);
-        }
       }
-      named_bar_sync(1, kCT);  // part_s is reused by the next pass / the next phase's staging
+    }
+    __syncwarp();
+    if (lane == 0) {
+      red_ctr(p.counter);
+      stamp(p.trace, n_phases, i, 4);
+    }
+    ++gphase;
+  }
+  if (b == 0 && lane == 0) {  // every CTA read both at its start, long before CTA 0 can get here
+    *reinterpret_cast<volatile int32_t*>(p.pos) = pos + 1;
+    *reinterpret_cast<volatile uint32_t*>(p.step) = step + 1u;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ consumers: input staging
+// This code runs once per projection between two streaming loops, on 4 warps per scheduler: its cost is its instruction
+// count (and its footprint in the instruction cache), not memory traffic — the first version's 2300 - 3000-instruction
+// staging functions took 3 us per projection.  Hence: one instantiation per (kind, chunks per thread), straight-line,
+// packed bf16x2 arithmetic wherever it is exact, no division, no generic fall-back.
+__device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_add(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_absmax_nan(uint32_t m, uint32_t v) {  // max(m, |v|) per half, NaN wins
+  uint32_t d;
+  const uint32_t av = v & 0x7fff7fffu;
+  asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(m), "r"(av));
+  return d;
+}
+__device__ __forceinline__ uint32_t cvt_bf2(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
+// one chunk (8 activations as 4 bf16x2 words, k order) -> three int8 limb rows in shared memory + the segment's limb
+// sums.  Executed by whole warps in uniform control flow (the segment sums are shuffles); `valid` = the chunk exists.
+// Balanced limbs without carries: X + 0x808080 = sum (a_i + 128) 256^i, so its bytes xor 0x80 ARE the two's-complement
+// limbs a_i; x * 2^e + 1.5 * 2^23 puts X + 2^22 into the float's mantissa (see gemv_int4_imma.cu).
+template <int G>
+__device__ __forceinline__ void emit_limbs(uint32_t x_u, uint32_t limb_row, uint32_t S_u, int ci, bool valid, const uint4 y,
+                                           float up) {
+  using GE = Geom<G>;
+  int s01 = 0, s2 = 0;  // limb sums of the chunk: (limb 1 << 16) + limb 0 (each |.| <= 1024), limb 2
+  if (valid) {
+    const uint32_t w[4] = {y.x, y.y, y.z, y.w};
+    uint32_t v[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      v[2 * e] = __float_as_uint(fmaf(__uint_as_float(w[e] << 16), up, kMagicF)) + 0x00408080u;
+      v[2 * e + 1] = __float_as_uint(fmaf(__uint_as_float(w[e] & 0xFFFF0000u), up, kMagicF)) + 0x00408080u;
+    }
+    uint32_t lw[3][2];
+#pragma unroll
+    for (int l = 0; l < 3; ++l) {
+      // limb l lives in byte (2 - l) of every v; gathered in the order of the weight bytes after the nibble split:
+      // (k0, k0+4, k0+1, k0+5 | k0+2, k0+6, k0+3, k0+7)
+      const uint32_t sel = l == 0 ? 0x0062u : (l == 1 ? 0x0051u : 0x0040u);
+      const uint32_t p04 = __byte_perm(v[0], v[4], sel), p15 = __byte_perm(v[1], v[5], sel);
+      const uint32_t p26 = __byte_perm(v[2], v[6], sel), p37 = __byte_perm(v[3], v[7], sel);
+      lw[l][0] = __byte_perm(p04, p15, 0x5410) ^ 0x80808080u;
+      lw[l][1] = __byte_perm(p26, p37, 0x5410) ^ 0x80808080u;
+    }
+    const int sl0 = __dp4a((int)lw[0][0], 0x01010101, __dp4a((int)lw[0][1], 0x01010101, 0));
+    const int sl1 = __dp4a((int)lw[1][0], 0x01010101, __dp4a((int)lw[1][1], 0x01010101, 0));
+    s2 = __dp4a((int)lw[2][0], 0x01010101, __dp4a((int)lw[2][1], 0x01010101, 0));
+    s01 = sl1 * 65536 + sl0;
+    const uint32_t a = x_u + (uint32_t)ci * 8u;
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a), "r"(lw[0][0]), "r"(lw[0][1]) : "memory");
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a + limb_row), "r"(lw[1][0]), "r"(lw[1][1]) : "memory");
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a + 2u * limb_row), "r"(lw[2][0]), "r"(lw[2][1]) : "memory");
+  }
+  // a segment = kSegLanes consecutive chunks = consecutive lanes; two sums travel in one register (|sum| <= 16384 each)
+#pragma unroll
+  for (int o = GE::kSegLanes / 2; o; o >>= 1) {
+    s01 += __shfl_xor_sync(0xffffffffu, s01, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  if (valid && (ci & (GE::kSegLanes - 1)) == 0) {
+    const int sl0 = (int)(short)(s01 & 0xffff);
+    const int sl1 = (s01 - sl0) >> 16;
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(S_u + (uint32_t)(ci / GE::kSegLanes) * 32u), "f"((float)sl0),
+                 "f"((float)sl1), "f"((float)s2), "f"(0.f) : "memory");
+  }
+}
+
+// second level of the statistics reduction: every warp reduces the 16 warps' partials itself; returns the power of two
+// `up` that brings the bound into [2^21, 2^22) and (warp 0) publishes the row scale for the epilogue warp.
+__device__ __forceinline__ float finish_stats(const float* part, int lane, int warp, bool with_norm, float inv_k, float eps,
+                                              float* row_scale_slot, float& rnorm) {
+  float t = 0.f;
+  uint32_t am = 0u;
+  if (lane < kC) {
+    t = part[lane * 2];
+    am = __float_as_uint(part[lane * 2 + 1]);
+  }
+#pragma unroll
+  for (int o = 8; o; o >>= 1) {
+    t += __shfl_xor_sync(0xffffffffu, t, o);
+    am = max(am, __shfl_xor_sync(0xffffffffu, am, o));
+  }
+  t = __shfl_sync(0xffffffffu, t, 0);
+  am = __shfl_sync(0xffffffffu, am, 0);
+  float bound = __uint_as_float(am);
+  bool bad = am >= 0x7f800000u;  // an Inf / NaN activation
+  rnorm = 1.f;
+  if (with_norm) {
+    rnorm = rsqrtf(fmaf(t, inv_k, eps));
+    // |bf16(bf16(x r) w)| <= |bf16(x w)| r (1 + 2^-8)^3: a bound within 2x of the true maximum costs at most one of the 23 bits
+    bound = bound * rnorm * 1.0158f;
+    bad = bad || !(bound < 3.0e38f);
+  }
+  // 2^e brings the bound into [2^21, 2^22): |round(x 2^e)| <= 2^22 - 2^14 for every bf16 x below the bound
+  int e = 0;
+  if (bound > 0.f) e = 21 - ((int)((__float_as_uint(bound) >> 23) & 0xFF) - 127);
+  e = max(-106, min(100, e));
+  if (warp == 0 && lane == 0)
+    *row_scale_slot = bad ? __uint_as_float(0x7fc00000u) : __uint_as_float((uint32_t)(127 - e) << 23);
+  return __uint_as_float((uint32_t)(e + 127) << 23);
+}
+
+// IN_H: h += sum over ranks of the published deltas (h stays in shared memory; rank order; world == 1: one packed bf16x2
+// add == bf16(h + d) exactly), then RMSNorm.forward (model.py:498-503): bf16(bf16(h * rsqrt(mean(h^2) + eps)) * w).
+// The norm weights are requested BEFORE the wait (a DRAM miss, once per token).  NCH = chunks of 8 per thread (K <= 4096 NCH).
+template <int G, int NCH>
+__device__ __noinline__ void stage_h(const Params& p, int n_chunks, uint32_t in_off, const __nv_bfloat16* norm_w_p, float inv_k,
+                                     int i, uint32_t tag_in, uint64_t cnt_target, float* row_scale_slot, uint32_t x_u,
+                                     uint32_t S_u, uint4* h_s, float* part) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t limb_row = (uint32_t)n_chunks * 8u + 32u;
+  const uint64_t* in_pk = in_off == kNone ? nullptr : p.xchg[p.rank] + in_off;
+  const uint4* norm_w = reinterpret_cast<const uint4*>(norm_w_p);
+  const int world = p.world;
+  uint4 wn[NCH], hv[NCH];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int ci = c * kCT + tid;
+    wn[c] = ci < n_chunks ? __ldg(norm_w + ci) : make_uint4(0u, 0u, 0u, 0u);
+    hv[c] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  if (tid == 0) {
+    stamp(p.trace, p.n_phases, i, 0);
+    if (i > 0) wait_counter(p.counter, cnt_target);
+  }
+  named_bar_sync(1, kCT);  // B1: phase i - 1 is published; every consumer warp of this CTA has left its main loop
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 1);
+  float ss = 0.f;
+  uint32_t am2 = 0u;  // packed max |bf16(h w)|
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int ci = c * kCT + tid;
+    if (ci < n_chunks) {
+      uint4 h = h_s[ci];
+      if (in_pk != nullptr) {
+        if (world == 1) {
+          const uint4 d = poll_chunk(in_pk + ci * 4, tag_in);
+          h = make_uint4(bf2_add(h.x, d.x), bf2_add(h.y, d.y), bf2_add(h.z, d.z), bf2_add(h.w, d.w));
+        } else {
+          float acc[8], hf[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+          for (int r = 0; r < world; ++r) {
+            float df[8];
+            unpack8(poll_chunk(in_pk + (size_t)r * (n_chunks * 4) + ci * 4, tag_in), df);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += df[e];
+          }
+          unpack8(h, hf);
+          h = make_uint4(cvt_bf2(hf[0] + acc[0], hf[1] + acc[1]), cvt_bf2(hf[2] + acc[2], hf[3] + acc[3]),
+                         cvt_bf2(hf[4] + acc[4], hf[5] + acc[5]), cvt_bf2(hf[6] + acc[6], hf[7] + acc[7]));
+        }
+        h_s[ci] = h;
+      }
+      hv[c] = h;
+      float f[8];
+      unpack8(h, f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
+      am2 = bf2_absmax_nan(am2, bf2_mul(h.x, wn[c].x));
+      am2 = bf2_absmax_nan(am2, bf2_mul(h.y, wn[c].y));
+      am2 = bf2_absmax_nan(am2, bf2_mul(h.z, wn[c].z));
+      am2 = bf2_absmax_nan(am2, bf2_mul(h.w, wn[c].w));
+    }
+  }
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 7);
+  uint32_t am = max(am2 << 16, am2 & 0xffff0000u);  // as fp32 bits (a NaN has the largest bits)
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    am = max(am, __shfl_xor_sync(0xffffffffu, am, o));
+  }
+  if (lane == 0) {
+    part[warp * 2] = ss;
+    part[warp * 2 + 1] = __uint_as_float(am);
+  }
+  named_bar_sync(1, kCT);  // B2
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 6);
+  float rnorm;
+  const float up = finish_stats(part, lane, warp, true, inv_k, p.eps, row_scale_slot, rnorm);
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int ci = c * kCT + tid;
+    if (NCH == 1 || c * kCT < n_chunks) {  // warp-uniform: some chunk of this round exists
+      float f[8];
+      unpack8(hv[c], f);
+      uint4 y;
+      y.x = bf2_mul(cvt_bf2(f[0] * rnorm, f[1] * rnorm), wn[c].x);
+      y.y = bf2_mul(cvt_bf2(f[2] * rnorm, f[3] * rnorm), wn[c].y);
+      y.z = bf2_mul(cvt_bf2(f[4] * rnorm, f[5] * rnorm), wn[c].z);
+      y.w = bf2_mul(cvt_bf2(f[6] * rnorm, f[7] * rnorm), wn[c].w);
+      emit_limbs<G>(x_u, limb_row, S_u, ci, ci < n_chunks, y, up);
+    }
+  }
+  named_bar_sync(1, kCT);  // B3: limbs, segment sums and the row scale are in place
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 2);
+}
+
+// IN_PK: the packets of the previous phase as they are.  The thread keeps its chunks in registers between the two passes.
+template <int G, int NCH>
+__device__ __noinline__ void stage_x(const Params& p, int n_chunks, uint32_t in_off, int i, uint32_t tag_in, uint64_t cnt_target,
+                                     float* row_scale_slot, uint32_t x_u, uint32_t S_u, float* part) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t limb_row = (uint32_t)n_chunks * 8u + 32u;
+  const uint64_t* in_pk = p.xchg[p.rank] + in_off;
+  if (tid == 0) {
+    stamp(p.trace, p.n_phases, i, 0);
+    wait_counter(p.counter, cnt_target);
+  }
+  named_bar_sync(1, kCT);  // B1
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 1);
+  uint4 xv[NCH];
+  uint32_t am2 = 0u;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int ci = c * kCT + tid;
+    xv[c] = make_uint4(0u, 0u, 0u, 0u);
+    if (ci < n_chunks) {
+      xv[c] = poll_chunk(in_pk + ci * 4, tag_in);
+      am2 = bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(am2, xv[c].x), xv[c].y), xv[c].z), xv[c].w);
+    }
+  }
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 7);
+  uint32_t am = max(am2 << 16, am2 & 0xffff0000u);
+#pragma unroll
+  for (int o = 16; o; o >>= 1) am = max(am, __shfl_xor_sync(0xffffffffu, am, o));
+  if (lane == 0) {
+    part[warp * 2] = 0.f;
+    part[warp * 2 + 1] = __uint_as_float(am);
+  }
+  named_bar_sync(1, kCT);  // B2
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 6);
+  float rnorm;
+  const float up = finish_stats(part, lane, warp, false, 0.f, 0.f, row_scale_slot, rnorm);
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int ci = c * kCT + tid;
+    if (NCH == 1 || c * kCT < n_chunks) emit_limbs<G>(x_u, limb_row, S_u, ci, ci < n_chunks, xv[c], up);
+  }
+  named_bar_sync(1, kCT);  // B3
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 2);
+}
+
+// ------------------------------------------------------------------------------------------------ consumers: main loop
+// one stage of one strip for one warp (its 128 k x 16 rows): yacc += sum over the segments of  s * acc + (z - 8 s) * S
+template <int NS>
+__device__ __forceinline__ void stage_math(const uint4 wa, const uint4 wb, const uint32_t (&p0)[NS], const uint32_t (&p1)[NS],
+                                           const uint2 (&xb)[4], const float2 (&S)[NS], float (&yacc)[4]) {
+  constexpr uint32_t kM = 0x0f0f0f0fu;
+  // half h: words (row g, row g + 8); low nibbles = k (k0, k0+4, k0+1, k0+5), high nibbles = (k0+2, k0+6, k0+3, k0+7)
+  const uint32_t wl[4][2] = {{wa.x, wa.y}, {wa.z, wa.w}, {wb.x, wb.y}, {wb.z, wb.w}};
+  if constexpr (NS == 1) {
+    int a0[4] = {(int)kMagicI, (int)kMagicI, (int)kMagicI, (int)kMagicI}, a1[4] = {0, 0, 0, 0};
+    imma_16832(a0, wl[0][0] & kM, wl[0][1] & kM, (wl[0][0] >> 4) & kM, (wl[0][1] >> 4) & kM, xb[0].x, xb[0].y);
+    imma_16832(a1, wl[1][0] & kM, wl[1][1] & kM, (wl[1][0] >> 4) & kM, (wl[1][1] >> 4) & kM, xb[1].x, xb[1].y);
+    imma_16832(a0, wl[2][0] & kM, wl[2][1] & kM, (wl[2][0] >> 4) & kM, (wl[2][1] >> 4) & kM, xb[2].x, xb[2].y);
+    imma_16832(a1, wl[3][0] & kM, wl[3][1] & kM, (wl[3][0] >> 4) & kM, (wl[3][1] >> 4) & kM, xb[3].x, xb[3].y);
+    const float sc0 = __uint_as_float(p0[0] << 16), sc1 = __uint_as_float(p1[0] << 16);
+    const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0[0] & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1[0] & 0xFFFF0000u));
+    const float f0 = __int_as_float(a0[0] + a1[0]) - kMagicF, f1 = __int_as_float(a0[1] + a1[1]) - kMagicF;
+    const float f2 = __int_as_float(a0[2] + a1[2]) - kMagicF, f3 = __int_as_float(a0[3] + a1[3]) - kMagicF;
+    yacc[0] = fmaf(sc0, f0, fmaf(zz0, S[0].x, yacc[0]));
+    yacc[1] = fmaf(sc0, f1, fmaf(zz0, S[0].y, yacc[1]));
+    yacc[2] = fmaf(sc1, f2, fmaf(zz1, S[0].x, yacc[2]));
+    yacc[3] = fmaf(sc1, f3, fmaf(zz1, S[0].y, yacc[3]));
+  } else {
+    constexpr int kHS = 4 / NS;  // 32-k halves per segment
+#pragma unroll
+    for (int sg = 0; sg < NS; ++sg) {
+      int a[4] = {(int)kMagicI, (int)kMagicI, (int)kMagicI, (int)kMagicI};
+#pragma unroll
+      for (int hh = 0; hh < kHS; ++hh) {
+        const int h = sg * kHS + hh;
+        imma_16832(a, wl[h][0] & kM, wl[h][1] & kM, (wl[h][0] >> 4) & kM, (wl[h][1] >> 4) & kM, xb[h].x, xb[h].y);
+      }
+      const float sc0 = __uint_as_float(p0[sg] << 16), sc1 = __uint_as_float(p1[sg] << 16);
+      const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0[sg] & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1[sg] & 0xFFFF0000u));
+      yacc[0] = fmaf(sc0, __int_as_float(a[0]) - kMagicF, fmaf(zz0, S[sg].x, yacc[0]));
+      yacc[1] = fmaf(sc0, __int_as_float(a[1]) - kMagicF, fmaf(zz0, S[sg].y, yacc[1]));
+      yacc[2] = fmaf(sc1, __int_as_float(a[2]) - kMagicF, fmaf(zz1, S[sg].x, yacc[2]));
+      yacc[3] = fmaf(sc1, __int_as_float(a[3]) - kMagicF, fmaf(zz1, S[sg].y, yacc[3]));
     }
   }
 }
 
-// ------------------------------------------------------------------------------------------------ the kernel
-template <int G>
-__global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p) {
+// Warp w owns k-tiles 2 w, 2 w + 1 (128 k) of every stage.  XREG (KT <= 64: K <= 4096, at most two stages per strip): the
+// warp's slice of the activation limbs and their segment sums are the same for every strip, so they are read from shared
+// memory ONCE per phase and stay in registers.  A stage's slot is released as soon as its words are in registers (the
+// loads are unconditional — a warp past the end of a short stage reads stale bytes it never uses).
+// Returns the ring state (slot | parity << 8).
+template <int G, bool XREG>
+__device__ __noinline__ uint32_t gemv_main(uint32_t ring_u, uint32_t bar0, int stages, int KT, int n_my, uint32_t x_u,
+                                           uint32_t limb_row, uint32_t S_u, uint32_t red_u, uint32_t state, uint32_t li,
+                                           int dbg) {
   using GE = Geom<G>;
   constexpr int kStageBytes = GE::kStageBytes;
-  extern __shared__ __align__(128) uint8_t smem[];
-  uint8_t* ring = smem;
-  uint8_t* x_s = smem + p.off_x;                                  // limbs [3][Kp + 32] int8 / attention scratch
-  float* S_s = reinterpret_cast<float*>(smem + p.off_S);          // [Kp / kSegK][8]: limb sums per segment
-  float* red = reinterpret_cast<float*>(smem + p.off_red);        // [2][16 warps][32][4]
-  uint4* h_s = reinterpret_cast<uint4*>(smem + p.off_h);          // residual stream, bf16 [dim]
-  float* part = reinterpret_cast<float*>(smem + p.off_misc);      // [16 warps][2]: {sum sq, max |.| bits}
-  float* row_scale = part + 2 * kC;                               // [2] (GEMV-phase parity)
-  volatile uint32_t* abort_s = reinterpret_cast<volatile uint32_t*>(row_scale + 2);
-  uint64_t* full = reinterpret_cast<uint64_t*>(row_scale + 4);
-  uint64_t* empty = full + p.stages;
-  uint64_t* red_full = empty + p.stages;
-  uint64_t* red_free = red_full + kRedBufs;
+  constexpr int NS = GE::kNSeg;
+  constexpr uint32_t kSOff = (kStageTiles * 64 / GE::kSegK) * 32u;  // S_s bytes per stage
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, c = lane & 3;
+  const uint32_t full0 = bar0, empty0 = bar0 + 8u * stages, red_full0 = empty0 + 8u * stages, red_free0 = red_full0 + 8u * kRedBufs;
+  int slot = (int)(state & 0xffu);
+  uint32_t par = state >> 8;
+  const uint32_t w_off = (uint32_t)warp * 1024u + (uint32_t)lane * 16u;
+  const uint32_t sz_off = (uint32_t)kStageW + (uint32_t)(G >= 128 ? warp * 128 / G : warp * NS) * 64u + (uint32_t)g * 4u;
+  const uint32_t S_u0 = S_u + (uint32_t)(warp * NS) * 32u + (uint32_t)c * 8u;
+  const uint32_t x_u0 = x_u + (uint32_t)min(g, 2) * limb_row + (uint32_t)warp * 128u + (uint32_t)c * 8u;
+  const bool x_on = g < 3;  // MMA column g = limb g of the activation row
+  const bool skip = (dbg & 1) != 0;
+  const uint32_t red_w = red_u + (uint32_t)(warp * 32 + lane) * 16u;
+
+  uint2 xr[2][4];
+  float2 Sr[2][NS];
+  if constexpr (XREG) {
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      const bool on = 2 * warp < KT - kStageTiles * s;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) xr[s][h] = (on && x_on) ? lds64u(x_u0 + 2048u * s + 32u * h) : make_uint2(0u, 0u);
+#pragma unroll
+      for (int sg = 0; sg < NS; ++sg) Sr[s][sg] = on ? lds64f(S_u0 + kSOff * s + 32u * sg) : make_float2(0.f, 0.f);
+    }
+  }
+  const int n_st = XREG ? 1 : (KT + kStageTiles - 1) / kStageTiles;  // XREG: the (<= 2) stages are unrolled below
+  for (int n = 0; n < n_my; ++n) {
+    float yacc[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t xo = 0, So = 0;
+    int kt0 = 0;
+    for (int st = 0; st < n_st; ++st) {
+#pragma unroll
+      for (int s = 0; s < (XREG ? 2 : 1); ++s) {
+        if (!XREG || kStageTiles * s < KT) {
+          const uint32_t stage_u = ring_u + (uint32_t)slot * kStageBytes;
+          bar_wait(full0 + 8u * slot, par, 32u);
+          const uint4 wa = lds128(stage_u + w_off), wb = lds128(stage_u + w_off + 512u);
+          uint32_t p0[NS], p1[NS];
+#pragma unroll
+          for (int sg = 0; sg < NS; ++sg) {
+            p0[sg] = lds32(stage_u + sz_off + 64u * sg);
+            p1[sg] = lds32(stage_u + sz_off + 64u * sg + 32u);
+          }
+          uint2 xb[4];
+          float2 S[NS];
+          if constexpr (XREG) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) xb[h] = xr[s][h];
+#pragma unroll
+            for (int sg = 0; sg < NS; ++sg) S[sg] = Sr[s][sg];
+          } else {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) xb[h] = x_on ? lds64u(x_u0 + xo + 32u * h) : make_uint2(0u, 0u);
+#pragma unroll
+            for (int sg = 0; sg < NS; ++sg) S[sg] = lds64f(S_u0 + So + 32u * sg);
+          }
+          __syncwarp();
+          if (lane == 0) bar_arrive(empty0 + 8u * slot);
+          if (++slot == stages) {
+            slot = 0;
+            par ^= 1u;
+          }
+          const bool on = 2 * warp < KT - (XREG ? kStageTiles * s : kt0);
+          if (on && !skip) stage_math<NS>(wa, wb, p0, p1, xb, S, yacc);
+        }
+      }
+      xo += kStageTiles * 64u;
+      So += kSOff;
+      kt0 += kStageTiles;
+    }
+    // hand the strip's partial sums to the epilogue warp
+    const uint32_t rbuf = li & 1u, use = li >> 1;
+    if (use > 0) bar_wait(red_free0 + 8u * rbuf, (use - 1) & 1u, 64u);
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(red_w + rbuf * (kC * 128 * 4)), "f"(yacc[0]), "f"(yacc[1]),
+                 "f"(yacc[2]), "f"(yacc[3]) : "memory");
+    __syncwarp();
+    if (lane == 0) bar_arrive(red_full0 + 8u * rbuf);
+    ++li;
+  }
+  return (uint32_t)slot | (par << 8);
+}
+
+// ------------------------------------------------------------------------------------------------ consumers: attention
+// Attention.forward for the new token (model.py:405-440).  One (kv head, range of 32-position tiles) per CTA; the GQ q
+// heads of the group share every K / V row.  The K / V rows arrive through the weight ring (the producer requested them
+// long before q existed), 32 positions per stage: warp w takes positions 2 w, 2 w + 1 of the tile — 16 lanes x 8 dims per
+// position for q.K, 32 lanes x 4 dims for P.V — and keeps its own online-softmax state per head; the 16 warps are merged
+// through shared memory, the splits of a long sequence through {fp32 | tag} packets gathered by split 0.
+// The new token's k (roped) and v come out of the qkv packets: the CTA that owns the last tile appends them to the cache
+// (for the next launches) and patches them into its copy of the tile.  q dims are stored permuted (qidx) so that the 16
+// lanes of a position read 256 contiguous bytes per load.
+__device__ __forceinline__ int qidx(int d) { return (d & 4) ? 64 + ((d >> 3) << 2) + (d & 3) : ((d >> 3) << 2) + (d & 3); }
+
+template <int GQ>
+__device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16* k_cache, __nv_bfloat16* v_cache, uint32_t in_off,
+                                                 uint32_t out_off, uint32_t aux_off, int i, int pos, uint32_t tag_in,
+                                                 uint64_t cnt_target, uint32_t ring_u, uint32_t stage_bytes, uint32_t bar0,
+                                                 uint8_t* x_s, uint32_t state) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x, n_phases = p.n_phases;
+  const int H = p.H, Hkv = p.Hkv, S = p.S;
+  const Bars bars = make_bars(bar0, p.stages);
+  const AttnPart a = attn_partition(pos, S, Hkv, p.attn_spc, p.attn_max_split, b);
+  uint64_t* xq = p.xchg[p.rank];
+  const uint32_t tag_out = tag_in + 1u;
+  float* q_s = reinterpret_cast<float*>(x_s);                      // [GQ][128] fp32 (scaled, dims permuted)
+  uint32_t* kv_new = reinterpret_cast<uint32_t*>(q_s + GQ * 128);  // [2][64] bf16x2: roped k, v of the new token
+  float* part_s = reinterpret_cast<float*>(kv_new + 128);          // [16 warps][GQ][kPartStride]
+  constexpr int kItems = (GQ + 2) * 64;                            // (q heads, k, v) x 64 pairs
+  constexpr int kIt = (kItems + kCT - 1) / kCT;
+  // cos / sin of the position: independent of everybody, requested before the wait
+  uint32_t cs[kIt];
+#pragma unroll
+  for (int it = 0; it < kIt; ++it) {
+    const int idx = it * kCT + tid;
+    cs[it] = 0u;
+    if (a.active && idx < (GQ + 1) * 64)
+      cs[it] = __ldg(reinterpret_cast<const uint32_t*>(p.freqs) + (int64_t)min(pos, S - 1) * 64 + (idx & 63));
+  }
+  if (tid == 0) {
+    stamp(p.trace, n_phases, i, 0);
+    wait_counter(p.counter, cnt_target);
+  }
+  named_bar_sync(1, kCT);  // B1: qkv is published; every consumer warp has left the wqkv main loop
+  if (tid == 0) stamp(p.trace, n_phases, i, 1);
+  if (!a.active) {
+    if (tid == 0) {
+      red_ctr(p.counter);
+      stamp(p.trace, n_phases, i, 4);
+    }
+    return state;
+  }
+  const bool owner = a.split == a.nsplit - 1 && pos < S;
+  __nv_bfloat16* kc = k_cache + (int64_t)a.kvh * S * 128;
+  __nv_bfloat16* vc = v_cache + (int64_t)a.kvh * S * 128;
+  {
+    const uint64_t* qkv = xq + in_off;
+#pragma unroll
+    for (int it = 0; it < kIt; ++it) {
+      const int idx = it * kCT + tid;
+      if (idx < kItems) {
+        const int which = idx >> 6, pr = idx & 63;
+        const int elem = which < GQ ? (a.kvh * GQ + which) * 128 : (which == GQ ? (H + a.kvh) * 128 : (H + Hkv + a.kvh) * 128);
+        const uint32_t raw = poll_pk(qkv + (elem >> 1) + pr, tag_in);
+        uint32_t o = raw;
+        float r0 = 0.f, r1 = 0.f;
+        if (which <= GQ) {  // RoPE, model.py:547-559: fp32 math on bf16 cos / sin, rounded to bf16
+          const float x0 = __uint_as_float(raw << 16), x1 = __uint_as_float(raw & 0xFFFF0000u);
+          const float cc = __uint_as_float(cs[it] << 16), sn = __uint_as_float(cs[it] & 0xFFFF0000u);
+          r0 = bf16r(x0 * cc - x1 * sn);
+          r1 = bf16r(x1 * cc + x0 * sn);
+          o = float_to_bf16_bits(r0) | (float_to_bf16_bits(r1) << 16);
+        }
+        if (which < GQ) {
+          *reinterpret_cast<float2*>(q_s + which * 128 + qidx(2 * pr)) = make_float2(r0 * p.attn_scale, r1 * p.attn_scale);
+        } else {
+          kv_new[(which - GQ) * 64 + pr] = o;
+          if (owner) *reinterpret_cast<uint32_t*>((which == GQ ? kc : vc) + (int64_t)pos * 128 + 2 * pr) = o;  // KVCache.update
+        }
+      }
+    }
+  }
+  named_bar_sync(1, kCT);  // q and the new k / v are in shared memory
+  if (tid == 0) stamp(p.trace, n_phases, i, 2);
+
+  int slot = (int)(state & 0xffu);
+  uint32_t par = state >> 8;
+  float m[GQ], l[GQ], acc[GQ][4];
+#pragma unroll
+  for (int h = 0; h < GQ; ++h) {
+    m[h] = -INFINITY;
+    l[h] = 0.f;
+    acc[h][0] = acc[h][1] = acc[h][2] = acc[h][3] = 0.f;
+  }
+  const int half = lane >> 4, ds = lane & 15;
+  const uint32_t q_u = smem_u32(q_s) + (uint32_t)ds * 16u;
+  for (int t = a.t0; t < a.t1; ++t) {
+    const uint32_t stage_u = ring_u + (uint32_t)slot * stage_bytes;
+    bar_wait(bars.full + 8u * slot, par, 32u);
+    if (owner && t == a.n_t - 1) {  // CTA-uniform: the tile that holds the new position
+      const int row = pos - t * kAttnPos;
+      if (tid < 128) sts32(stage_u + (uint32_t)(tid >> 6) * 8192u + (uint32_t)row * 256u + (uint32_t)(tid & 63) * 4u, kv_new[tid]);
+      fence_proxy_async();  // generic writes into a buffer the bulk-copy engine will overwrite later
+      named_bar_sync(1, kCT);
+    }
+    const int j0 = t * kAttnPos + 2 * warp;
+    const bool valid = j0 + half < a.len;
+    float kf[8];
+    unpack8(lds128(stage_u + (uint32_t)(2 * warp + half) * 256u + (uint32_t)ds * 16u), kf);
+    float sc[GQ];
+#pragma unroll
+    for (int h = 0; h < GQ; ++h) {
+      const uint4 qa = lds128(q_u + (uint32_t)h * 512u), qb = lds128(q_u + (uint32_t)h * 512u + 256u);
+      float s = __uint_as_float(qa.x) * kf[0] + __uint_as_float(qa.y) * kf[1] + __uint_as_float(qa.z) * kf[2] +
+                __uint_as_float(qa.w) * kf[3] + __uint_as_float(qb.x) * kf[4] + __uint_as_float(qb.y) * kf[5] +
+                __uint_as_float(qb.z) * kf[6] + __uint_as_float(qb.w) * kf[7];
+#pragma unroll
+      for (int o = 8; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      sc[h] = valid ? s : -INFINITY;
+    }
+    uint2 v0 = lds64u(stage_u + 8192u + (uint32_t)(2 * warp) * 256u + (uint32_t)lane * 8u);
+    uint2 v1 = lds64u(stage_u + 8192u + (uint32_t)(2 * warp + 1) * 256u + (uint32_t)lane * 8u);
+    if (j0 >= a.len) v0 = make_uint2(0u, 0u);      // rows past the sequence hold stale bytes: keep them out of 0 * x
+    if (j0 + 1 >= a.len) v1 = make_uint2(0u, 0u);
+    __syncwarp();
+    if (lane == 0) bar_arrive(bars.empty + 8u * slot);
+    if (++slot == p.stages) {
+      slot = 0;
+      par ^= 1u;
+    }
+    const float v00 = __uint_as_float(v0.x << 16), v01 = __uint_as_float(v0.x & 0xFFFF0000u);
+    const float v02 = __uint_as_float(v0.y << 16), v03 = __uint_as_float(v0.y & 0xFFFF0000u);
+    const float v10 = __uint_as_float(v1.x << 16), v11 = __uint_as_float(v1.x & 0xFFFF0000u);
+    const float v12 = __uint_as_float(v1.y << 16), v13 = __uint_as_float(v1.y & 0xFFFF0000u);
+#pragma unroll
+    for (int h = 0; h < GQ; ++h) {
+      const float mb = fmaxf(sc[h], __shfl_xor_sync(0xffffffffu, sc[h], 16));
+      const float m_new = fmaxf(m[h], mb);
+      const float m_use = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = __expf(m[h] - m_use);
+      const float pm = valid ? __expf(sc[h] - m_use) : 0.f;
+      const float p0 = __shfl_sync(0xffffffffu, pm, 0), p1 = __shfl_sync(0xffffffffu, pm, 16);
+      l[h] = l[h] * corr + p0 + p1;
+      acc[h][0] = acc[h][0] * corr + p0 * v00 + p1 * v10;
+      acc[h][1] = acc[h][1] * corr + p0 * v01 + p1 * v11;
+      acc[h][2] = acc[h][2] * corr + p0 * v02 + p1 * v12;
+      acc[h][3] = acc[h][3] * corr + p0 * v03 + p1 * v13;
+      m[h] = m_new;
+    }
+  }
+  if (tid == 0) stamp(p.trace, n_phases, i, 3);
+#pragma unroll
+  for (int h = 0; h < GQ; ++h) {
+    float* pp = part_s + (warp * GQ + h) * kPartStride;
+    *reinterpret_cast<float4*>(pp + lane * 4) = make_float4(acc[h][0], acc[h][1], acc[h][2], acc[h][3]);
+    if (lane == 0) {
+      pp[128] = m[h];
+      pp[129] = l[h];
+    }
+  }
+  named_bar_sync(1, kCT);
+  if (warp < GQ) {
+    // merge the 16 warps' partials of head kvh GQ + warp
+    const int head = a.kvh * GQ + warp;
+    float ms = -INFINITY, ls = 0.f;
+    if (lane < kC) {
+      ms = part_s[(lane * GQ + warp) * kPartStride + 128];
+      ls = part_s[(lane * GQ + warp) * kPartStride + 129];
+    }
+    float mm = ms;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mm = fmaxf(mm, __shfl_xor_sync(0xffffffffu, mm, o));
+    const float wgt = ls > 0.f ? __expf(ms - mm) : 0.f;
+    float ll = warp_sum(ls * wgt);
+    float o4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < kC; ++s) {
+      const float ws = __shfl_sync(0xffffffffu, wgt, s);
+      const float4 po = *reinterpret_cast<const float4*>(part_s + (s * GQ + warp) * kPartStride + lane * 4);
+      o4[0] += po.x * ws; o4[1] += po.y * ws; o4[2] += po.z * ws; o4[3] += po.w * ws;
+    }
+    if (a.nsplit > 1) {
+      // split partials as packets {fp32 | tag}: [head][split][kPartStride]
+      uint64_t* pp = xq + aux_off + ((size_t)head * p.attn_max_split) * kPartStride;
+      if (a.split > 0) {
+        uint64_t* mine = pp + (size_t)a.split * kPartStride;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) st_pk(mine + lane * 4 + e, __float_as_uint(o4[e]), tag_out);
+        if (lane == 0) st_pk(mine + 128, __float_as_uint(mm), tag_out);
+        if (lane == 1) st_pk(mine + 129, __float_as_uint(ll), tag_out);
+      } else {
+        for (int s = 1; s < a.nsplit; ++s) {
+          const uint64_t* theirs = pp + (size_t)s * kPartStride;
+          const float m2 = __uint_as_float(poll_pk(theirs + 128, tag_out));
+          const float l2 = __uint_as_float(poll_pk(theirs + 129, tag_out));
+          float a2[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) a2[e] = __uint_as_float(poll_pk(theirs + lane * 4 + e, tag_out));
+          const float mn = fmaxf(mm, m2);
+          const float w1 = __expf(mm - mn), w2 = l2 > 0.f ? __expf(m2 - mn) : 0.f;
+          ll = ll * w1 + l2 * w2;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) o4[e] = o4[e] * w1 + a2[e] * w2;
+          mm = mn;
+        }
+      }
+    }
+    if (a.split == 0) {
+      const float inv = 1.f / ll;
+      const uint32_t o0 = float_to_bf16_bits(o4[0] * inv) | (float_to_bf16_bits(o4[1] * inv) << 16);
+      const uint32_t o1 = float_to_bf16_bits(o4[2] * inv) | (float_to_bf16_bits(o4[3] * inv) << 16);
+      uint64_t* dst = xq + out_off + ((head * 128 + lane * 4) >> 1);
+      st_pk(dst, o0, tag_out);
+      st_pk(dst + 1, o1, tag_out);
+    }
+  }
+  if (tid == 0) {
+    red_ctr(p.counter);
+    stamp(p.trace, n_phases, i, 4);
+  }
+  return (uint32_t)slot | (par << 8);
+}
+
+// ------------------------------------------------------------------------------------------------ the kernel
+template <int G>
+__global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Params p) {
+  using GE = Geom<G>;
+  constexpr int kStageBytes = GE::kStageBytes;
+  extern __shared__ __align__(128) uint8_t smem_mega[];
+  uint8_t* ring = smem_mega + kHdrBytes;
+  uint8_t* x_s = smem_mega + p.off_x;                              // limbs [3][Kp + 32] int8 / attention scratch
+  float* S_s = reinterpret_cast<float*>(smem_mega + p.off_S);      // [Kp / kSegK][8]: limb sums per segment
+  uint4* h_s = reinterpret_cast<uint4*>(smem_mega + p.off_h);      // residual stream, bf16 [dim]
+  float* part = reinterpret_cast<float*>(smem_mega + p.off_misc);  // [16 warps][2]: {sum sq, max |.| bits}
+  float* row_scale = part + 2 * kC;                                // [2] (GEMV-phase parity)
+  uint64_t* bar_p = reinterpret_cast<uint64_t*>(row_scale + 4);    // full[stages], empty[stages], red_full[2], red_free[2]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x, n_cta = p.n_cta;
-  const int stages = p.stages;
-  const int n_phases = p.n_phases;
-  const Phase* __restrict__ phases = p.phases;
-
+  const int stages = p.stages, n_phases = p.n_phases;
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(p.layers);
+    uint4* dst = reinterpret_cast<uint4*>(smem_mega + p.off_lay);
+    for (int k = tid; k < p.n_layer * (int)(sizeof(LayerPtrs) / 16); k += kThreads) dst[k] = __ldg(src + k);
+  }
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], kC);
+      mbar_init(&bar_p[s], 1);
+      mbar_init(&bar_p[stages + s], kC);
     }
     for (int s = 0; s < kRedBufs; ++s) {
-      mbar_init(&red_full[s], kC);
-      mbar_init(&red_free[s], 1);
+      mbar_init(&bar_p[2 * stages + s], kC);
+      mbar_init(&bar_p[2 * stages + kRedBufs + s], 1);
     }
-    *abort_s = 0u;
+    SCtx* c = sctx();
+    c->abort = 0u;
+    c->status = p.status;
+    c->timeout_ns = p.timeout_ns;
     fence_barrier_init();
   }
   __syncthreads();
-  Ctx ctx{abort_s, p.status, p.timeout_ns};
 
   const uint32_t step = *reinterpret_cast<volatile uint32_t*>(p.step);
   const int pos = *reinterpret_cast<volatile int32_t*>(p.pos);
-  const uint32_t tag0 = step * (uint32_t)n_phases;                           // phase i publishes with tag tag0 + i + 1
-  const uint64_t cnt0 = (uint64_t)step * (uint64_t)n_phases * (uint64_t)n_cta;  // counter before this launch
-  uint64_t* xq = p.xchg[p.rank];
+  const uint32_t ring_u = smem_u32(ring), bar0 = smem_u32(bar_p), red_u = smem_u32(smem_mega + p.off_red);
 
   if (warp == kC) {
-    // ===================== producer: the CTA's share of every weight, in phase order =====================
-    if (lane == 0) {
-      int slot = 0;
-      uint32_t par = 1;
-      for (int i = 0; i < n_phases; ++i) {
-        const Phase* ph = phases + i;
-        if (ph->type != PH_GEMV) continue;
-        const int KT = ph->KT;
-        int s0, s1;
-        strip_range(b, n_cta, ph->n_strips, ph->rot, s0, s1);
-        const int n_groups = KT * 64 / G;
-        const uint8_t* packed = ph->packed;
-        const uint32_t* sz = ph->sz;
-        for (int strip = s0; strip < s1; ++strip) {
-          const uint8_t* wrow = packed + (int64_t)strip * KT * 512;
-          const uint32_t* srow = sz + (int64_t)strip * n_groups * 16;
-          for (int kt0 = 0; kt0 < KT; kt0 += kStageTiles) {
-            const int cnt = min(kStageTiles, KT - kt0);
-            uint8_t* dst = ring + (size_t)slot * kStageBytes;
-            mbar_wait_b(&empty[slot], par, ctx, 8u);
-            const uint32_t sz_bytes = (uint32_t)(cnt * 64 / G) * 64u;
-            mbar_arrive_expect_tx(&full[slot], (uint32_t)(cnt * 512) + sz_bytes);
-            bulk_g2s(dst + kStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, &full[slot]);
-            bulk_g2s(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), &full[slot]);
-            if (++slot == stages) {
-              slot = 0;
-              par ^= 1u;
-            }
-          }
-        }
-        stamp(p.trace, n_phases, i, 5);
-      }
-    }
+    if (lane == 0) producer_loop<G>(p, pos, ring_u, bar0);
     return;
   }
-
   if (warp == kC + 1) {
-    // ===================== epilogue warp =====================
-    const int g = lane >> 2, c = lane & 3;
-    uint32_t li = 0;   // strips handed over so far (all phases)
-    int gphase = 0;    // GEMV phases so far
-    for (int i = 0; i < n_phases; ++i) {
-      const Phase* ph = phases + i;
-      if (ph->type != PH_GEMV) continue;
-      int s0, s1;
-      strip_range(b, n_cta, ph->n_strips, ph->rot, s0, s1);
-      const int out_kind = ph->out_kind;
-      const int N_out = ph->N_out;
-      const uint32_t tag = tag0 + (uint32_t)i + 1u;
-      const uint32_t out_off = ph->out_off;
-      __nv_bfloat16* out_plain = ph->out_plain;
-      for (int strip = s0; strip < s1; ++strip, ++li) {
-        const int rbuf = (int)(li & 1u);
-        const uint32_t use = li >> 1;
-        const float* rb = red + (size_t)rbuf * (kC * 128);
-        mbar_wait_b(&red_full[rbuf], use & 1u, ctx, 16u);
-        uint64_t vlo = 0ull, vhi = 0ull;
-#pragma unroll
-        for (int w = 0; w < kC; ++w) {
-          const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(rb + (w * 32 + lane) * 4);
-          asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vlo) : "l"(t.x));
-          asm("add.rn.f32x2 %0, %0, %1;" : "+l"(vhi) : "l"(t.y));
-        }
-        const float4 v = make_float4(__uint_as_float((uint32_t)vlo), __uint_as_float((uint32_t)(vlo >> 32)),
-                                     __uint_as_float((uint32_t)vhi), __uint_as_float((uint32_t)(vhi >> 32)));
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&red_free[rbuf]);
-        // limb recombination (M = 1): lane (g, c = 0) holds limbs 0, 1 of rows g (x, y) and g + 8 (z, w); limb 2 sits in
-        // lane (g, c = 1).x / .z
-        const float t2x = __shfl_down_sync(0xffffffffu, v.x, 1), t2z = __shfl_down_sync(0xffffffffu, v.z, 1);
-        const float rsc = row_scale[gphase & 1];
-        const float v0 = fmaf(65536.f, v.x, fmaf(256.f, v.y, t2x)) * rsc;   // row g      (valid on lanes c == 0)
-        const float v1 = fmaf(65536.f, v.z, fmaf(256.f, v.w, t2z)) * rsc;   // row g + 8
-        if (out_kind == OUT_SILU) {
-          // rows g = gate (w1), rows g + 8 = up (w3) of output n = 8 strip + g   (model.py:486)
-          const float gate = bf16r(v0), up = bf16r(v1);
-          const float sg = bf16r(gate / (1.f + __expf(-gate)));
-          const uint32_t o = float_to_bf16_bits(sg * up);
-          const uint32_t on = __shfl_down_sync(0xffffffffu, o, 4);  // row g + 1
-          const int n = 8 * strip + g;
-          if (c == 0 && (g & 1) == 0 && n < N_out) st_pk(xq + out_off + (n >> 1), o | (on << 16), tag);
-        } else if (out_kind == OUT_PLAIN) {
-          const int n0 = 16 * strip + g;
-          if (c == 0) {
-            if (n0 < N_out) out_plain[n0] = __float2bfloat16_rn(v0);
-            if (n0 + 8 < N_out) out_plain[n0 + 8] = __float2bfloat16_rn(v1);
-          }
-        } else {
-          const uint32_t o0 = float_to_bf16_bits(v0), o1 = float_to_bf16_bits(v1);
-          const uint32_t o0n = __shfl_down_sync(0xffffffffu, o0, 4), o1n = __shfl_down_sync(0xffffffffu, o1, 4);
-          const int n0 = 16 * strip + g;
-          if (c == 0 && (g & 1) == 0) {
-            const uint32_t d0 = o0 | (o0n << 16), d1 = o1 | (o1n << 16);
-            if (out_kind == OUT_PK) {
-              if (n0 < N_out) st_pk(xq + out_off + (n0 >> 1), d0, tag);
-              if (n0 + 8 < N_out) st_pk(xq + out_off + ((n0 + 8) >> 1), d1, tag);
-            } else {  // OUT_DELTA: this rank's slot in every rank's region (own first, then staggered over the peers)
-              const uint32_t off = out_off + (uint32_t)p.rank * (uint32_t)(N_out >> 1);
-              for (int d = 0; d < p.world; ++d) {
-                int r = p.rank + d;
-                if (r >= p.world) r -= p.world;
-                uint64_t* dst = p.xchg[r] + off;
-                if (n0 < N_out) st_pk(dst + (n0 >> 1), d0, tag);
-                if (n0 + 8 < N_out) st_pk(dst + ((n0 + 8) >> 1), d1, tag);
-              }
-            }
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) {
-        red_ctr(p.counter);
-        stamp(p.trace, n_phases, i, 4);
-      }
-      ++gphase;
-    }
-    if (b == 0 && lane == 0) {  // every CTA read both at its start, long before CTA 0 can get here
-      *reinterpret_cast<volatile int32_t*>(p.pos) = pos + 1;
-      *reinterpret_cast<volatile uint32_t*>(p.step) = step + 1u;
-    }
+    epilogue_loop(p, pos, step, red_u, bar0, row_scale);
     return;
   }
 
   // ===================== consumers =====================
-  const int g = lane >> 2, c = lane & 3;
   {
     // residual stream := embedding row of the fed token (model.py:358)
     const int64_t tok = *reinterpret_cast<const volatile int64_t*>(p.tok);
     const uint4* erow = reinterpret_cast<const uint4*>(p.emb + tok * (int64_t)p.dim);
     for (int ci = tid; ci < p.dim / 8; ci += kCT) h_s[ci] = __ldg(erow + ci);
   }
-  const uint32_t ring_u = smem_u32(ring);
-  int slot = 0;
-  uint32_t par = 0;
-  uint32_t stage_u = ring_u;
+  const uint32_t tag0 = step * (uint32_t)n_phases;                              // phase i publishes with tag tag0 + i + 1
+  const uint64_t cnt0 = (uint64_t)step * (uint64_t)n_phases * (uint64_t)n_cta;  // counter before this launch
+  const int GQ = p.H / p.Hkv;
+  uint32_t state = 0;  // ring slot | parity << 8
   uint32_t li = 0;
-  int gphase = 0;
-
+  int gphase = 0, rot = 0;
   for (int i = 0; i < n_phases; ++i) {
-    const Phase* ph = phases + i;
+    const Phase phv = get_phase(p, i);
+    const Phase* ph = &phv;
     const uint32_t tag_in = tag0 + (uint32_t)i;  // tag of phase i - 1
-    const uint32_t tag_out = tag_in + 1u;
-    // RMSNorm weights do not depend on anybody: request them before waiting (they are a DRAM miss, once per token)
-    const bool is_gemv = ph->type == PH_GEMV;
-    const int in_kind = ph->in_kind;
-    const int Kx = ph->Kx;
-    const __nv_bfloat16* norm_w = ph->norm_w;
-    uint4 wn_first = make_uint4(0u, 0u, 0u, 0u);
-    if (is_gemv && in_kind == IN_H && tid * 8 < Kx) wn_first = __ldg(reinterpret_cast<const uint4*>(norm_w) + tid);
-    if (tid == 0) stamp(p.trace, n_phases, i, 0);
-    if (i > 0) {
-      if (tid == 0) wait_counter(p.counter, cnt0 + (uint64_t)i * (uint64_t)n_cta, ctx);
-    }
-    named_bar_sync(1, kCT);  // B1: phase i - 1 is published; every consumer warp of this CTA has left its main loop
-
-    if (!is_gemv) {
-      // ================= attention of the new token (model.py:405-440), one kv head x sequence split per CTA =================
-      if (tid == 0) stamp(p.trace, n_phases, i, 1);
-      attention_phase(p, ph, x_s, xq, pos, tag_in, tag_out, ctx);
-      if (tid == 0) {
-        red_ctr(p.counter);
-        stamp(p.trace, n_phases, i, 4);
+    const uint64_t cnt_target = cnt0 + (uint64_t)i * (uint64_t)n_cta;
+    if (ph->type != PH_GEMV) {
+      switch (GQ) {
+        case 1: state = attention_phase<1>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        case 2: state = attention_phase<2>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        case 4: state = attention_phase<4>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        default: state = attention_phase<8>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
       }
       continue;
     }
-
-    // ================= GEMV phase: stage the activation row as int8 limbs =================
-    const int KT = ph->KT;
-    const int chunks_p = KT * 8;                 // 8-element chunks over Kp
-    const int n_chunks = Kx >> 3;
-    const uint32_t limb_row = (uint32_t)KT * 64u + 32u;
-    const uint64_t* in_pk = ph->in_off == kNone ? nullptr : xq + ph->in_off;
-    if (tid == 0) stamp(p.trace, n_phases, i, 1);
-    float ss = 0.f;
-    uint32_t amax_u = 0u;  // max |.| as bits: an Inf / NaN input shows up as >= 0x7f800000
-    if (in_kind == IN_H) {
-      // h += sum over ranks of the published deltas (rank order, fp32), then statistics of h and of h * w
-      for (int ci = tid; ci < n_chunks; ci += kCT) {
-        uint4 hv = h_s[ci];
-        if (in_pk != nullptr) {
-          float hf[8], acc[8];
-          unpack8(hv, hf);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-          for (int r0 = 0; r0 < p.world; r0 += 4) {
-            uint4 d[4];
-#pragma unroll
-            for (int rr = 0; rr < 4; ++rr)
-              if (r0 + rr < p.world) d[rr] = poll_chunk(in_pk + (size_t)(r0 + rr) * (Kx >> 1) + ci * 4, tag_in, ctx);
-#pragma unroll
-            for (int rr = 0; rr < 4; ++rr)
-              if (r0 + rr < p.world) {
-                float df[8];
-                unpack8(d[rr], df);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) acc[e] += df[e];
-              }
-          }
-          uint32_t o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            o[e] = float_to_bf16_bits(hf[2 * e] + acc[2 * e]) | (float_to_bf16_bits(hf[2 * e + 1] + acc[2 * e + 1]) << 16);
-          hv = make_uint4(o[0], o[1], o[2], o[3]);
-          h_s[ci] = hv;
-        }
-        const uint4 wn = ci == tid ? wn_first : __ldg(reinterpret_cast<const uint4*>(norm_w) + ci);
-        float f[8], wf[8];
-        unpack8(hv, f);
-        unpack8(wn, wf);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          ss = fmaf(f[e], f[e], ss);
-          amax_u = max(amax_u, __float_as_uint(f[e] * wf[e]) & 0x7fffffffu);
-        }
-      }
-    } else {
-      for (int ci = tid; ci < n_chunks; ci += kCT) {
-        const uint4 xv = poll_chunk(in_pk + ci * 4, tag_in, ctx);
-        float f[8];
-        unpack8(xv, f);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) amax_u = max(amax_u, __float_as_uint(f[e]) & 0x7fffffffu);
-      }
-    }
-    ss = warp_sum(ss);
-    amax_u = warp_max_u(amax_u);
-    if (lane == 0) {
-      part[warp * 2] = ss;
-      part[warp * 2 + 1] = __uint_as_float(amax_u);
-    }
-    named_bar_sync(1, kCT);  // B2
-    if (tid == 0) stamp(p.trace, n_phases, i, 6);
-    float up, rnorm = 1.f;
     {
-      float t = 0.f;
-      uint32_t am = 0u;
-      if (lane < kC) {
-        t = part[lane * 2];
-        am = __float_as_uint(part[lane * 2 + 1]);
-      }
-      t = warp_sum(t);
-      am = warp_max_u(am);
-      float bound = __uint_as_float(am);
-      bool bad = am >= 0x7f800000u;
-      if (in_kind == IN_H) {
-        rnorm = rsqrtf(t / (float)Kx + p.eps);
-        // |bf16(bf16(x r) w)| <= |x w| r (1 + 2^-8)^2: a bound within 2x of the true maximum costs at most one of the 23 bits
-        bound = bound * rnorm * 1.0079f;
-        bad = bad || !(bound < 3.0e38f);
-      }
-      // 2^e brings the bound into [2^21, 2^22): |round(x 2^e)| <= 2^22 - 2^14 for every bf16 x below the bound
-      int e = 0;
-      if (bound > 0.f) e = 21 - ((int)((__float_as_uint(bound) >> 23) & 0xFF) - 127);
-      e = max(-106, min(100, e));
-      up = __uint_as_float((uint32_t)(e + 127) << 23);
-      if (warp == 0 && lane == 0)
-        row_scale[gphase & 1] = bad ? __uint_as_float(0x7fc00000u) : __uint_as_float((uint32_t)(127 - e) << 23);
-    }
-    {
-      uint8_t* rows = x_s;
-      const int n_iter = (chunks_p + kCT - 1) / kCT;
-      for (int it = 0; it < n_iter; ++it) {
-        const int ci = it * kCT + tid;
-        const bool valid = ci < chunks_p;
-        float f[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = 0.f;
-        if (ci < n_chunks) {
-          if (in_kind == IN_H) {
-            float wf[8];
-            unpack8(h_s[ci], f);
-            unpack8(__ldg(reinterpret_cast<const uint4*>(norm_w) + ci), wf);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = bf16r(bf16r(f[e] * rnorm) * wf[e]);   // RMSNorm.forward, model.py:498-503
-          } else {
-            unpack8(load_chunk(in_pk + ci * 4), f);
-          }
-        }
-        int sl0 = 0, sl1 = 0, sl2 = 0;
-        if (valid) {
-          // balanced limbs without carries: X + 0x808080 = sum (a_i + 128) 256^i (see gemv_int4_imma.cu)
-          uint32_t v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = __float_as_uint(fmaf(f[e], up, kMagicF)) + 0x00408080u;
-          uint32_t lw[3][2];
-#pragma unroll
-          for (int l = 0; l < 3; ++l) {
-            const uint32_t sel = l == 0 ? 0x0062u : (l == 1 ? 0x0051u : 0x0040u);
-            const uint32_t p04 = __byte_perm(v[0], v[4], sel), p15 = __byte_perm(v[1], v[5], sel);
-            const uint32_t p26 = __byte_perm(v[2], v[6], sel), p37 = __byte_perm(v[3], v[7], sel);
-            lw[l][0] = __byte_perm(p04, p15, 0x5410) ^ 0x80808080u;
-            lw[l][1] = __byte_perm(p26, p37, 0x5410) ^ 0x80808080u;
-          }
-          sl0 = __dp4a((int)lw[0][0], 0x01010101, __dp4a((int)lw[0][1], 0x01010101, 0));
-          sl1 = __dp4a((int)lw[1][0], 0x01010101, __dp4a((int)lw[1][1], 0x01010101, 0));
-          sl2 = __dp4a((int)lw[2][0], 0x01010101, __dp4a((int)lw[2][1], 0x01010101, 0));
-          *reinterpret_cast<uint2*>(rows + (size_t)ci * 8) = make_uint2(lw[0][0], lw[0][1]);
-          *reinterpret_cast<uint2*>(rows + limb_row + (size_t)ci * 8) = make_uint2(lw[1][0], lw[1][1]);
-          *reinterpret_cast<uint2*>(rows + 2 * limb_row + (size_t)ci * 8) = make_uint2(lw[2][0], lw[2][1]);
-        }
-#pragma unroll
-        for (int o = GE::kSegLanes / 2; o; o >>= 1) {
-          sl0 += __shfl_xor_sync(0xffffffffu, sl0, o);
-          sl1 += __shfl_xor_sync(0xffffffffu, sl1, o);
-          sl2 += __shfl_xor_sync(0xffffffffu, sl2, o);
-        }
-        if (valid && (ci % GE::kSegLanes) == 0) {
-          float* Sp = S_s + (ci / GE::kSegLanes) * 8;
-          Sp[0] = (float)sl0; Sp[1] = (float)sl1; Sp[2] = (float)sl2; Sp[3] = 0.f;
-        }
+      const int n_chunks = ph->KT * 8;  // Kp == Kx in this kernel (check_model)
+      const int nch = (n_chunks + kCT - 1) / kCT;
+      float* rs = row_scale + (gphase & 1);
+      const uint32_t x_u = smem_u32(x_s), S_u = smem_u32(S_s);
+      if (ph->in_kind == IN_H) {
+        const float inv_k = 1.0f / (float)ph->Kx;
+        if (nch <= 1) stage_h<G, 1>(p, n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
+        else stage_h<G, 2>(p, n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
+      } else {
+        if (nch <= 1) stage_x<G, 1>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else if (nch <= 2) stage_x<G, 2>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else if (nch <= 4) stage_x<G, 4>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else stage_x<G, 8>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
       }
     }
-    named_bar_sync(1, kCT);  // B3: limbs, segment sums and the row scale are in place
-    if (tid == 0) stamp(p.trace, n_phases, i, 2);
-
-    // ================= main loop: warp w owns k-tiles 2 w, 2 w + 1 (128 k) of every stage =================
     int s0, s1;
-    strip_range(b, n_cta, ph->n_strips, ph->rot, s0, s1);
-    const uint32_t w_off = (uint32_t)warp * 1024u + (uint32_t)lane * 16u;
-    const uint32_t sz_off = (uint32_t)kStageW + (uint32_t)(G >= 128 ? warp * 128 / G : warp * GE::kNSeg) * 64u + (uint32_t)g * 4u;
-    const uint32_t S_u0 = smem_u32(S_s) + (uint32_t)(warp * GE::kNSeg) * 32u + (uint32_t)c * 8u;
-    const bool x_on = g < 3;  // MMA column g = limb g of the activation row
-    const uint32_t x_u0 = smem_u32(x_s) + (uint32_t)min(g, 2) * limb_row + (uint32_t)warp * 128u + (uint32_t)c * 8u;
-    for (int strip = s0; strip < s1; ++strip, ++li) {
-      float yacc[4] = {0.f, 0.f, 0.f, 0.f};
-      uint32_t xo = 0, S_u = S_u0;
-      for (int kt0 = 0; kt0 < KT; kt0 += kStageTiles) {
-        mbar_wait_b(&full[slot], par, ctx, 32u);
-        if (2 * warp < KT - kt0) {
-          const uint4 wa = lds128(stage_u + w_off), wb = lds128(stage_u + w_off + 512u);
-          uint2 xb[4];
-#pragma unroll
-          for (int h = 0; h < 4; ++h) xb[h] = x_on ? lds64u(x_u0 + xo + 32u * h) : make_uint2(0u, 0u);
-          constexpr uint32_t kM = 0x0f0f0f0fu;
-          const uint32_t wl[4][2] = {{wa.x, wa.y}, {wa.z, wa.w}, {wb.x, wb.y}, {wb.z, wb.w}};
-          if constexpr (GE::kNSeg == 1) {
-            const uint32_t p0 = lds32(stage_u + sz_off), p1 = lds32(stage_u + sz_off + 32u);
-            const float2 S = lds64f(S_u);
-            int a0[4] = {(int)kMagicI, (int)kMagicI, (int)kMagicI, (int)kMagicI}, a1[4] = {0, 0, 0, 0};
-            imma_16832(a0, wl[0][0] & kM, wl[0][1] & kM, (wl[0][0] >> 4) & kM, (wl[0][1] >> 4) & kM, xb[0].x, xb[0].y);
-            imma_16832(a1, wl[1][0] & kM, wl[1][1] & kM, (wl[1][0] >> 4) & kM, (wl[1][1] >> 4) & kM, xb[1].x, xb[1].y);
-            imma_16832(a0, wl[2][0] & kM, wl[2][1] & kM, (wl[2][0] >> 4) & kM, (wl[2][1] >> 4) & kM, xb[2].x, xb[2].y);
-            imma_16832(a1, wl[3][0] & kM, wl[3][1] & kM, (wl[3][0] >> 4) & kM, (wl[3][1] >> 4) & kM, xb[3].x, xb[3].y);
-            const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
-            const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0 & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1 & 0xFFFF0000u));
-            const float f0 = __int_as_float(a0[0] + a1[0]) - kMagicF, f1 = __int_as_float(a0[1] + a1[1]) - kMagicF;
-            const float f2 = __int_as_float(a0[2] + a1[2]) - kMagicF, f3 = __int_as_float(a0[3] + a1[3]) - kMagicF;
-            yacc[0] = fmaf(sc0, f0, fmaf(zz0, S.x, yacc[0]));
-            yacc[1] = fmaf(sc0, f1, fmaf(zz0, S.y, yacc[1]));
-            yacc[2] = fmaf(sc1, f2, fmaf(zz1, S.x, yacc[2]));
-            yacc[3] = fmaf(sc1, f3, fmaf(zz1, S.y, yacc[3]));
-          } else {
-            constexpr int kHS = 4 / GE::kNSeg;
-#pragma unroll
-            for (int sg = 0; sg < GE::kNSeg; ++sg) {
-              const uint32_t p0 = lds32(stage_u + sz_off + 64u * sg), p1 = lds32(stage_u + sz_off + 64u * sg + 32u);
-              const float2 S = lds64f(S_u + 32u * sg);
-              int a[4] = {(int)kMagicI, (int)kMagicI, (int)kMagicI, (int)kMagicI};
-#pragma unroll
-              for (int hh = 0; hh < kHS; ++hh) {
-                const int h = sg * kHS + hh;
-                imma_16832(a, wl[h][0] & kM, wl[h][1] & kM, (wl[h][0] >> 4) & kM, (wl[h][1] >> 4) & kM, xb[h].x, xb[h].y);
-              }
-              const float sc0 = __uint_as_float(p0 << 16), sc1 = __uint_as_float(p1 << 16);
-              const float zz0 = fmaf(-8.f, sc0, __uint_as_float(p0 & 0xFFFF0000u)), zz1 = fmaf(-8.f, sc1, __uint_as_float(p1 & 0xFFFF0000u));
-              yacc[0] = fmaf(sc0, __int_as_float(a[0]) - kMagicF, fmaf(zz0, S.x, yacc[0]));
-              yacc[1] = fmaf(sc0, __int_as_float(a[1]) - kMagicF, fmaf(zz0, S.y, yacc[1]));
-              yacc[2] = fmaf(sc1, __int_as_float(a[2]) - kMagicF, fmaf(zz1, S.x, yacc[2]));
-              yacc[3] = fmaf(sc1, __int_as_float(a[3]) - kMagicF, fmaf(zz1, S.y, yacc[3]));
-            }
-          }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[slot]);
-        xo += kStageTiles * 64u;
-        S_u += (kStageTiles * 64 / GE::kSegK) * 32u;
-        stage_u += kStageBytes;
-        if (++slot == stages) {
-          slot = 0;
-          par ^= 1u;
-          stage_u = ring_u;
-        }
-      }
-      const int rbuf = (int)(li & 1u);
-      const uint32_t use = li >> 1;
-      float* rb = red + (size_t)rbuf * (kC * 128);
-      if (use > 0) mbar_wait_b(&red_free[rbuf], (use - 1) & 1u, ctx, 64u);
-      *reinterpret_cast<float4*>(rb + (warp * 32 + lane) * 4) = make_float4(yacc[0], yacc[1], yacc[2], yacc[3]);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&red_full[rbuf]);
-    }
+    strip_range(b, n_cta, ph->n_strips, rot, s0, s1);
+    rot = next_rot(rot, ph->rot_inc, n_cta);
+    const int KT = ph->KT;
+    const uint32_t limb_row = (uint32_t)KT * 64u + 32u;
+    if (KT <= 2 * kStageTiles)
+      state = gemv_main<G, true>(ring_u, bar0, stages, KT, s1 - s0, smem_u32(x_s), limb_row, smem_u32(S_s), red_u, state, li, p.dbg);
+    else
+      state = gemv_main<G, false>(ring_u, bar0, stages, KT, s1 - s0, smem_u32(x_s), limb_row, smem_u32(S_s), red_u, state, li, p.dbg);
+    li += (uint32_t)(s1 - s0);
     if (tid == 0) stamp(p.trace, n_phases, i, 3);
     ++gphase;
   }
@@ -893,33 +1258,35 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const Params p
 struct SmemPlan {
   int stages;
   size_t smem;
-  uint32_t off_x, off_S, off_red, off_h, off_misc;
+  uint32_t off_x, off_S, off_red, off_h, off_misc, off_lay;
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-static bool plan_smem(int G, int64_t Kmax, int dim, int Gq, SmemPlan& pl) {
+static bool plan_smem(int G, int64_t Kmax, int dim, int Gq, int n_layer, SmemPlan& pl) {
   const int seg_k = G < 128 ? G : 128;
   const size_t stage_bytes = (size_t)kStageW + (size_t)(kStageTiles * 64 / G) * 64;
   const size_t limbs = (size_t)3 * (size_t)(Kmax + 32);
-  const size_t attn = ((size_t)((Gq * kQPad + 31) & ~31) + (size_t)kC * kHG * kPartStride) * 4;
+  const size_t attn = (size_t)Gq * 128 * 4 + 512 + (size_t)kC * Gq * kPartStride * 4;  // q, new k / v, warp partials
   const size_t x_bytes = align_up(limbs > attn ? limbs : attn, 128);
   const size_t S_bytes = align_up((size_t)(Kmax / seg_k) * 32, 128);
   const size_t red_bytes = (size_t)kRedBufs * kC * 128 * 4;
   const size_t h_bytes = align_up((size_t)dim * 2, 128);
   const size_t misc = align_up((2 * kC + 4) * 4 + (2 * 16 + 2 * kRedBufs) * 8, 128);
-  const size_t fixed = x_bytes + S_bytes + red_bytes + h_bytes + misc;
-  const size_t cap = 227 * 1024;
+  const size_t lay = align_up((size_t)n_layer * sizeof(LayerPtrs), 128);
+  const size_t fixed = x_bytes + S_bytes + red_bytes + h_bytes + misc + lay;
+  const size_t cap = 227 * 1024 - kHdrBytes;
   if (fixed + 3 * stage_bytes > cap) return false;
   int st = (int)((cap - fixed) / stage_bytes);
   if (st > 16) st = 16;
   pl.stages = st;
-  size_t off = (size_t)st * stage_bytes;
+  size_t off = kHdrBytes + (size_t)st * stage_bytes;
   pl.off_x = (uint32_t)off; off += x_bytes;
   pl.off_S = (uint32_t)off; off += S_bytes;
   pl.off_red = (uint32_t)off; off += red_bytes;
   pl.off_h = (uint32_t)off; off += h_bytes;
   pl.off_misc = (uint32_t)off; off += misc;
+  pl.off_lay = (uint32_t)off; off += lay;
   pl.smem = off;
   return true;
 }
@@ -945,8 +1312,11 @@ static Offsets xchg_layout(const ao_b200_mega_model& m) {
 
 static int check_model(const ao_b200_mega_model* m) {
   AO_CHECK_ARG(m && m->layers && m->n_layer > 0 && m->n_cta > 0);
-  AO_CHECK_ARG(m->head_dim == 128 && m->n_kv_head > 0 && m->n_head % m->n_kv_head == 0 && m->n_head / m->n_kv_head <= 8);
-  AO_CHECK_ARG(m->dim % 128 == 0 && m->inter % 128 == 0 && (m->n_head * 128) % 128 == 0 && m->vocab > 0);
+  AO_CHECK_ARG(m->head_dim == 128 && m->n_kv_head > 0 && m->n_head % m->n_kv_head == 0);
+  const int gq = m->n_head / m->n_kv_head;
+  AO_CHECK_ARG(gq == 1 || gq == 2 || gq == 4 || gq == 8);
+  AO_CHECK_ARG(m->dim % 128 == 0 && m->inter % 128 == 0 && m->vocab > 0);
+  if (m->dim > 8192 || m->inter > 32768 || m->n_head * 128 > 32768) return AO_B200_ERR_UNSUPPORTED;  // staging: <= 2 / 8 chunks of 8 per thread
   AO_CHECK_ARG(m->world >= 1 && m->world <= kMaxWorld && m->rank >= 0 && m->rank < m->world);
   AO_CHECK_ARG(m->emb && m->freqs && m->tok && m->pos && m->logits && m->state && m->out_packed && m->out_sz && m->out_norm);
   AO_CHECK_ARG(m->max_seq > 0 && m->n_kv_head <= m->n_cta);
@@ -963,7 +1333,7 @@ using namespace ao::mega;
 
 extern "C" int64_t ao_b200_decode_mega_plan_bytes(const ao_b200_mega_model* m) {
   if (check_model(m) != AO_B200_OK) return 0;
-  return (int64_t)sizeof(Phase) * (5 * (int64_t)m->n_layer + 1);
+  return (int64_t)sizeof(LayerPtrs) * (int64_t)m->n_layer;
 }
 
 extern "C" int64_t ao_b200_decode_mega_xchg_bytes(const ao_b200_mega_model* m) {
@@ -977,49 +1347,22 @@ extern "C" int ao_b200_decode_mega_setup(const ao_b200_mega_model* m, void* plan
   const int rc = check_model(m);
   if (rc != AO_B200_OK) return rc;
   AO_CHECK_ARG(plan_dev && plan_bytes >= ao_b200_decode_mega_plan_bytes(m));
-  const Offsets o = xchg_layout(*m);
-  const int n_phases = 5 * m->n_layer + 1;
-  std::vector<Phase> ph((size_t)n_phases);
-  memset(ph.data(), 0, sizeof(Phase) * ph.size());
-  int rot = 0;
-  auto gemv = [&](Phase& q, const void* packed, const void* sz, int64_t N, int64_t K) {
-    q.type = PH_GEMV;
-    q.packed = static_cast<const uint8_t*>(packed);
-    q.sz = static_cast<const uint32_t*>(sz);
-    q.KT = (int)(K / 64);
-    q.Kx = (int)K;
-    q.N_out = (int)N;
-    q.n_strips = (int)((N + 15) / 16);
-    q.rot = rot;
-    rot = (rot + q.n_strips % m->n_cta) % m->n_cta;  // the CTAs that got an extra strip rotate from phase to phase
-  };
-  const int64_t qkv_n = (int64_t)(m->n_head + 2 * m->n_kv_head) * 128, att_n = (int64_t)m->n_head * 128;
+  std::vector<LayerPtrs> lp((size_t)m->n_layer);
   for (int l = 0; l < m->n_layer; ++l) {
     const ao_b200_mega_layer& L = m->layers[l];
     AO_CHECK_ARG(L.wqkv_packed && L.wqkv_sz && L.wo_packed && L.wo_sz && L.w13_packed && L.w13_sz && L.w2_packed && L.w2_sz);
     AO_CHECK_ARG(L.attn_norm && L.ffn_norm && L.k_cache && L.v_cache);
-    Phase* q = &ph[(size_t)5 * l];
-    gemv(q[0], L.wqkv_packed, L.wqkv_sz, qkv_n, m->dim);
-    q[0].in_kind = IN_H; q[0].in_off = l == 0 ? kNone : o.d2; q[0].norm_w = static_cast<const __nv_bfloat16*>(L.attn_norm);
-    q[0].out_kind = OUT_PK; q[0].out_off = o.qkv;
-    q[1].type = PH_ATTN; q[1].in_off = o.qkv; q[1].out_off = o.att; q[1].aux_off = o.aux;
-    q[1].k_cache = static_cast<__nv_bfloat16*>(L.k_cache); q[1].v_cache = static_cast<__nv_bfloat16*>(L.v_cache);
-    gemv(q[2], L.wo_packed, L.wo_sz, m->dim, att_n);
-    q[2].in_kind = IN_PK; q[2].in_off = o.att; q[2].out_kind = OUT_DELTA; q[2].out_off = o.d1;
-    gemv(q[3], L.w13_packed, L.w13_sz, 2 * (int64_t)m->inter, m->dim);
-    q[3].N_out = m->inter;  // outputs after SiLU*mul (n_strips stays 2 I / 16)
-    q[3].in_kind = IN_H; q[3].in_off = o.d1; q[3].norm_w = static_cast<const __nv_bfloat16*>(L.ffn_norm);
-    q[3].out_kind = OUT_SILU; q[3].out_off = o.mid;
-    gemv(q[4], L.w2_packed, L.w2_sz, m->dim, m->inter);
-    q[4].in_kind = IN_PK; q[4].in_off = o.mid; q[4].out_kind = OUT_DELTA; q[4].out_off = o.d2;
+    LayerPtrs& q = lp[(size_t)l];
+    q.w[0] = static_cast<const uint8_t*>(L.wqkv_packed); q.sz[0] = static_cast<const uint32_t*>(L.wqkv_sz);
+    q.w[1] = static_cast<const uint8_t*>(L.wo_packed); q.sz[1] = static_cast<const uint32_t*>(L.wo_sz);
+    q.w[2] = static_cast<const uint8_t*>(L.w13_packed); q.sz[2] = static_cast<const uint32_t*>(L.w13_sz);
+    q.w[3] = static_cast<const uint8_t*>(L.w2_packed); q.sz[3] = static_cast<const uint32_t*>(L.w2_sz);
+    q.norm[0] = static_cast<const __nv_bfloat16*>(L.attn_norm); q.norm[1] = static_cast<const __nv_bfloat16*>(L.ffn_norm);
+    q.kc = static_cast<__nv_bfloat16*>(L.k_cache); q.vc = static_cast<__nv_bfloat16*>(L.v_cache);
   }
-  Phase& f = ph[(size_t)5 * m->n_layer];
-  gemv(f, m->out_packed, m->out_sz, m->vocab, m->dim);
-  f.in_kind = IN_H; f.in_off = o.d2; f.norm_w = static_cast<const __nv_bfloat16*>(m->out_norm);
-  f.out_kind = OUT_PLAIN; f.out_plain = static_cast<__nv_bfloat16*>(m->logits);
   auto s = static_cast<cudaStream_t>(stream);
-  if (cudaMemcpyAsync(plan_dev, ph.data(), sizeof(Phase) * ph.size(), cudaMemcpyHostToDevice, s) != cudaSuccess) return AO_B200_ERR_CUDA;
-  if (cudaStreamSynchronize(s) != cudaSuccess) return AO_B200_ERR_CUDA;  // ph is a host temporary (set-up time only)
+  if (cudaMemcpyAsync(plan_dev, lp.data(), sizeof(LayerPtrs) * lp.size(), cudaMemcpyHostToDevice, s) != cudaSuccess) return AO_B200_ERR_CUDA;
+  if (cudaStreamSynchronize(s) != cudaSuccess) return AO_B200_ERR_CUDA;  // lp is a host temporary (set-up time only)
   return AO_B200_OK;
 }
 
@@ -1028,16 +1371,40 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   if (rc != AO_B200_OK) return rc;
   AO_CHECK_ARG(plan_dev);
   const int Gq = m->n_head / m->n_kv_head;
-  const int64_t att_n = (int64_t)m->n_head * 128;
+  const int64_t qkv_n = (int64_t)(m->n_head + 2 * m->n_kv_head) * 128, att_n = (int64_t)m->n_head * 128;
   int64_t Kmax = m->dim > m->inter ? m->dim : m->inter;
   if (att_n > Kmax) Kmax = att_n;
   SmemPlan pl;
-  if (!plan_smem(m->group_size, Kmax, m->dim, Gq, pl)) return AO_B200_ERR_WORKSPACE;
+  if (!plan_smem(m->group_size, Kmax, m->dim, Gq, m->n_layer, pl)) return AO_B200_ERR_WORKSPACE;
   Params p;
   memset(&p, 0, sizeof p);
-  p.phases = static_cast<const Phase*>(plan_dev);
+  p.layers = static_cast<const LayerPtrs*>(plan_dev);
+  p.n_layer = m->n_layer;
   p.n_phases = 5 * m->n_layer + 1;
   p.n_cta = m->n_cta;
+  {
+    const Offsets o = xchg_layout(*m);
+    auto gemv = [&](Kind& q, int64_t N, int64_t K, int in_kind, uint32_t in_off, int out_kind, uint32_t out_off) {
+      q.type = PH_GEMV;
+      q.KT = (int)(K / 64);
+      q.Kx = (int)K;
+      q.N_out = (int)N;
+      q.n_strips = (int)((N + 15) / 16);
+      q.rot_inc = q.n_strips % m->n_cta;  // the CTAs that got an extra strip rotate from phase to phase
+      q.in_kind = in_kind; q.in_off = in_off; q.out_kind = out_kind; q.out_off = out_off;
+    };
+    gemv(p.kinds[K_WQKV], qkv_n, m->dim, IN_H, o.d2, OUT_PK, o.qkv);
+    p.kinds[K_ATTN].type = PH_ATTN; p.kinds[K_ATTN].in_off = o.qkv; p.kinds[K_ATTN].out_off = o.att; p.kinds[K_ATTN].aux_off = o.aux;
+    gemv(p.kinds[K_WO], m->dim, att_n, IN_PK, o.att, OUT_DELTA, o.d1);
+    gemv(p.kinds[K_W13], 2 * (int64_t)m->inter, m->dim, IN_H, o.d1, OUT_SILU, o.mid);
+    p.kinds[K_W13].N_out = m->inter;  // outputs after SiLU*mul (n_strips stays 2 I / 16)
+    gemv(p.kinds[K_W2], m->dim, m->inter, IN_PK, o.mid, OUT_DELTA, o.d2);
+    gemv(p.kinds[K_OUT], m->vocab, m->dim, IN_H, o.d2, OUT_PLAIN, 0);
+  }
+  p.out_w = static_cast<const uint8_t*>(m->out_packed);
+  p.out_sz = static_cast<const uint32_t*>(m->out_sz);
+  p.out_norm = static_cast<const __nv_bfloat16*>(m->out_norm);
+  p.logits = static_cast<__nv_bfloat16*>(m->logits);
   for (int r = 0; r < m->world; ++r) p.xchg[r] = static_cast<uint64_t*>(m->xchg[r]);
   p.world = m->world;
   p.rank = m->rank;
@@ -1048,16 +1415,20 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   uint8_t* st = static_cast<uint8_t*>(m->state);
   p.counter = reinterpret_cast<uint64_t*>(st);
   p.step = reinterpret_cast<uint32_t*>(st + 8);
-  p.status = reinterpret_cast<uint32_t*>(st + 12);
+  p.status = reinterpret_cast<uint32_t*>(st + 12);   // [status][slow polls]
   p.dim = m->dim; p.H = m->n_head; p.Hkv = m->n_kv_head; p.S = m->max_seq;
-  p.attn_bpc = m->attn_blocks_per_cta > 0 ? m->attn_blocks_per_cta : 32;
+  p.attn_spc = m->attn_blocks_per_cta > 0 ? m->attn_blocks_per_cta : 4;
   p.attn_max_split = m->n_cta / m->n_kv_head;
   p.eps = m->eps;
   p.attn_scale = 1.0f / sqrtf((float)m->head_dim);
   p.stages = pl.stages;
-  p.off_x = pl.off_x; p.off_S = pl.off_S; p.off_red = pl.off_red; p.off_h = pl.off_h; p.off_misc = pl.off_misc;
+  p.off_x = pl.off_x; p.off_S = pl.off_S; p.off_red = pl.off_red; p.off_h = pl.off_h; p.off_misc = pl.off_misc; p.off_lay = pl.off_lay;
   p.timeout_ns = (unsigned long long)(m->timeout_ms > 0 ? m->timeout_ms : 2000) * 1000000ull;
   p.trace = static_cast<unsigned long long*>(m->trace);
+  {
+    static const int dbg = []() { const char* e = std::getenv("AO_B200_MEGA_DEBUG"); return e ? std::atoi(e) : 0; }();
+    p.dbg = dbg;
+  }
   using KernelFn = void (*)(const Params);
   KernelFn kern = nullptr;
   int gi = 0;
