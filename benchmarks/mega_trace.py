@@ -75,6 +75,7 @@ def main():
                 d["n_active"] = int(on.sum())
                 d["q_ready"] = mmm((tr[:, idx, 2] - tr[:, idx, 1])[on])      # qkv packets polled, RoPE, q in shared memory
                 d["tiles"] = mmm((tr[:, idx, 3] - tr[:, idx, 2])[on])        # K / V tiles out of the ring
+                d["tiles_wait_first_round"] = mmm((tr[:, idx, 6] - tr[:, idx, 2])[on])   # of which: waiting for the tiles
                 d["merge_publish"] = mmm((tr[:, idx, 4] - tr[:, idx, 3])[on])
             d["total"] = mmm(tr[:, idx, 4] - tr[:, idx, 0])
         return d

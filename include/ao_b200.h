@@ -314,12 +314,15 @@ typedef struct ao_b200_mega_layer {
   const void* w13_packed; const void* w13_sz;
   const void* w2_packed; const void* w2_sz;
   const void* attn_norm; const void* ffn_norm;   /* bf16 [dim] */
-  void* k_cache; void* v_cache;
+  void* k_cache; void* v_cache;                  /* the model's KVCache, bf16 [n_kv_head][max_seq][128]: appended to */
+  void* k_pad; void* v_pad;                      /* the kernel's own copy with padded rows, bf16 [n_kv_head][S_pad][136],
+                                                    S_pad = max_seq rounded up to 32: must hold rows 0 .. *pos - 1 of the
+                                                    caches when a launch starts (the launch appends row *pos to both) */
 } ao_b200_mega_layer;
 
 typedef struct ao_b200_mega_model {
   int32_t n_layer, dim, n_head, n_kv_head, head_dim, inter, vocab, group_size, max_seq;
-  int32_t world, rank, n_cta, timeout_ms, attn_blocks_per_cta;  /* attn_blocks_per_cta: 16-position blocks per CTA before the sequence is split (0 = default 32) */
+  int32_t world, rank, n_cta, timeout_ms, attn_blocks_per_cta;  /* attn_blocks_per_cta: 32-position tiles per CTA before the sequence is split over more CTAs (0 = default 8) */
   float eps;
   int32_t reserved;
   const ao_b200_mega_layer* layers;   /* HOST array [n_layer] */

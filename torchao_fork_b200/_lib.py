@@ -15,7 +15,7 @@ _vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_
 class MegaLayer(ctypes.Structure):
     """ao_b200_mega_layer (include/ao_b200.h)"""
     _fields_ = [(n, _vp) for n in ("wqkv_packed", "wqkv_sz", "wo_packed", "wo_sz", "w13_packed", "w13_sz", "w2_packed",
-                                   "w2_sz", "attn_norm", "ffn_norm", "k_cache", "v_cache")]
+                                   "w2_sz", "attn_norm", "ffn_norm", "k_cache", "v_cache", "k_pad", "v_pad")]
 
 
 class MegaModel(ctypes.Structure):

@@ -223,6 +223,11 @@ class DecodeEngine:
         dev = self.device
         nl = len(self.layers)
         arr = (_lib.MegaLayer * nl)()
+        # the kernel's own K / V cache with padded rows (272 B: conflict-free ldmatrix): [layer][k | v][Hkv][S_pad][136]
+        s_pad = -(-self.S // 32) * 32
+        self._mega_kv = torch.zeros(nl, 2, self.Hkv, s_pad, 136, dtype=torch.bfloat16, device=dev)
+        for i, l in enumerate(self.layers):
+            arr[i].k_pad, arr[i].v_pad = self._mega_kv[i, 0].data_ptr(), self._mega_kv[i, 1].data_ptr()
         for i, l in enumerate(self.layers):
             a = arr[i]
             a.wqkv_packed, a.wqkv_sz = l["wqkv"].packed.data_ptr(), l["wqkv"].sz.data_ptr()
@@ -238,6 +243,8 @@ class DecodeEngine:
         m.n_cta = torch.cuda.get_device_properties(dev).multi_processor_count
         if os.environ.get("AO_B200_MEGA_CTAS"):
             m.n_cta = int(os.environ["AO_B200_MEGA_CTAS"])
+        if not attn_blocks_per_cta and os.environ.get("AO_B200_MEGA_ATTN_SPC"):  # tuning knob: 32-position tiles per CTA
+            attn_blocks_per_cta = int(os.environ["AO_B200_MEGA_ATTN_SPC"])
         m.timeout_ms, m.attn_blocks_per_cta = timeout_ms, attn_blocks_per_cta
         m.eps = self.eps
         m.layers = ctypes.cast(arr, ctypes.POINTER(_lib.MegaLayer))
@@ -263,6 +270,12 @@ class DecodeEngine:
         torch.cuda.synchronize(dev)
         _lib.check(L.ao_b200_decode_mega_setup(ctypes.byref(m), self._mega_plan.data_ptr(), pb,
                                                torch.cuda.current_stream(dev).cuda_stream), "decode_mega_setup")
+
+    def _sync_mega_kv(self):
+        """Copies the model's KV caches (rows written by prefill / the eager model) into the kernel's padded copy."""
+        for i, l in enumerate(self.layers):
+            self._mega_kv[i, 0, :, : self.S, :128].copy_(l["k_cache"][0])
+            self._mega_kv[i, 1, :, : self.S, :128].copy_(l["v_cache"][0])
 
     def mega_status(self) -> int:
         """Sticky status word of the persistent kernel (0 = fine; non-zero = a wait inside it timed out)."""
@@ -443,6 +456,8 @@ class DecodeEngine:
         self.tok.copy_(tokens.reshape(-1).to(torch.int64))
         self.pos.fill_(pos)
         self._host_pos = pos
+        if self.mega:
+            self._sync_mega_kv()
 
     def step(self) -> torch.Tensor:
         """Runs one decode step; returns the device buffer holding the sampled tokens [B] (overwritten by

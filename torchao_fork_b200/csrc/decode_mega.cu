@@ -53,9 +53,14 @@ constexpr int kRedBufs = 2;
 constexpr uint32_t kMagicI = 0x4B400000u;    // bits of 1.5 * 2^23
 constexpr float kMagicF = 12582912.0f;
 constexpr int kMaxWorld = 8;
-constexpr int kAttnPos = 32;                 // cache positions per ring stage: 8 KB of K rows + 8 KB of V rows
+constexpr int kAttnPos = 32;                 // cache positions per ring stage
+constexpr int kKvPitch = 136;                // elements per row of the private K / V cache: 272 B, so that the 8 rows of an
+                                             // ldmatrix land in 8 different 16-byte bank groups (a 256 B pitch: 8-way conflicts)
+constexpr int kKvTileBytes = kAttnPos * kKvPitch * 2;   // 8704 B of K rows, then 8704 B of V rows
+constexpr int kAttnStageBytes = 2 * kKvTileBytes;       // 17408
+constexpr int kAttnRound = 8;                // tiles walked concurrently by a CTA (one warp each)
 constexpr int kPartStride = 132;             // attention partial: 128 acc + m + l (+ pad)
-constexpr int kHdrBytes = 128;               // shared-memory header (wait context) in front of the ring
+constexpr int kHdrBytes = 1024;              // shared-memory header in front of the ring: wait context + a copy of Params
 
 enum { PH_GEMV = 0, PH_ATTN = 1 };
 enum { IN_H = 0, IN_PK = 1 };
@@ -66,12 +71,14 @@ constexpr uint32_t kNone = 0xffffffffu;
 // per-kind constants (kernel parameters = constant bank): a phase's description costs no global load on the critical path
 // (the first version read a 96-byte Phase record per phase from global memory: a DRAM miss per phase per SM, because the
 // weight stream evicts it from L2 between tokens).
-struct alignas(16) LayerPtrs {      // 96 bytes
+struct alignas(16) LayerPtrs {      // 112 bytes
   const uint8_t* w[4];              // wqkv, wo, w13, w2: strip-major int4 [Np/16][Kp/64][512 B]
   const uint32_t* sz[4];            // strip-major [Np/16][Kp/G][16] (scale | zero << 16)
   const __nv_bfloat16* norm[2];     // attention_norm, ffn_norm
-  __nv_bfloat16* kc;                // [Hkv][S][128]
+  __nv_bfloat16* kc;                // [Hkv][S][128]: the model's KVCache (appended to, never read here)
   __nv_bfloat16* vc;
+  __nv_bfloat16* kp;                // [Hkv][S_pad][136]: the kernel's own copy with padded rows (read through the ring)
+  __nv_bfloat16* vp;
 };
 enum { K_WQKV = 0, K_ATTN = 1, K_WO = 2, K_W13 = 3, K_W2 = 4, K_OUT = 5, kKinds = 6 };
 struct Kind {
@@ -89,6 +96,8 @@ struct Phase {
   __nv_bfloat16* out_plain;
   __nv_bfloat16* k_cache;
   __nv_bfloat16* v_cache;
+  __nv_bfloat16* k_pad;
+  __nv_bfloat16* v_pad;
   uint32_t in_off, out_off, aux_off;
   int type, in_kind, out_kind;
   int KT, n_strips, N_out, Kx, rot_inc;
@@ -111,7 +120,7 @@ struct Params {
   uint64_t* counter;              // arrivals, monotonic over the life of the state buffer
   uint32_t* step;                 // launches so far
   uint32_t* status;               // sticky error bits
-  int dim, H, Hkv, S, attn_spc, attn_max_split;
+  int dim, H, Hkv, S, S_pad, attn_spc, attn_max_split;
   float eps, attn_scale;
   int stages;
   uint32_t off_x, off_S, off_red, off_h, off_misc, off_lay;
@@ -130,6 +139,14 @@ struct SCtx {
 __device__ __forceinline__ SCtx* sctx() {
   extern __shared__ __align__(128) uint8_t smem_mega[];
   return reinterpret_cast<SCtx*>(smem_mega);
+}
+// The kernel parameters, copied to shared memory at kernel start: the non-inlined role functions read them with LDS
+// instead of generic loads from the parameter window (a reference to a __grid_constant__ parameter: every p.x was a
+// long-scoreboard stall on the critical path between two projections).
+static_assert(sizeof(Params) + 64 <= kHdrBytes, "Params must fit the shared-memory header");
+__device__ __forceinline__ const Params& sparams() {
+  extern __shared__ __align__(128) uint8_t smem_mega[];
+  return *reinterpret_cast<const Params*>(smem_mega + 64);
 }
 
 // ------------------------------------------------------------------------------------------------ small helpers
@@ -325,7 +342,8 @@ struct Geom {
   static constexpr int kNSeg = 128 / kSegK;
   static constexpr int kSegLanes = kSegK / 8;
   static constexpr int kStageSZ = (kStageTiles * 64 / G) * 64;
-  static constexpr int kStageBytes = kStageW + kStageSZ;
+  static constexpr int kStageBytes = kStageW + kStageSZ;                                         // a weight stage
+  static constexpr int kSlotBytes = kStageBytes > kAttnStageBytes ? kStageBytes : kAttnStageBytes;  // a ring slot
 };
 
 // shared-memory addresses of the barriers, derived from the first one
@@ -354,10 +372,11 @@ __device__ __forceinline__ Phase get_phase(const Params& p, int i) {
   ph.type = k.type; ph.in_kind = k.in_kind; ph.out_kind = k.out_kind;
   ph.KT = k.KT; ph.n_strips = k.n_strips; ph.N_out = k.N_out; ph.Kx = k.Kx; ph.rot_inc = k.rot_inc;
   ph.packed = nullptr; ph.sz = nullptr; ph.norm_w = nullptr; ph.out_plain = nullptr; ph.k_cache = nullptr; ph.v_cache = nullptr;
+  ph.k_pad = nullptr; ph.v_pad = nullptr;
   if (kind == K_OUT) {
     ph.packed = p.out_w; ph.sz = p.out_sz; ph.norm_w = p.out_norm; ph.out_plain = p.logits;
   } else if (kind == K_ATTN) {
-    ph.k_cache = lay_s[layer].kc; ph.v_cache = lay_s[layer].vc;
+    ph.k_cache = lay_s[layer].kc; ph.v_cache = lay_s[layer].vc; ph.k_pad = lay_s[layer].kp; ph.v_pad = lay_s[layer].vp;
   } else {
     const int wi = kind == K_WQKV ? 0 : kind - 1;
     ph.packed = lay_s[layer].w[wi]; ph.sz = lay_s[layer].sz[wi];
@@ -374,8 +393,9 @@ __device__ __forceinline__ int next_rot(int rot, int inc, int n_cta) {
 // ------------------------------------------------------------------------------------------------ producer warp
 // The CTA's share of every byte of the token, in phase order, through the ring.
 template <int G>
-__device__ __noinline__ void producer_loop(const Params& p, int pos, uint32_t ring_u, uint32_t bar0) {
-  constexpr int kStageBytes = Geom<G>::kStageBytes;
+__device__ __noinline__ void producer_loop(int pos, uint32_t ring_u, uint32_t bar0) {
+  constexpr int kStageBytes = Geom<G>::kSlotBytes;
+  const Params& p = sparams();
   const int b = blockIdx.x, n_cta = p.n_cta, stages = p.stages, n_phases = p.n_phases;
   const Bars bars = make_bars(bar0, stages);
   int slot = 0, rot = 0;
@@ -409,21 +429,20 @@ __device__ __noinline__ void producer_loop(const Params& p, int pos, uint32_t ri
         srow += (int64_t)n_groups * 16;
       }
     } else {
-      // K / V rows of this CTA's attention slice: rows [32 t, 32 t + 32) of the kv head, K into the first 8 KB of the
-      // stage, V into the second.  Rows written by EARLIER launches only; the new token's row is patched in by the
-      // consumers (attention_phase).
+      // K / V rows of this CTA's attention slice out of the padded private cache: rows [32 t, 32 t + 32) of the kv head,
+      // K into the first 8704 B of the slot, V into the second.  Rows written by EARLIER launches only; the new token's
+      // row is patched in by the consumers (attention_phase).
       const AttnPart a = attn_partition(pos, p.S, p.Hkv, p.attn_spc, p.attn_max_split, b);
       if (a.active) {
-        const __nv_bfloat16* kc = ph->k_cache + (int64_t)a.kvh * p.S * 128;
-        const __nv_bfloat16* vc = ph->v_cache + (int64_t)a.kvh * p.S * 128;
+        const __nv_bfloat16* kc = ph->k_pad + (int64_t)a.kvh * p.S_pad * kKvPitch;
+        const __nv_bfloat16* vc = ph->v_pad + (int64_t)a.kvh * p.S_pad * kKvPitch;
         for (int t = a.t0; t < a.t1; ++t) {
-          const int j0 = t * kAttnPos;
-          const uint32_t bytes = (uint32_t)min(kAttnPos, p.S - j0) * 256u;
+          const int64_t e0 = (int64_t)t * kAttnPos * kKvPitch;
           const uint32_t dst = ring_u + (uint32_t)slot * kStageBytes;
           bar_wait(bars.empty + 8u * slot, par, 8u);
-          bar_expect_tx(bars.full + 8u * slot, 2u * bytes);
-          bulk_g2s_u(dst, kc + (int64_t)j0 * 128, bytes, bars.full + 8u * slot);
-          bulk_g2s_u(dst + 8192u, vc + (int64_t)j0 * 128, bytes, bars.full + 8u * slot);
+          bar_expect_tx(bars.full + 8u * slot, (uint32_t)kAttnStageBytes);
+          bulk_g2s_u(dst, kc + e0, (uint32_t)kKvTileBytes, bars.full + 8u * slot);
+          bulk_g2s_u(dst + (uint32_t)kKvTileBytes, vc + e0, (uint32_t)kKvTileBytes, bars.full + 8u * slot);
           if (++slot == stages) {
             slot = 0;
             par ^= 1u;
@@ -437,8 +456,8 @@ __device__ __noinline__ void producer_loop(const Params& p, int pos, uint32_t ri
 
 // ------------------------------------------------------------------------------------------------ epilogue warp
 // Per strip: sum the 16 consumer warps' partials, recombine the limbs, apply the row scale, publish.
-__device__ __noinline__ void epilogue_loop(const Params& p, int pos, uint32_t step, uint32_t red_u, uint32_t bar0,
-                                           const float* row_scale) {
+__device__ __noinline__ void epilogue_loop(int pos, uint32_t step, uint32_t red_u, uint32_t bar0, const float* row_scale) {
+  const Params& p = sparams();
   const int lane = threadIdx.x & 31;
   const int g = lane >> 2, c = lane & 3;
   const int b = blockIdx.x, n_cta = p.n_cta, n_phases = p.n_phases;
@@ -649,9 +668,10 @@ __device__ __forceinline__ float finish_stats(const float* part, int lane, int w
 // add == bf16(h + d) exactly), then RMSNorm.forward (model.py:498-503): bf16(bf16(h * rsqrt(mean(h^2) + eps)) * w).
 // The norm weights are requested BEFORE the wait (a DRAM miss, once per token).  NCH = chunks of 8 per thread (K <= 4096 NCH).
 template <int G, int NCH>
-__device__ __noinline__ void stage_h(const Params& p, int n_chunks, uint32_t in_off, const __nv_bfloat16* norm_w_p, float inv_k,
+__device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_bfloat16* norm_w_p, float inv_k,
                                      int i, uint32_t tag_in, uint64_t cnt_target, float* row_scale_slot, uint32_t x_u,
                                      uint32_t S_u, uint4* h_s, float* part) {
+  const Params& p = sparams();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t limb_row = (uint32_t)n_chunks * 8u + 32u;
   const uint64_t* in_pk = in_off == kNone ? nullptr : p.xchg[p.rank] + in_off;
@@ -743,8 +763,9 @@ __device__ __noinline__ void stage_h(const Params& p, int n_chunks, uint32_t in_
 
 // IN_PK: the packets of the previous phase as they are.  The thread keeps its chunks in registers between the two passes.
 template <int G, int NCH>
-__device__ __noinline__ void stage_x(const Params& p, int n_chunks, uint32_t in_off, int i, uint32_t tag_in, uint64_t cnt_target,
+__device__ __noinline__ void stage_x(int n_chunks, uint32_t in_off, int i, uint32_t tag_in, uint64_t cnt_target,
                                      float* row_scale_slot, uint32_t x_u, uint32_t S_u, float* part) {
+  const Params& p = sparams();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t limb_row = (uint32_t)n_chunks * 8u + 32u;
   const uint64_t* in_pk = p.xchg[p.rank] + in_off;
@@ -838,7 +859,7 @@ __device__ __noinline__ uint32_t gemv_main(uint32_t ring_u, uint32_t bar0, int s
                                            uint32_t limb_row, uint32_t S_u, uint32_t red_u, uint32_t state, uint32_t li,
                                            int dbg) {
   using GE = Geom<G>;
-  constexpr int kStageBytes = GE::kStageBytes;
+  constexpr int kStageBytes = GE::kSlotBytes;
   constexpr int NS = GE::kNSeg;
   constexpr uint32_t kSOff = (kStageTiles * 64 / GE::kSegK) * 32u;  // S_s bytes per stage
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -924,30 +945,59 @@ __device__ __noinline__ uint32_t gemv_main(uint32_t ring_u, uint32_t bar0, int s
 }
 
 // ------------------------------------------------------------------------------------------------ consumers: attention
-// Attention.forward for the new token (model.py:405-440).  One (kv head, range of 32-position tiles) per CTA; the GQ q
-// heads of the group share every K / V row.  The K / V rows arrive through the weight ring (the producer requested them
-// long before q existed), 32 positions per stage: warp w takes positions 2 w, 2 w + 1 of the tile — 16 lanes x 8 dims per
-// position for q.K, 32 lanes x 4 dims for P.V — and keeps its own online-softmax state per head; the 16 warps are merged
-// through shared memory, the splits of a long sequence through {fp32 | tag} packets gathered by split 0.
-// The new token's k (roped) and v come out of the qkv packets: the CTA that owns the last tile appends them to the cache
-// (for the next launches) and patches them into its copy of the tile.  q dims are stored permuted (qidx) so that the 16
-// lanes of a position read 256 contiguous bytes per load.
-__device__ __forceinline__ int qidx(int d) { return (d & 4) ? 64 + ((d >> 3) << 2) + (d & 3) : ((d >> 3) << 2) + (d & 3); }
+// Attention.forward for the new token (model.py:405-440) on the tensor cores.  One (kv head, range of 32-position tiles)
+// per CTA; the GQ q heads of the group are the M rows of the MMAs (padded to 16), so every K / V row is read once for
+// all of them.  The K / V rows arrive through the weight ring out of the kernel's padded cache (the producer requested
+// them long before q existed); ONE WARP walks one tile:
+//     S^T = K Q^T     16 x mma.m16n8k16 (bf16, fp32 accumulate): positions are the M rows (K fragments by ldmatrix.x4 out of
+//                     272-byte rows: no bank conflicts), the GQ <= 8 heads the N columns — no accumulator is wasted
+//     online softmax  on the accumulator fragments (a lane holds 4 positions x 2 heads: 3 shuffles per reduction)
+//     P^T -> B frags  movmatrix (register transpose of the 8x8 blocks), P rounded to bf16 like the reference's softmax output
+//     O^T += V^T P^T  16 x mma.m16n8k16: dims are the M rows, V^T fragments by ldmatrix.x4.trans
+// about 150 instructions per tile against 4000 for the first version (fp32 FMAs + shuffle reductions: 1 us per 32
+// positions of every layer's critical path).  Up to 8 tiles are walked concurrently; the warps' (m, l, O) are merged through
+// shared memory, the splits of a long sequence through {fp32 | tag} packets gathered by split 0.
+// The new token's k (roped) and v come out of the qkv packets: the CTA that owns the last tile appends them to both
+// caches (for the next launches) and patches them into its copy of the tile.
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+// D(16x8, fp32) += A(16x16, bf16, row) * B(16x8, bf16, col)
+__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// transpose of an 8x8 bf16 matrix held one row-pair per lane (lane (g, c): row g, columns 2c, 2c + 1)
+__device__ __forceinline__ uint32_t movmatrix_t(uint32_t a) {
+  uint32_t d;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
 
 template <int GQ>
-__device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16* k_cache, __nv_bfloat16* v_cache, uint32_t in_off,
-                                                 uint32_t out_off, uint32_t aux_off, int i, int pos, uint32_t tag_in,
-                                                 uint64_t cnt_target, uint32_t ring_u, uint32_t stage_bytes, uint32_t bar0,
-                                                 uint8_t* x_s, uint32_t state) {
+__device__ __noinline__ uint32_t attention_phase(__nv_bfloat16* k_cache, __nv_bfloat16* v_cache, __nv_bfloat16* k_pad,
+                                                 __nv_bfloat16* v_pad, uint32_t in_off, uint32_t out_off, uint32_t aux_off, int i,
+                                                 int pos, uint32_t tag_in, uint64_t cnt_target, uint32_t ring_u,
+                                                 uint32_t slot_bytes, uint32_t bar0, uint8_t* x_s, uint32_t state) {
+  const Params& p = sparams();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x, n_phases = p.n_phases;
   const int H = p.H, Hkv = p.Hkv, S = p.S;
-  const Bars bars = make_bars(bar0, p.stages);
+  const int stages = p.stages;
+  const Bars bars = make_bars(bar0, stages);
   const AttnPart a = attn_partition(pos, S, Hkv, p.attn_spc, p.attn_max_split, b);
   uint64_t* xq = p.xchg[p.rank];
   const uint32_t tag_out = tag_in + 1u;
-  float* q_s = reinterpret_cast<float*>(x_s);                      // [GQ][128] fp32 (scaled, dims permuted)
-  uint32_t* kv_new = reinterpret_cast<uint32_t*>(q_s + GQ * 128);  // [2][64] bf16x2: roped k, v of the new token
+  // scratch in the limb region
+  uint32_t* q_s = reinterpret_cast<uint32_t*>(x_s);                // [GQ][68] bf16x2: roped q, rows of 272 B
+  uint32_t* kv_new = q_s + 8 * (kKvPitch / 2);                     // [2][64] bf16x2: roped k, v of the new token
   float* part_s = reinterpret_cast<float*>(kv_new + 128);          // [16 warps][GQ][kPartStride]
   constexpr int kItems = (GQ + 2) * 64;                            // (q heads, k, v) x 64 pairs
   constexpr int kIt = (kItems + kCT - 1) / kCT;
@@ -974,8 +1024,6 @@ __device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16*
     return state;
   }
   const bool owner = a.split == a.nsplit - 1 && pos < S;
-  __nv_bfloat16* kc = k_cache + (int64_t)a.kvh * S * 128;
-  __nv_bfloat16* vc = v_cache + (int64_t)a.kvh * S * 128;
   {
     const uint64_t* qkv = xq + in_off;
 #pragma unroll
@@ -986,19 +1034,20 @@ __device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16*
         const int elem = which < GQ ? (a.kvh * GQ + which) * 128 : (which == GQ ? (H + a.kvh) * 128 : (H + Hkv + a.kvh) * 128);
         const uint32_t raw = poll_pk(qkv + (elem >> 1) + pr, tag_in);
         uint32_t o = raw;
-        float r0 = 0.f, r1 = 0.f;
         if (which <= GQ) {  // RoPE, model.py:547-559: fp32 math on bf16 cos / sin, rounded to bf16
           const float x0 = __uint_as_float(raw << 16), x1 = __uint_as_float(raw & 0xFFFF0000u);
           const float cc = __uint_as_float(cs[it] << 16), sn = __uint_as_float(cs[it] & 0xFFFF0000u);
-          r0 = bf16r(x0 * cc - x1 * sn);
-          r1 = bf16r(x1 * cc + x0 * sn);
-          o = float_to_bf16_bits(r0) | (float_to_bf16_bits(r1) << 16);
+          o = cvt_bf2(x0 * cc - x1 * sn, x1 * cc + x0 * sn);
         }
         if (which < GQ) {
-          *reinterpret_cast<float2*>(q_s + which * 128 + qidx(2 * pr)) = make_float2(r0 * p.attn_scale, r1 * p.attn_scale);
+          q_s[which * (kKvPitch / 2) + pr] = o;
         } else {
           kv_new[(which - GQ) * 64 + pr] = o;
-          if (owner) *reinterpret_cast<uint32_t*>((which == GQ ? kc : vc) + (int64_t)pos * 128 + 2 * pr) = o;  // KVCache.update
+          if (owner) {  // KVCache.update (model.py:175-192) + the kernel's padded copy
+            const bool is_k = which == GQ;
+            *reinterpret_cast<uint32_t*>((is_k ? k_cache : v_cache) + ((int64_t)a.kvh * S + pos) * 128 + 2 * pr) = o;
+            *reinterpret_cast<uint32_t*>((is_k ? k_pad : v_pad) + ((int64_t)a.kvh * p.S_pad + pos) * kKvPitch + 2 * pr) = o;
+          }
         }
       }
     }
@@ -1008,77 +1057,155 @@ __device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16*
 
   int slot = (int)(state & 0xffu);
   uint32_t par = state >> 8;
-  float m[GQ], l[GQ], acc[GQ][4];
+  const int g = lane >> 2, c = lane & 3;
+  const float scale = p.attn_scale;
+  // this lane's slice of the state: heads 2 c, 2 c + 1 (columns of the accumulators); rows = dims 16 dm + g, + 8
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+  float Ot[8][4];
 #pragma unroll
-  for (int h = 0; h < GQ; ++h) {
-    m[h] = -INFINITY;
-    l[h] = 0.f;
-    acc[h][0] = acc[h][1] = acc[h][2] = acc[h][3] = 0.f;
-  }
-  const int half = lane >> 4, ds = lane & 15;
-  const uint32_t q_u = smem_u32(q_s) + (uint32_t)ds * 16u;
-  for (int t = a.t0; t < a.t1; ++t) {
-    const uint32_t stage_u = ring_u + (uint32_t)slot * stage_bytes;
-    bar_wait(bars.full + 8u * slot, par, 32u);
-    if (owner && t == a.n_t - 1) {  // CTA-uniform: the tile that holds the new position
-      const int row = pos - t * kAttnPos;
-      if (tid < 128) sts32(stage_u + (uint32_t)(tid >> 6) * 8192u + (uint32_t)row * 256u + (uint32_t)(tid & 63) * 4u, kv_new[tid]);
+  for (int dm = 0; dm < 8; ++dm) Ot[dm][0] = Ot[dm][1] = Ot[dm][2] = Ot[dm][3] = 0.f;
+  const int round_max = min(kAttnRound, stages - 1);
+  // ldmatrix row addresses of this lane: matrix mi = lane >> 3, row r8 = lane & 7
+  const int mi = lane >> 3, r8 = lane & 7;
+  // K (A operand, row = position): matrices (rows 0-7 | 8-15) x (dims 0-7 | 8-15) in the order a0..a3
+  const uint32_t k_lane = (uint32_t)(8 * (mi & 1) + r8) * (kKvPitch * 2) + (uint32_t)(mi >> 1) * 16u;   // + tile + 16 mt rows + 32 ks bytes
+  // V^T (A operand, row = dim): stored blocks (positions 0-7 | 8-15 -> a0/a1 vs a2/a3) x (dims 0-7 | 8-15)
+  const uint32_t v_lane = (uint32_t)kKvTileBytes + (uint32_t)(8 * (mi >> 1) + r8) * (kKvPitch * 2) + (uint32_t)(mi & 1) * 16u;
+  const uint32_t q_lane = smem_u32(q_s) + (uint32_t)g * (kKvPitch * 2) + (uint32_t)c * 4u;  // Q^T (B operand): head g, dims 2 c, + 1
+
+  for (int tb = a.t0; tb < a.t1; tb += round_max) {
+    const int R = min(round_max, a.t1 - tb);
+    {
+      int sl = slot;
+      uint32_t pr = par;
+      for (int r = 0; r < R; ++r) {  // every warp waits for every tile of the round (the patch below needs a CTA barrier)
+        bar_wait(bars.full + 8u * sl, pr, 32u);
+        if (++sl == stages) {
+          sl = 0;
+          pr ^= 1u;
+        }
+      }
+    }
+    if (owner && a.n_t - 1 < tb + R) {  // CTA-uniform: the round holds the tile of the new position (always the last one)
+      int sl = slot + (a.n_t - 1 - tb);
+      if (sl >= stages) sl -= stages;
+      const uint32_t stage_u = ring_u + (uint32_t)sl * slot_bytes;
+      const int row = pos - (a.n_t - 1) * kAttnPos;
+      if (tid < 128)
+        sts32(stage_u + (uint32_t)(tid >> 6) * kKvTileBytes + (uint32_t)row * (kKvPitch * 2) + (uint32_t)(tid & 63) * 4u, kv_new[tid]);
       fence_proxy_async();  // generic writes into a buffer the bulk-copy engine will overwrite later
       named_bar_sync(1, kCT);
     }
-    const int j0 = t * kAttnPos + 2 * warp;
-    const bool valid = j0 + half < a.len;
-    float kf[8];
-    unpack8(lds128(stage_u + (uint32_t)(2 * warp + half) * 256u + (uint32_t)ds * 16u), kf);
-    float sc[GQ];
+    if (tid == 0 && tb == a.t0) stamp(p.trace, n_phases, i, 6);  // the first round's tiles are in shared memory
+    if (warp < R) {
+      int sl = slot + warp;
+      if (sl >= stages) sl -= stages;
+      const uint32_t stage_u = ring_u + (uint32_t)sl * slot_bytes;
+      const int jt = (tb + warp) * kAttnPos;
+      // ---- S^T = K Q^T: 2 blocks of 16 positions x 8 k-steps of 16 dims
+      float st[2][4];
 #pragma unroll
-    for (int h = 0; h < GQ; ++h) {
-      const uint4 qa = lds128(q_u + (uint32_t)h * 512u), qb = lds128(q_u + (uint32_t)h * 512u + 256u);
-      float s = __uint_as_float(qa.x) * kf[0] + __uint_as_float(qa.y) * kf[1] + __uint_as_float(qa.z) * kf[2] +
-                __uint_as_float(qa.w) * kf[3] + __uint_as_float(qb.x) * kf[4] + __uint_as_float(qb.y) * kf[5] +
-                __uint_as_float(qb.z) * kf[6] + __uint_as_float(qb.w) * kf[7];
+      for (int mt = 0; mt < 2; ++mt) st[mt][0] = st[mt][1] = st[mt][2] = st[mt][3] = 0.f;
 #pragma unroll
-      for (int o = 8; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      sc[h] = valid ? s : -INFINITY;
+      for (int ks = 0; ks < 8; ++ks) {
+        const uint32_t qb0 = g < GQ ? lds32(q_lane + 32u * ks) : 0u, qb1 = g < GQ ? lds32(q_lane + 32u * ks + 16u) : 0u;
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          uint32_t ka[4];
+          ldsm_x4(ka, stage_u + k_lane + (uint32_t)(16 * mt) * (kKvPitch * 2) + 32u * ks);
+          mma_bf16(st[mt], ka, qb0, qb1);
+        }
+      }
+      // ---- online softmax: this lane holds positions g, g + 8, g + 16, g + 24 of the tile for heads 2 c, 2 c + 1
+      float corr[2];
+      uint32_t pk[2][2];  // P^T blocks (8 positions x 8 heads) as bf16x2 (heads 2c | 2c + 1): [16-position block][first | second 8]
+      {
+        float mt2[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const bool ok = jt + 16 * mt + 8 * hf + g < a.len;
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              st[mt][2 * hf + e] = ok ? st[mt][2 * hf + e] * scale : -INFINITY;
+              mt2[e] = fmaxf(mt2[e], st[mt][2 * hf + e]);
+            }
+          }
+        }
+        float m_use[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          mt2[e] = fmaxf(mt2[e], __shfl_xor_sync(0xffffffffu, mt2[e], 4));
+          mt2[e] = fmaxf(mt2[e], __shfl_xor_sync(0xffffffffu, mt2[e], 8));
+          mt2[e] = fmaxf(mt2[e], __shfl_xor_sync(0xffffffffu, mt2[e], 16));
+          const float m_new = fmaxf(m_run[e], mt2[e]);
+          m_use[e] = m_new == -INFINITY ? 0.f : m_new;
+          corr[e] = __expf(m_run[e] - m_use[e]);
+          m_run[e] = m_new;
+        }
+        float ls[2] = {0.f, 0.f};
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            // exp(-inf) = 0 past the sequence; rounded to bf16 like softmax(...).to(bf16) @ V, and the row sum uses the
+            // ROUNDED probabilities so that the weights and their normaliser agree
+            const uint32_t w = cvt_bf2(__expf(st[mt][2 * hf] - m_use[0]), __expf(st[mt][2 * hf + 1] - m_use[1]));
+            pk[mt][hf] = w;
+            ls[0] += __uint_as_float(w << 16);
+            ls[1] += __uint_as_float(w & 0xFFFF0000u);
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          ls[e] += __shfl_xor_sync(0xffffffffu, ls[e], 4);
+          ls[e] += __shfl_xor_sync(0xffffffffu, ls[e], 8);
+          ls[e] += __shfl_xor_sync(0xffffffffu, ls[e], 16);
+          l_run[e] = l_run[e] * corr[e] + ls[e];
+        }
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        Ot[dm][0] *= corr[0]; Ot[dm][2] *= corr[0];
+        Ot[dm][1] *= corr[1]; Ot[dm][3] *= corr[1];
+      }
+      // ---- O^T += V^T P^T: 8 blocks of 16 dims x 2 k-steps of 16 positions
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) {
+        const uint32_t pb0 = movmatrix_t(pk[ks][0]), pb1 = movmatrix_t(pk[ks][1]);  // lane (g, c): head g, positions 2c, 2c + 1
+#pragma unroll
+        for (int dm = 0; dm < 8; ++dm) {
+          uint32_t va[4];
+          ldsm_x4_t(va, stage_u + v_lane + (uint32_t)(16 * ks) * (kKvPitch * 2) + 32u * dm);
+          mma_bf16(Ot[dm], va, pb0, pb1);
+        }
+      }
     }
-    uint2 v0 = lds64u(stage_u + 8192u + (uint32_t)(2 * warp) * 256u + (uint32_t)lane * 8u);
-    uint2 v1 = lds64u(stage_u + 8192u + (uint32_t)(2 * warp + 1) * 256u + (uint32_t)lane * 8u);
-    if (j0 >= a.len) v0 = make_uint2(0u, 0u);      // rows past the sequence hold stale bytes: keep them out of 0 * x
-    if (j0 + 1 >= a.len) v1 = make_uint2(0u, 0u);
     __syncwarp();
-    if (lane == 0) bar_arrive(bars.empty + 8u * slot);
-    if (++slot == p.stages) {
-      slot = 0;
-      par ^= 1u;
-    }
-    const float v00 = __uint_as_float(v0.x << 16), v01 = __uint_as_float(v0.x & 0xFFFF0000u);
-    const float v02 = __uint_as_float(v0.y << 16), v03 = __uint_as_float(v0.y & 0xFFFF0000u);
-    const float v10 = __uint_as_float(v1.x << 16), v11 = __uint_as_float(v1.x & 0xFFFF0000u);
-    const float v12 = __uint_as_float(v1.y << 16), v13 = __uint_as_float(v1.y & 0xFFFF0000u);
-#pragma unroll
-    for (int h = 0; h < GQ; ++h) {
-      const float mb = fmaxf(sc[h], __shfl_xor_sync(0xffffffffu, sc[h], 16));
-      const float m_new = fmaxf(m[h], mb);
-      const float m_use = m_new == -INFINITY ? 0.f : m_new;
-      const float corr = __expf(m[h] - m_use);
-      const float pm = valid ? __expf(sc[h] - m_use) : 0.f;
-      const float p0 = __shfl_sync(0xffffffffu, pm, 0), p1 = __shfl_sync(0xffffffffu, pm, 16);
-      l[h] = l[h] * corr + p0 + p1;
-      acc[h][0] = acc[h][0] * corr + p0 * v00 + p1 * v10;
-      acc[h][1] = acc[h][1] * corr + p0 * v01 + p1 * v11;
-      acc[h][2] = acc[h][2] * corr + p0 * v02 + p1 * v12;
-      acc[h][3] = acc[h][3] * corr + p0 * v03 + p1 * v13;
-      m[h] = m_new;
+    for (int r = 0; r < R; ++r) {  // every warp releases every slot of the round
+      if (lane == 0) bar_arrive(bars.empty + 8u * slot);
+      if (++slot == stages) {
+        slot = 0;
+        par ^= 1u;
+      }
     }
   }
   if (tid == 0) stamp(p.trace, n_phases, i, 3);
 #pragma unroll
-  for (int h = 0; h < GQ; ++h) {
-    float* pp = part_s + (warp * GQ + h) * kPartStride;
-    *reinterpret_cast<float4*>(pp + lane * 4) = make_float4(acc[h][0], acc[h][1], acc[h][2], acc[h][3]);
-    if (lane == 0) {
-      pp[128] = m[h];
-      pp[129] = l[h];
+  for (int e = 0; e < 2; ++e) {
+    const int h = 2 * c + e;
+    if (h < GQ) {
+      float* pp = part_s + (warp * GQ + h) * kPartStride;
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        pp[16 * dm + g] = Ot[dm][e];
+        pp[16 * dm + g + 8] = Ot[dm][2 + e];
+      }
+      if (g == 0) {
+        pp[128] = m_run[e];
+        pp[129] = l_run[e];
+      }
     }
   }
   named_bar_sync(1, kCT);
@@ -1130,11 +1257,9 @@ __device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16*
     }
     if (a.split == 0) {
       const float inv = 1.f / ll;
-      const uint32_t o0 = float_to_bf16_bits(o4[0] * inv) | (float_to_bf16_bits(o4[1] * inv) << 16);
-      const uint32_t o1 = float_to_bf16_bits(o4[2] * inv) | (float_to_bf16_bits(o4[3] * inv) << 16);
       uint64_t* dst = xq + out_off + ((head * 128 + lane * 4) >> 1);
-      st_pk(dst, o0, tag_out);
-      st_pk(dst + 1, o1, tag_out);
+      st_pk(dst, cvt_bf2(o4[0] * inv, o4[1] * inv), tag_out);
+      st_pk(dst + 1, cvt_bf2(o4[2] * inv, o4[3] * inv), tag_out);
     }
   }
   if (tid == 0) {
@@ -1146,25 +1271,31 @@ __device__ __noinline__ uint32_t attention_phase(const Params& p, __nv_bfloat16*
 
 // ------------------------------------------------------------------------------------------------ the kernel
 template <int G>
-__global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Params p_arg) {
   using GE = Geom<G>;
-  constexpr int kStageBytes = GE::kStageBytes;
+  constexpr int kStageBytes = GE::kSlotBytes;
   extern __shared__ __align__(128) uint8_t smem_mega[];
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&p_arg);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem_mega + 64);
+    for (int k = threadIdx.x; k < (int)(sizeof(Params) / 4); k += kThreads) dst[k] = src[k];
+  }
+  const Params& p = sparams();  // valid after the __syncthreads below; until then only p_arg is used
   uint8_t* ring = smem_mega + kHdrBytes;
-  uint8_t* x_s = smem_mega + p.off_x;                              // limbs [3][Kp + 32] int8 / attention scratch
-  float* S_s = reinterpret_cast<float*>(smem_mega + p.off_S);      // [Kp / kSegK][8]: limb sums per segment
-  uint4* h_s = reinterpret_cast<uint4*>(smem_mega + p.off_h);      // residual stream, bf16 [dim]
-  float* part = reinterpret_cast<float*>(smem_mega + p.off_misc);  // [16 warps][2]: {sum sq, max |.| bits}
+  uint8_t* x_s = smem_mega + p_arg.off_x;                              // limbs [3][Kp + 32] int8 / attention scratch
+  float* S_s = reinterpret_cast<float*>(smem_mega + p_arg.off_S);      // [Kp / kSegK][8]: limb sums per segment
+  uint4* h_s = reinterpret_cast<uint4*>(smem_mega + p_arg.off_h);      // residual stream, bf16 [dim]
+  float* part = reinterpret_cast<float*>(smem_mega + p_arg.off_misc);  // [16 warps][2]: {sum sq, max |.| bits}
   float* row_scale = part + 2 * kC;                                // [2] (GEMV-phase parity)
   uint64_t* bar_p = reinterpret_cast<uint64_t*>(row_scale + 4);    // full[stages], empty[stages], red_full[2], red_free[2]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.x, n_cta = p.n_cta;
-  const int stages = p.stages, n_phases = p.n_phases;
+  const int b = blockIdx.x, n_cta = p_arg.n_cta;
+  const int stages = p_arg.stages, n_phases = p_arg.n_phases;
   {
-    const uint4* src = reinterpret_cast<const uint4*>(p.layers);
-    uint4* dst = reinterpret_cast<uint4*>(smem_mega + p.off_lay);
-    for (int k = tid; k < p.n_layer * (int)(sizeof(LayerPtrs) / 16); k += kThreads) dst[k] = __ldg(src + k);
+    const uint4* src = reinterpret_cast<const uint4*>(p_arg.layers);
+    uint4* dst = reinterpret_cast<uint4*>(smem_mega + p_arg.off_lay);
+    for (int k = tid; k < p_arg.n_layer * (int)(sizeof(LayerPtrs) / 16); k += kThreads) dst[k] = __ldg(src + k);
   }
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -1177,22 +1308,22 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
     }
     SCtx* c = sctx();
     c->abort = 0u;
-    c->status = p.status;
-    c->timeout_ns = p.timeout_ns;
+    c->status = p_arg.status;
+    c->timeout_ns = p_arg.timeout_ns;
     fence_barrier_init();
   }
   __syncthreads();
 
-  const uint32_t step = *reinterpret_cast<volatile uint32_t*>(p.step);
-  const int pos = *reinterpret_cast<volatile int32_t*>(p.pos);
-  const uint32_t ring_u = smem_u32(ring), bar0 = smem_u32(bar_p), red_u = smem_u32(smem_mega + p.off_red);
+  const uint32_t step = *reinterpret_cast<volatile uint32_t*>(p_arg.step);
+  const int pos = *reinterpret_cast<volatile int32_t*>(p_arg.pos);
+  const uint32_t ring_u = smem_u32(ring), bar0 = smem_u32(bar_p), red_u = smem_u32(smem_mega + p_arg.off_red);
 
   if (warp == kC) {
-    if (lane == 0) producer_loop<G>(p, pos, ring_u, bar0);
+    if (lane == 0) producer_loop<G>(pos, ring_u, bar0);
     return;
   }
   if (warp == kC + 1) {
-    epilogue_loop(p, pos, step, red_u, bar0, row_scale);
+    epilogue_loop(pos, step, red_u, bar0, row_scale);
     return;
   }
 
@@ -1216,10 +1347,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
     const uint64_t cnt_target = cnt0 + (uint64_t)i * (uint64_t)n_cta;
     if (ph->type != PH_GEMV) {
       switch (GQ) {
-        case 1: state = attention_phase<1>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        case 2: state = attention_phase<2>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        case 4: state = attention_phase<4>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        default: state = attention_phase<8>(p, ph->k_cache, ph->v_cache, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        case 1: state = attention_phase<1>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        case 2: state = attention_phase<2>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        case 4: state = attention_phase<4>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
+        default: state = attention_phase<8>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
       }
       continue;
     }
@@ -1230,13 +1361,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
       const uint32_t x_u = smem_u32(x_s), S_u = smem_u32(S_s);
       if (ph->in_kind == IN_H) {
         const float inv_k = 1.0f / (float)ph->Kx;
-        if (nch <= 1) stage_h<G, 1>(p, n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
-        else stage_h<G, 2>(p, n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
+        if (nch <= 1) stage_h<G, 1>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
+        else stage_h<G, 2>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
       } else {
-        if (nch <= 1) stage_x<G, 1>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else if (nch <= 2) stage_x<G, 2>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else if (nch <= 4) stage_x<G, 4>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else stage_x<G, 8>(p, n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        if (nch <= 1) stage_x<G, 1>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else if (nch <= 2) stage_x<G, 2>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else if (nch <= 4) stage_x<G, 4>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        else stage_x<G, 8>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
       }
     }
     int s0, s1;
@@ -1265,9 +1396,10 @@ static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static bool plan_smem(int G, int64_t Kmax, int dim, int Gq, int n_layer, SmemPlan& pl) {
   const int seg_k = G < 128 ? G : 128;
-  const size_t stage_bytes = (size_t)kStageW + (size_t)(kStageTiles * 64 / G) * 64;
+  size_t stage_bytes = (size_t)kStageW + (size_t)(kStageTiles * 64 / G) * 64;
+  if (stage_bytes < (size_t)kAttnStageBytes) stage_bytes = kAttnStageBytes;  // a ring slot also holds a K / V tile
   const size_t limbs = (size_t)3 * (size_t)(Kmax + 32);
-  const size_t attn = (size_t)Gq * 128 * 4 + 512 + (size_t)kC * Gq * kPartStride * 4;  // q, new k / v, warp partials
+  const size_t attn = (size_t)8 * kKvPitch * 2 + 512 + (size_t)kC * Gq * kPartStride * 4;  // q, new k / v, warp partials
   const size_t x_bytes = align_up(limbs > attn ? limbs : attn, 128);
   const size_t S_bytes = align_up((size_t)(Kmax / seg_k) * 32, 128);
   const size_t red_bytes = (size_t)kRedBufs * kC * 128 * 4;
@@ -1351,7 +1483,7 @@ extern "C" int ao_b200_decode_mega_setup(const ao_b200_mega_model* m, void* plan
   for (int l = 0; l < m->n_layer; ++l) {
     const ao_b200_mega_layer& L = m->layers[l];
     AO_CHECK_ARG(L.wqkv_packed && L.wqkv_sz && L.wo_packed && L.wo_sz && L.w13_packed && L.w13_sz && L.w2_packed && L.w2_sz);
-    AO_CHECK_ARG(L.attn_norm && L.ffn_norm && L.k_cache && L.v_cache);
+    AO_CHECK_ARG(L.attn_norm && L.ffn_norm && L.k_cache && L.v_cache && L.k_pad && L.v_pad);
     LayerPtrs& q = lp[(size_t)l];
     q.w[0] = static_cast<const uint8_t*>(L.wqkv_packed); q.sz[0] = static_cast<const uint32_t*>(L.wqkv_sz);
     q.w[1] = static_cast<const uint8_t*>(L.wo_packed); q.sz[1] = static_cast<const uint32_t*>(L.wo_sz);
@@ -1359,6 +1491,7 @@ extern "C" int ao_b200_decode_mega_setup(const ao_b200_mega_model* m, void* plan
     q.w[3] = static_cast<const uint8_t*>(L.w2_packed); q.sz[3] = static_cast<const uint32_t*>(L.w2_sz);
     q.norm[0] = static_cast<const __nv_bfloat16*>(L.attn_norm); q.norm[1] = static_cast<const __nv_bfloat16*>(L.ffn_norm);
     q.kc = static_cast<__nv_bfloat16*>(L.k_cache); q.vc = static_cast<__nv_bfloat16*>(L.v_cache);
+    q.kp = static_cast<__nv_bfloat16*>(L.k_pad); q.vp = static_cast<__nv_bfloat16*>(L.v_pad);
   }
   auto s = static_cast<cudaStream_t>(stream);
   if (cudaMemcpyAsync(plan_dev, lp.data(), sizeof(LayerPtrs) * lp.size(), cudaMemcpyHostToDevice, s) != cudaSuccess) return AO_B200_ERR_CUDA;
@@ -1417,7 +1550,8 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   p.step = reinterpret_cast<uint32_t*>(st + 8);
   p.status = reinterpret_cast<uint32_t*>(st + 12);   // [status][slow polls]
   p.dim = m->dim; p.H = m->n_head; p.Hkv = m->n_kv_head; p.S = m->max_seq;
-  p.attn_spc = m->attn_blocks_per_cta > 0 ? m->attn_blocks_per_cta : 4;
+  p.S_pad = (m->max_seq + kAttnPos - 1) / kAttnPos * kAttnPos;
+  p.attn_spc = m->attn_blocks_per_cta > 0 ? m->attn_blocks_per_cta : kAttnRound;
   p.attn_max_split = m->n_cta / m->n_kv_head;
   p.eps = m->eps;
   p.attn_scale = 1.0f / sqrtf((float)m->head_dim);
@@ -1454,11 +1588,28 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = pl.smem;
   cfg.stream = static_cast<cudaStream_t>(stream);
+  // The CTAs wait on one another, so all of them must be resident.  A cooperative launch guarantees it (or fails); a
+  // plain launch of <= (SMs x occupancy) CTAs gets there too as soon as whatever else runs on the GPU drains, and every
+  // wait in the kernel is bounded — AO_B200_MEGA_COOP=0 selects it (a cooperative kernel node costs the serving loop
+  // extra launch latency per token: profiles/).  The grid is checked against the occupancy either way.
+  static const bool coop = []() { const char* e = std::getenv("AO_B200_MEGA_COOP"); return e ? std::atoi(e) != 0 : true; }();
+  static int max_ctas[4] = {0, 0, 0, 0};
+  if (max_ctas[gi] == 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, pl.smem) != cudaSuccess) per_sm = 0;
+    max_ctas[gi] = sms * per_sm;
+  }
+  if (m->n_cta > max_ctas[gi]) {
+    if (debug) fprintf(stderr, "ao_b200_decode_mega_step: %d CTAs cannot be co-resident (limit %d)\n", m->n_cta, max_ctas[gi]);
+    return AO_B200_ERR_UNSUPPORTED;
+  }
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident or the launch fails: the CTAs wait on one another
+  attr[0].id = cudaLaunchAttributeCooperative;
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = coop ? 1 : 0;
   const cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p);
   if (le != cudaSuccess) {
     if (debug) fprintf(stderr, "ao_b200_decode_mega_step: launch (grid %d, smem %zu, stages %d): %s\n", m->n_cta, pl.smem, pl.stages, cudaGetErrorString(le));
