@@ -24,9 +24,9 @@ from ...dtypes.layouts import PlainAQTTensorImpl, TensorCoreTiledAQTTensorImpl
 from .model import Transformer
 
 
-# persistent one-launch-per-token kernel (csrc/decode_mega.cu) as the batch-1 int4 default: "1" once it beats the
-# per-projection graph on the bench (profiles/), AO_B200_MEGA overrides
-MEGA_DEFAULT = "0"
+# persistent one-launch-per-token kernel (csrc/decode_mega.cu) is the batch-1 int4 default (it beats the per-projection
+# graph of 161 launches: profiles/r02_*); AO_B200_MEGA=0 selects the per-projection graph
+MEGA_DEFAULT = "1"
 
 
 def _ptr(t: Optional[torch.Tensor]):

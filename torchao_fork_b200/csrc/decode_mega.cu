@@ -87,6 +87,7 @@ struct Kind {
   uint32_t aux_off;               // ATTN: split partials
   int type, in_kind, out_kind;
   int KT, n_strips, N_out, Kx, rot_inc;
+  int gate;                       // arrivals the sweep of this phase does not wait for (their packets are polled directly)
 };
 // a phase as the roles see it (registers)
 struct Phase {
@@ -100,7 +101,7 @@ struct Phase {
   __nv_bfloat16* v_pad;
   uint32_t in_off, out_off, aux_off;
   int type, in_kind, out_kind;
-  int KT, n_strips, N_out, Kx, rot_inc;
+  int KT, n_strips, N_out, Kx, rot_inc, gate;
 };
 
 struct Params {
@@ -126,7 +127,7 @@ struct Params {
   uint32_t off_x, off_S, off_red, off_h, off_misc, off_lay;
   unsigned long long timeout_ns;
   unsigned long long* trace;      // optional: [n_cta][n_phases][8] clock64 stamps (benchmarks/mega_trace.py)
-  int dbg;                        // profiling switches (AO_B200_MEGA_DEBUG): 1 = main loops skip the math (stream only)
+  int dbg;                        // profiling switches (AO_B200_MEGA_DEBUG): 1 = main loops skip the math (stream only), 2 = count slow polls
 };
 
 // wait context at the start of dynamic shared memory: reachable from every (non-inlined) function without arguments
@@ -271,7 +272,7 @@ __device__ __noinline__ void wait_counter(const uint64_t* ctr, uint64_t target) 
 }
 // one packet
 __device__ __noinline__ uint32_t poll_pk_slow(const uint64_t* p, uint32_t tag) {
-  atomicAdd(sctx()->status + 1, 1u);  // statistics: how often a sweep ran ahead of its packets (state word 4)
+  if (sparams().dbg & 2) atomicAdd(sctx()->status + 1, 1u);  // statistics: how often a poll ran ahead of its packet (state word 4)
   const unsigned long long t0 = globaltimer();
   const unsigned long long lim = sctx()->timeout_ns;
   uint32_t n = 0;
@@ -292,20 +293,39 @@ __device__ __forceinline__ uint32_t poll_pk(const uint64_t* p, uint32_t tag) {
   if ((uint32_t)(v >> 32) == tag) return (uint32_t)v;
   return poll_pk_slow(p, tag);
 }
-// 4 consecutive packets (8 bf16 = one staging chunk); p is 32-byte aligned
+// 4 consecutive packets (8 bf16 = one staging chunk); p is 32-byte aligned.  The slow path is the normal way in for the
+// last arrivals of a phase: the arrival counter only gates the sweep ("almost everybody has published"), the tags decide.
+__device__ __noinline__ uint4 poll_chunk_slow(const uint64_t* p, uint32_t tag) {
+  if (sparams().dbg & 2) atomicAdd(sctx()->status + 1, 1u);  // statistics (AO_B200_MEGA_DEBUG=2): sweeps that ran ahead
+  const unsigned long long t0 = globaltimer();
+  const unsigned long long lim = sctx()->timeout_ns;
+  uint32_t n = 0;
+  for (;;) {
+    const ulonglong2 a = ld_pk2(p), b = ld_pk2(p + 2);
+    if (((uint32_t)(a.x >> 32) == tag) & ((uint32_t)(a.y >> 32) == tag) & ((uint32_t)(b.x >> 32) == tag) &
+        ((uint32_t)(b.y >> 32) == tag))
+      return make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
+    if ((++n & 63u) == 0) {
+      if (aborted()) break;
+      if (globaltimer() - t0 > lim) {
+        raise_abort(4u);
+        break;
+      }
+    }
+  }
+  return make_uint4(0u, 0u, 0u, 0u);
+}
 __device__ __forceinline__ uint4 poll_chunk(const uint64_t* p, uint32_t tag) {
   const ulonglong2 a = ld_pk2(p), b = ld_pk2(p + 2);
-  uint4 r = make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
   const bool ok = ((uint32_t)(a.x >> 32) == tag) & ((uint32_t)(a.y >> 32) == tag) & ((uint32_t)(b.x >> 32) == tag) &
                   ((uint32_t)(b.y >> 32) == tag);
-  if (!ok) {
-    r.x = poll_pk_slow(p, tag);
-    r.y = poll_pk_slow(p + 1, tag);
-    r.z = poll_pk_slow(p + 2, tag);
-    r.w = poll_pk_slow(p + 3, tag);
-  }
-  return r;
+  if (ok) return make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
+  return poll_chunk_slow(p, tag);
 }
+// Staging chunk of (round c, lane, warp): the chunks a warp stages are exactly the ones its main loop reads (warp w owns
+// k in [2048 s + 128 w, + 128) of every stage s: chunks 256 s + 16 w + 0..15), lanes 0-15 take stage 2 c, lanes 16-31
+// stage 2 c + 1 — so the limbs need no CTA barrier before the main loop, only a __syncwarp.
+__device__ __forceinline__ int stage_chunk(int c, int lane, int warp) { return 256 * (2 * c + (lane >> 4)) + 16 * warp + (lane & 15); }
 
 __device__ __forceinline__ void strip_range(int b, int n_cta, int n_strips, int rot, int& s0, int& s1) {
   int bb = b + rot;
@@ -370,7 +390,7 @@ __device__ __forceinline__ Phase get_phase(const Params& p, int i) {
   ph.in_off = (i == 0) ? kNone : k.in_off;   // the first projection of the token has no delta to add
   ph.out_off = k.out_off; ph.aux_off = k.aux_off;
   ph.type = k.type; ph.in_kind = k.in_kind; ph.out_kind = k.out_kind;
-  ph.KT = k.KT; ph.n_strips = k.n_strips; ph.N_out = k.N_out; ph.Kx = k.Kx; ph.rot_inc = k.rot_inc;
+  ph.KT = k.KT; ph.n_strips = k.n_strips; ph.N_out = k.N_out; ph.Kx = k.Kx; ph.rot_inc = k.rot_inc; ph.gate = k.gate;
   ph.packed = nullptr; ph.sz = nullptr; ph.norm_w = nullptr; ph.out_plain = nullptr; ph.k_cache = nullptr; ph.v_cache = nullptr;
   ph.k_pad = nullptr; ph.v_pad = nullptr;
   if (kind == K_OUT) {
@@ -659,8 +679,9 @@ __device__ __forceinline__ float finish_stats(const float* part, int lane, int w
   int e = 0;
   if (bound > 0.f) e = 21 - ((int)((__float_as_uint(bound) >> 23) & 0xFF) - 127);
   e = max(-106, min(100, e));
-  if (warp == 0 && lane == 0)
-    *row_scale_slot = bad ? __uint_as_float(0x7fc00000u) : __uint_as_float((uint32_t)(127 - e) << 23);
+  // every warp publishes the (identical) row scale itself: the epilogue warp reads it after ANY warp's first hand-over
+  // of the phase, and only a warp's own stores are ordered before its own mbarrier arrive
+  if (lane == 0) *row_scale_slot = bad ? __uint_as_float(0x7fc00000u) : __uint_as_float((uint32_t)(127 - e) << 23);
   return __uint_as_float((uint32_t)(e + 127) << 23);
 }
 
@@ -680,7 +701,7 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
   uint4 wn[NCH], hv[NCH];
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int ci = c * kCT + tid;
+    const int ci = stage_chunk(c, lane, warp);
     wn[c] = ci < n_chunks ? __ldg(norm_w + ci) : make_uint4(0u, 0u, 0u, 0u);
     hv[c] = make_uint4(0u, 0u, 0u, 0u);
   }
@@ -694,7 +715,7 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
   uint32_t am2 = 0u;  // packed max |bf16(h w)|
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int ci = c * kCT + tid;
+    const int ci = stage_chunk(c, lane, warp);
     if (ci < n_chunks) {
       uint4 h = h_s[ci];
       if (in_pk != nullptr) {
@@ -745,8 +766,8 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
   const float up = finish_stats(part, lane, warp, true, inv_k, p.eps, row_scale_slot, rnorm);
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int ci = c * kCT + tid;
-    if (NCH == 1 || c * kCT < n_chunks) {  // warp-uniform: some chunk of this round exists
+    const int ci = stage_chunk(c, lane, warp);
+    if (NCH == 1 || 512 * c < n_chunks) {  // warp-uniform: stage 2 c exists
       float f[8];
       unpack8(hv[c], f);
       uint4 y;
@@ -757,7 +778,7 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
       emit_limbs<G>(x_u, limb_row, S_u, ci, ci < n_chunks, y, up);
     }
   }
-  named_bar_sync(1, kCT);  // B3: limbs, segment sums and the row scale are in place
+  __syncwarp();  // the warp's own limbs and segment sums are in place (the row scale was published before B2's readers left)
   if (tid == 0) stamp(p.trace, p.n_phases, i, 2);
 }
 
@@ -779,7 +800,7 @@ __device__ __noinline__ void stage_x(int n_chunks, uint32_t in_off, int i, uint3
   uint32_t am2 = 0u;
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int ci = c * kCT + tid;
+    const int ci = stage_chunk(c, lane, warp);
     xv[c] = make_uint4(0u, 0u, 0u, 0u);
     if (ci < n_chunks) {
       xv[c] = poll_chunk(in_pk + ci * 4, tag_in);
@@ -800,10 +821,10 @@ __device__ __noinline__ void stage_x(int n_chunks, uint32_t in_off, int i, uint3
   const float up = finish_stats(part, lane, warp, false, 0.f, 0.f, row_scale_slot, rnorm);
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int ci = c * kCT + tid;
-    if (NCH == 1 || c * kCT < n_chunks) emit_limbs<G>(x_u, limb_row, S_u, ci, ci < n_chunks, xv[c], up);
+    const int ci = stage_chunk(c, lane, warp);
+    if (NCH == 1 || 512 * c < n_chunks) emit_limbs<G>(x_u, limb_row, S_u, ci, ci < n_chunks, xv[c], up);
   }
-  named_bar_sync(1, kCT);  // B3
+  __syncwarp();
   if (tid == 0) stamp(p.trace, p.n_phases, i, 2);
 }
 
@@ -1286,7 +1307,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
   float* S_s = reinterpret_cast<float*>(smem_mega + p_arg.off_S);      // [Kp / kSegK][8]: limb sums per segment
   uint4* h_s = reinterpret_cast<uint4*>(smem_mega + p_arg.off_h);      // residual stream, bf16 [dim]
   float* part = reinterpret_cast<float*>(smem_mega + p_arg.off_misc);  // [16 warps][2]: {sum sq, max |.| bits}
-  float* row_scale = part + 2 * kC;                                // [2] (GEMV-phase parity)
+  float* row_scale = part + 4 * kC;                                // [2] (GEMV-phase parity); part is double-buffered too
   uint64_t* bar_p = reinterpret_cast<uint64_t*>(row_scale + 4);    // full[stages], empty[stages], red_full[2], red_free[2]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1344,7 +1365,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
     const Phase phv = get_phase(p, i);
     const Phase* ph = &phv;
     const uint32_t tag_in = tag0 + (uint32_t)i;  // tag of phase i - 1
-    const uint64_t cnt_target = cnt0 + (uint64_t)i * (uint64_t)n_cta;
+    // arrivals to wait for before sweeping: all but `gate` — the stragglers' packets are polled directly, which takes one
+    // L2 round trip off the critical path (measured: profiles/)
+    const uint64_t cnt_target = cnt0 + (uint64_t)i * (uint64_t)n_cta - (uint64_t)ph->gate;
     if (ph->type != PH_GEMV) {
       switch (GQ) {
         case 1: state = attention_phase<1>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
@@ -1356,18 +1379,19 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
     }
     {
       const int n_chunks = ph->KT * 8;  // Kp == Kx in this kernel (check_model)
-      const int nch = (n_chunks + kCT - 1) / kCT;
+      const int nch = ((ph->KT + kStageTiles - 1) / kStageTiles + 1) / 2;  // stages of the strip, two per staging round
       float* rs = row_scale + (gphase & 1);
+      float* part_g = part + (gphase & 1) * 2 * kC;
       const uint32_t x_u = smem_u32(x_s), S_u = smem_u32(S_s);
       if (ph->in_kind == IN_H) {
         const float inv_k = 1.0f / (float)ph->Kx;
-        if (nch <= 1) stage_h<G, 1>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
-        else stage_h<G, 2>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part);
+        if (nch <= 1) stage_h<G, 1>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part_g);
+        else stage_h<G, 2>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part_g);
       } else {
-        if (nch <= 1) stage_x<G, 1>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else if (nch <= 2) stage_x<G, 2>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else if (nch <= 4) stage_x<G, 4>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
-        else stage_x<G, 8>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part);
+        if (nch <= 1) stage_x<G, 1>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
+        else if (nch <= 2) stage_x<G, 2>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
+        else if (nch <= 4) stage_x<G, 4>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
+        else stage_x<G, 8>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
       }
     }
     int s0, s1;
@@ -1404,7 +1428,7 @@ static bool plan_smem(int G, int64_t Kmax, int dim, int Gq, int n_layer, SmemPla
   const size_t S_bytes = align_up((size_t)(Kmax / seg_k) * 32, 128);
   const size_t red_bytes = (size_t)kRedBufs * kC * 128 * 4;
   const size_t h_bytes = align_up((size_t)dim * 2, 128);
-  const size_t misc = align_up((2 * kC + 4) * 4 + (2 * 16 + 2 * kRedBufs) * 8, 128);
+  const size_t misc = align_up((4 * kC + 4) * 4 + (2 * 16 + 2 * kRedBufs) * 8, 128);
   const size_t lay = align_up((size_t)n_layer * sizeof(LayerPtrs), 128);
   const size_t fixed = x_bytes + S_bytes + red_bytes + h_bytes + misc + lay;
   const size_t cap = 227 * 1024 - kHdrBytes;
@@ -1562,6 +1586,9 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   {
     static const int dbg = []() { const char* e = std::getenv("AO_B200_MEGA_DEBUG"); return e ? std::atoi(e) : 0; }();
     p.dbg = dbg;
+    static const int gate_env = []() { const char* e = std::getenv("AO_B200_MEGA_GATE"); return e ? std::atoi(e) : 32; }();
+    const int gate = gate_env < 0 ? 0 : (gate_env > m->n_cta - 1 ? m->n_cta - 1 : gate_env);
+    for (int k = 0; k < kKinds; ++k) p.kinds[k].gate = gate;
   }
   using KernelFn = void (*)(const Params);
   KernelFn kern = nullptr;
