@@ -22,9 +22,17 @@ import sys
 import threading
 import time
 
-# stdout carries ONE JSON line: keep NCCL's version banner (printed to stdout when NCCL_DEBUG=VERSION) out of it
-if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+# stdout carries ONE JSON line.  Libraries print to fd 1 too (NCCL's version banner under NCCL_DEBUG=VERSION, which the
+# driver sets and this script leaves alone): keep the real stdout on a private descriptor for the JSON line and point
+# fd 1 at stderr for everything else.
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line: dict):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -195,7 +203,7 @@ def run_reference(args):
             "config": {"workload": args.workload, "batch_size": 1, "group_size": spec["group_size"]},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------- GPU arm
@@ -378,7 +386,7 @@ def run_b200(args):
             except Exception as e:  # the checker is optional at run time; the product path is not
                 line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "reference",
                                         "sample": f"unavailable: {type(e).__name__}: {e}"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # tear-down: the graph holds NCCL kernels, release it before the communicator; exit without
         # destroy_process_group (it can block on a communicator that captured graphs have used)

@@ -282,10 +282,15 @@ class DecodeEngine:
         return int(self._mega_state[12:16].view(torch.int32).item()) if self.mega else 0
 
     def check_status(self):
+        """Raises if a bounded wait on the device gave up since the last check (the persistent kernel's hand-overs, the
+        tensor-parallel peer exchange): the tokens produced since then are garbage.  Called once per generate call."""
         st = self.mega_status()
         if st:
             raise RuntimeError(f"ao_b200_decode_mega: a wait inside the kernel timed out (status {st:#x}); "
                                "outputs since then are invalid — rebuild the engine")
+        if self.tp is not None and self.tp.peer is not None and self.tp.peer.status() != 0:
+            raise RuntimeError("tensor-parallel peer exchange: a rank never arrived within the kernel's spin bound; "
+                               "outputs since then are invalid")
 
     def _launch_step_mega(self):
         import ctypes

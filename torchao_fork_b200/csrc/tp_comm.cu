@@ -53,14 +53,17 @@ tp_allreduce_add_kernel(const __nv_bfloat16* __restrict__ partial, __nv_bfloat16
   //   data_off + (r * max_n / 2 + pk0 + 32 j) * 8,  pk0 = (global warp * 4) * 32 + lane:
   // one warp-wide store instruction covers 256 contiguous bytes = two full 128-byte lines on the link (lane-major
   // packets would make it 32 partial sectors)
-  const size_t data_off = kTpHeaderBytes + ((size_t)slot * world) * (max_n / 2) * 8;
+  // a rank's region is sized for whole warps (256 elements = 128 packets each): a partly active last warp still writes
+  // its packets at warp * 128 + lane + 32 j, which must stay inside the region (max_n only has to be a multiple of 8)
+  const size_t region_pk = (size_t)((max_n + 255) / 256) * 128;
+  const size_t data_off = kTpHeaderBytes + ((size_t)slot * world) * region_pk * 8;
   const size_t pk0 = (size_t)((blockIdx.x * kTpThreads + threadIdx.x) >> 5) * 128 + (threadIdx.x & 31);
   if (i < n) {
     const uint4 v = *reinterpret_cast<const uint4*>(partial + i);
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
     for (int d = 1; d < world; ++d) {  // staggered so that the ranks do not all hit the same peer first
       const int p = (rank + d) % world;
-      uint8_t* dst = peers.buf[p] + data_off + ((size_t)rank * (max_n / 2) + pk0) * 8;
+      uint8_t* dst = peers.buf[p] + data_off + ((size_t)rank * region_pk + pk0) * 8;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_packet(dst + 256 * j, w[j], e);
     }
@@ -75,7 +78,7 @@ tp_allreduce_add_kernel(const __nv_bfloat16* __restrict__ partial, __nv_bfloat16
       for (int d = 1; d < kTpMaxWorld; ++d) {
         if (d < world) {
           const int r = (rank + d) % world;
-          const uint8_t* src = mine + data_off + ((size_t)r * (max_n / 2) + pk0) * 8;
+          const uint8_t* src = mine + data_off + ((size_t)r * region_pk + pk0) * 8;
           uint2 pk[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) pk[j] = ld_packet(src + 256 * j);
@@ -137,7 +140,7 @@ tp_allreduce_add_kernel(const __nv_bfloat16* __restrict__ partial, __nv_bfloat16
 extern "C" int64_t ao_b200_tp_buffer_bytes(int world, int64_t max_elems) {
   if (world < 1 || world > ao::kTpMaxWorld || max_elems <= 0 || max_elems % 8 != 0) return 0;
   if (max_elems > (int64_t)ao::kTpMaxCtas * ao::kTpThreads * 8) return 0;
-  return ao::kTpHeaderBytes + (int64_t)2 * world * (max_elems / 2) * 8;
+  return ao::kTpHeaderBytes + (int64_t)2 * world * ((max_elems + 255) / 256 * 128) * 8;
 }
 
 extern "C" int ao_b200_tp_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_out) {
