@@ -374,7 +374,9 @@ def test_aqt_mechanics():
 
 def test_opcheck():
     from torch.library import opcheck
-    utils = ["test_schema", "test_autograd_registration", "test_faketensor"]
+    # the four utilities of the reference's own op tests (test/test_ops.py:300-307): test_aot_dispatch_dynamic is what
+    # makes the ops traceable by torch.compile(fullgraph=True) (generate.py:868-872)
+    utils = ["test_schema", "test_autograd_registration", "test_faketensor", "test_aot_dispatch_dynamic"]
     q = torch.randint(0, 16, (64, 256), dtype=torch.int32, device=DEV)
     packed_t = _aten_pack(q, 2)
     sz = torch.randn(256 // 64, 64, 2, dtype=torch.bfloat16, device=DEV)
@@ -394,6 +396,21 @@ def test_opcheck():
     opcheck(T.b200_int8_unpack, (p8, 64, 256), test_utils=utils)
     opcheck(T.b200_int8_weight_only_mm, (x, p8, s8), test_utils=utils)
     opcheck(T.b200_int8_gemv_fused, (x, p8, s8, None, 0.0, None, 0), test_utils=utils)
+
+
+@pytest.mark.parametrize("kind", ["int4", "int8"])
+def test_quantized_linear_traces_under_torch_compile_fullgraph(kind):
+    """A quantized nn.Linear must go through torch.compile(fullgraph=True) in one graph — tensor subclass, dispatch table
+    and the torch.library ops with their fake impls (the reference decodes under torch.compile, generate.py:865-875).
+    backend="aot_eager": dynamo + AOT autograd tracing, no Triton."""
+    torch._dynamo.reset()
+    lin = torch.nn.Linear(256, 128, bias=True, device=DEV, dtype=torch.bfloat16)
+    x = torch.randn(3, 256, dtype=torch.bfloat16, device=DEV)
+    ao.quantize_(lin, ao.Int4WeightOnlyConfig(group_size=64) if kind == "int4" else ao.Int8WeightOnlyConfig())
+    with torch.no_grad():
+        y_eager = lin(x)
+        y = torch.compile(lin, fullgraph=True, backend="aot_eager")(x)
+    assert torch.equal(y, y_eager)
 
 
 def test_errors_are_loud():
