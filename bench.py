@@ -266,6 +266,93 @@ def time_gemv_launch(engine, which, iters):
     return e0.elapsed_time(e1) * 1e-3 / (iters * len(lins)), lin0, sum(l.weight_bytes for l in lins)
 
 
+def time_mega_kernel(eng, iters):
+    """Average duration of the persistent decode kernel ALONE (no sampling): a CUDA graph of `iters` launches (each one
+    advances the position, streams all the weights — 4 GB >> L2 — and appends to the caches), CUDA events around it."""
+    import ctypes
+    import torch
+    from torchao_fork_b200 import _lib
+    pos0 = int(eng.pos.item())
+    iters = max(1, min(iters, eng.S - pos0 - 1))
+    L = _lib.lib()
+
+    def launch():
+        _lib.check(L.ao_b200_decode_mega_step(ctypes.byref(eng._mega_model), eng._mega_plan.data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream), "decode_mega_step")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        launch()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    eng.pos.fill_(pos0)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(iters):
+            launch()
+    eng.pos.fill_(pos0)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    eng.check_status()
+    eng.pos.fill_(pos0)
+    return e0.elapsed_time(e1) * 1e-3 / iters, pos0, iters
+
+
+def time_reference_gpu_kernels(quant, group_size, shapes, n_layer, iters, device):
+    """The reference's own GPU kernel on the same shapes, same run: for int4
+    aten._weight_int4pack_mm on weights packed by aten._convert_weight_to_int4pack(inner_k_tiles=8)
+    (tensor_core_tiled_layout.py:104,279); for int8 the eager formula mm(x, w.t().to(bf16)) * scale (plain_layout.py:256-262).
+    One CUDA graph per shape over `n_layer` DISTINCT weights (> L2 in total), M = 1, CUDA events."""
+    import torch
+    out = {}
+    for name, (n, k) in shapes.items():
+        layers = n_layer if name != "output" else 2
+        if quant == "int8":
+            layers = min(layers, 4)   # the eager formula materialises a bf16 copy of the weight per call
+        x = torch.randn(1, k, dtype=torch.bfloat16, device=device)
+        ws = []
+        for _ in range(layers):
+            if quant == "int4":
+                q = torch.randint(0, 256, (n, k // 2), dtype=torch.uint8, device=device)
+                ws.append((torch.ops.aten._convert_weight_to_int4pack(q, 8),
+                           torch.randn(k // group_size, n, 2, dtype=torch.bfloat16, device=device)))
+            else:
+                ws.append((torch.randint(-128, 128, (n, k), dtype=torch.int8, device=device),
+                           torch.rand(n, dtype=torch.bfloat16, device=device)))
+
+        def run(w):
+            if quant == "int4":
+                return torch.ops.aten._weight_int4pack_mm(x, w[0], group_size, w[1])
+            return torch.mm(x, w[0].t().to(torch.bfloat16)) * w[1]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            run(ws[0])
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for w in ws:
+                run(w)
+        for _ in range(2):
+            g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = {"n": n, "k": k, "us_per_launch": e0.elapsed_time(e1) * 1e3 / (iters * layers)}
+        del ws, g
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -328,6 +415,8 @@ def run_b200(args):
         t_dev, t_e2e = t.tolist()
 
     toks = K * args.batch_size
+    pos_value = (PROMPT_LEN, PROMPT_LEN + W + K)                       # positions decoded in the `value` window
+    pos_e2e = (PROMPT_LEN + W + K, PROMPT_LEN + 2 * (W + K))           # ... and in the `e2e` window that follows it
     line = {"metric": "llama3_8b_int4_decode_tok_per_s" if args.workload == "llama3-8b-int4" else args.workload + "_decode_tok_per_s",
             "value": toks / t_dev, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": t_dev / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -336,7 +425,12 @@ def run_b200(args):
             "data": "synthetic (random-init weights, random tokens)",
             "config": {"workload": args.workload, "batch_size": args.batch_size, "group_size": spec["group_size"],
                        "prompt_len": PROMPT_LEN, "sampling": f"temperature={args.temperature}, top_k={args.top_k}",
-                       "parallelism": f"tp{world}", "l2": "inputs larger than L2 (weights %.2f GB per step per rank)" % (eng.weight_bytes / 1e9)},
+                       "parallelism": f"tp{world}", "l2": "inputs larger than L2 (weights %.2f GB per step per rank)" % (eng.weight_bytes / 1e9),
+                       "engine": "persistent decode kernel, 1 launch + sampling per token" if eng.mega else "per-projection CUDA graph",
+                       "context": {"value_positions": list(pos_value), "e2e_positions": list(pos_e2e)},
+                       "timing_windows_ms": {"value": t_dev * 1e3, "e2e": t_e2e * 1e3,
+                                             "note": "value and e2e are timed one after the other (e2e at the longer context); "
+                                                     "windows under ~100 ms are inside run-to-run noise of a few percent"}},
             "e2e": {"value": toks / t_e2e, "unit": "tok/s", "h2d_bytes_per_step": 8 * args.batch_size,
                     "d2h_bytes_per_step": 8 * args.batch_size},
             "gpu_launches": eng.launches_per_step * K,
@@ -350,31 +444,91 @@ def run_b200(args):
             peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
-        which = "w13" if eng.layers[0]["w13"] is not None else "w2"
-        t_launch, lin, _ = time_gemv_launch(eng, which, max(10, K // 10))
-        if lin.kind == "int4":
-            alg = int4_gemv_bytes(args.batch_size, lin.n, lin.k, lin.group_size)
-        else:
-            alg = lin.weight_bytes + args.batch_size * (lin.n + lin.k) * 2
-        traffic = None
-        tp_path = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp_path):
-            tr = json.load(open(tp_path))
-            if tr.get("n") == lin.n and tr.get("k") == lin.k and tr.get("kind") == lin.kind:
-                traffic = tr.get("dram_bytes_per_launch")
-        line["roofline"] = {"bound": "hbm", "achieved": alg / t_launch / 1e9, "peak": peak, "unit": "GB/s",
-                            "frac": alg / t_launch / 1e9 / peak, "traffic": traffic,
-                            "kernel": f"{lin.kind} weight-only GEMV {lin.n}x{lin.k} (fused w1|w3), M={args.batch_size}",
-                            "algorithmic_bytes_per_launch": alg, "us_per_launch": t_launch * 1e6, "peak_source": peak_src}
-        # all GEMV launches of one step, back to back (share of the step)
-        t_all, b_all = 0.0, 0
+        sm_mhz = line["clocks"].get("sm_mhz") or 1965.0
+        shapes = {}
         for nm in ("wqkv", "wo", "w13", "w1", "w3", "w2"):
             if eng.layers[0][nm] is not None:
-                t1, l1, wb = time_gemv_launch(eng, nm, max(5, K // 20))
-                t_all += t1 * len(eng.layers)
-                b_all += wb
-        line["roofline"]["all_layer_gemvs"] = {"gbs": b_all / t_all / 1e9, "frac": b_all / t_all / 1e9 / peak,
-                                               "share_of_step": t_all / (t_dev / K)}
+                shapes[nm] = (eng.layers[0][nm].n, eng.layers[0][nm].k)
+        # ---- the per-projection kernels, each in a graph over the 32 layers' distinct weights (standalone launches:
+        #      what `ao_b200_int4_mm` / the torchao:: ops deliver for one linear; config 1 = the 4096 x 4096 one)
+        standalone, t_all, b_all = {}, 0.0, 0
+        for nm in shapes:
+            t1, l1, wb = time_gemv_launch(eng, nm, max(5, K // 20))
+            alg1 = (int4_gemv_bytes(args.batch_size, l1.n, l1.k, l1.group_size) if l1.kind == "int4"
+                    else l1.weight_bytes + args.batch_size * (l1.n + l1.k) * 2)
+            standalone[nm] = {"n": l1.n, "k": l1.k, "us_per_launch": t1 * 1e6, "gbs": alg1 / t1 / 1e9, "frac": alg1 / t1 / 1e9 / peak}
+            t_all += t1 * len(eng.layers)
+            b_all += wb
+        line["standalone_gemv_kernels"] = {"per_shape": standalone, "all_layers": {"gbs": b_all / t_all / 1e9, "frac": b_all / t_all / 1e9 / peak},
+                                           "how": "each linear's own kernel launched back to back over the 32 layers' weights in a CUDA graph (PDL chain), CUDA events"}
+        if "wo" in standalone and standalone["wo"]["n"] == 4096 and standalone["wo"]["k"] == 4096:
+            line["config1"] = dict(standalone["wo"], workload="single Linear 4096x4096, Int4WeightOnlyConfig(group_size=128), M=1 (BASELINE.json configs[0])")
+        traffic = None
+        tp_path = os.path.join(ROOT, "profiles", "traffic.json")
+        tr = json.load(open(tp_path)) if os.path.exists(tp_path) else {}
+        if eng.mega:
+            # ---- the dominant kernel IS the step: the persistent decode kernel, timed alone
+            eng.set_state(prompt[-1:].repeat(args.batch_size), pos_value[0] + (pos_value[1] - pos_value[0]) // 2)
+            t_k, pos0, it_k = time_mega_kernel(eng, max(10, min(50, K // 4)))
+            kv_bytes = 2 * len(eng.layers) * eng.Hkv * 128 * 2 * (pos0 + it_k // 2)      # K and V rows read per token
+            alg = eng.weight_bytes + kv_bytes
+            if tr.get("kernel") == "decode_mega":
+                traffic = tr.get("dram_bytes_per_launch")
+            line["roofline"] = {"bound": "hbm", "achieved": alg / t_k / 1e9, "peak": peak, "unit": "GB/s",
+                                "frac": alg / t_k / 1e9 / peak, "traffic": traffic,
+                                "kernel": f"decode_mega_kernel<{eng.output.group_size}>: one launch = one decoded token (all 129 int4 linears, norms, RoPE, attention)",
+                                "algorithmic_bytes_per_launch": alg, "us_per_launch": t_k * 1e6, "peak_source": peak_src,
+                                "context_positions": [pos0, pos0 + it_k]}
+            # ---- inside the kernel: the streaming loops of the projections (clock64 stamps of every CTA)
+            cyc = eng.mega_phase_cycles()
+            phases, t_sum, b_sum = {}, 0.0, 0
+            for nm, key in (("wqkv", "wqkv"), ("wo", "wo"), ("w13", "w13"), ("w2", "w2")):
+                main = cyc[key]["main"] / sm_mhz                       # us [layers][ctas]
+                t_phase = float(main.max(axis=1).mean())               # a phase lasts until its slowest CTA is done
+                lin = eng.layers[0][nm]
+                alg1 = int4_gemv_bytes(1, lin.n, lin.k, lin.group_size)
+                phases[nm] = {"us": t_phase, "us_mean_cta": float(main.mean()), "gbs": alg1 / t_phase / 1e3, "frac": alg1 / t_phase / 1e3 / peak}
+                t_sum += t_phase
+                b_sum += alg1
+            om = cyc["output"]["main"] / sm_mhz
+            alg_o = int4_gemv_bytes(1, eng.output.n, eng.output.k, eng.output.group_size)
+            phases["output"] = {"us": float(om.max()), "gbs": alg_o / float(om.max()) / 1e3, "frac": alg_o / float(om.max()) / 1e3 / peak}
+            over = {nm: float((cyc[nm]["wait"] + cyc[nm].get("staging", cyc[nm].get("phase"))).mean() / sm_mhz) for nm in ("wqkv", "attn", "wo", "w13", "w2")}
+            line["roofline"]["all_layer_gemvs"] = {
+                "gbs": b_sum / t_sum / 1e3, "frac": b_sum / t_sum / 1e3 / peak, "share_of_kernel": t_sum * len(eng.layers) / (t_k * 1e6),
+                "per_projection": phases, "hand_over_us_per_layer": over,
+                "how": "streaming (main) loops of the 4 projections of a layer inside the persistent kernel, per phase the "
+                       "slowest CTA, mean over layers 1..31; clock64 stamps converted at the sampled SM clock "
+                       f"({sm_mhz:.0f} MHz); the ring prefetches the next projection's weights during the hand-over, so a "
+                       "loop can read above the HBM rate"}
+        else:
+            which = "w13" if eng.layers[0]["w13"] is not None else "w2"
+            st = standalone[which]
+            lin = eng.layers[0][which]
+            if tr.get("n") == lin.n and tr.get("k") == lin.k and tr.get("kind") == lin.kind:
+                traffic = tr.get("dram_bytes_per_launch")
+            alg = st["gbs"] * 1e9 * st["us_per_launch"] * 1e-6
+            line["roofline"] = {"bound": "hbm", "achieved": st["gbs"], "peak": peak, "unit": "GB/s", "frac": st["frac"], "traffic": traffic,
+                                "kernel": f"{lin.kind} weight-only GEMV {lin.n}x{lin.k} (fused w1|w3), M={args.batch_size}",
+                                "algorithmic_bytes_per_launch": alg, "us_per_launch": st["us_per_launch"], "peak_source": peak_src,
+                                "all_layer_gemvs": {"gbs": b_all / t_all / 1e9, "frac": b_all / t_all / 1e9 / peak, "share_of_step": t_all / (t_dev / K)}}
+        # ---- the reference's GPU kernel on the same shapes, same run
+        if spec["quant"] in ("int4", "int8") and world == 1 and not args.no_reference_gpu:
+            try:
+                ref_shapes = {"wqkv": shapes["wqkv"], "wo": shapes["wo"], "w1": (cfg.intermediate_size, cfg.dim), "w3": (cfg.intermediate_size, cfg.dim),
+                              "w2": shapes["w2"], "output": (eng.output.n, eng.output.k)}
+                rg = time_reference_gpu_kernels(spec["quant"], spec["group_size"], ref_shapes, len(eng.layers), 5, device)
+                t_layer = sum(rg[nm]["us_per_launch"] for nm in ("wqkv", "wo", "w1", "w3", "w2"))
+                t_tok = t_layer * len(eng.layers) + rg["output"]["us_per_launch"]
+                line["reference_gpu"] = {
+                    "kernel": "aten._weight_int4pack_mm (weights by aten._convert_weight_to_int4pack, inner_k_tiles=8)" if spec["quant"] == "int4"
+                              else "eager mm(x, w.t().to(bf16)) * scale (plain_layout.py:256-262)",
+                    "M": 1, "us_per_launch": {nm: v["us_per_launch"] for nm, v in rg.items()},
+                    "all_linears_us_per_token": t_tok, "all_layer_gbs": eng.weight_bytes / (t_tok * 1e-6) / 1e9,
+                    "implied_tok_s_linears_only": 1e6 / t_tok,
+                    "this_repo_standalone_us_per_launch": {nm: v["us_per_launch"] for nm, v in standalone.items()}}
+            except Exception as e:
+                line["reference_gpu"] = {"unavailable": f"{type(e).__name__}: {e}"}
         if world == 1 and not args.no_cpu_baseline:
             # separate process: the reference's torchao and this repo's ops both own the `torchao::` op namespace
             try:
@@ -410,6 +564,7 @@ def main():
     ap.add_argument("--temperature", type=float, default=0.8)
     ap.add_argument("--top-k", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-gpu", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "torchao_fork_b200", "lib", "libao_b200.so")
 PATTERNS = [("UTCMMA", r"\bUTC\w*MMA"), ("LDTM", r"\bLDTM"), ("STTM", r"\bSTTM"), ("UBLKCP", r"\bUBLKCP"),
             ("UTMALDG", r"\bUTMALDG"), ("UTMASTG", r"\bUTMASTG"), ("SYNCS", r"\bSYNCS"), ("HMMA", r"\bHMMA"),
-            ("IMMA", r"\bIMMA"), ("LDSM", r"\bLDSM"), ("MOVM", r"\bMOVM"), ("LDGSTS", r"\bLDGSTS"), ("instr", r"^\s+/\*[0-9a-f]{4}\*/")]
+            ("IMMA", r"\bIMMA"), ("LDSM", r"\bLDSM"), ("MOVM", r"\bMOVM"), ("LDGSTS", r"\bLDGSTS"), ("instr", r"^\s+/\*[0-9a-f]{4,}\*/\s+\S")]
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 demangle = {}
 names = sorted(set(re.findall(r"Function : (\S+)", out)))

@@ -277,6 +277,38 @@ class DecodeEngine:
             self._mega_kv[i, 0, :, : self.S, :128].copy_(l["k_cache"][0])
             self._mega_kv[i, 1, :, : self.S, :128].copy_(l["v_cache"][0])
 
+    def mega_phase_cycles(self):
+        """One traced launch of the persistent kernel at the current state -> {kind: {"main": cycles [layers][ctas], ...}}
+        (SM clock cycles from the kernel's own stamps: 0 phase entered, 1 inputs published, 6 statistics done, 2 staging
+        done, 3 main loop done, 4 outputs published).  Re-creates the kernel's buffers with a trace buffer attached: call
+        it after the timed runs (graphs captured before keep the old buffers)."""
+        assert self.mega
+        self._keep_alive = getattr(self, "_keep_alive", []) + [self._mega_xchg, self._mega_state, self._mega_plan, self._mega_kv]
+        self._setup_mega(trace=True)
+        self._sync_mega_kv()
+        for _ in range(2):
+            self._launch_step_mega()
+        torch.cuda.synchronize(self.device)
+        self.check_status()
+        tr = self._mega_trace.cpu().numpy().astype("float64")   # [cta][phase][8]
+        nl = len(self.layers)
+        kinds = ["wqkv", "attn", "wo", "w13", "w2"]
+        out = {}
+        for k, name in enumerate(kinds):
+            idx = [5 * l + k for l in range(1 if nl > 1 else 0, nl)]   # layer 0 starts cold
+            t = tr[:, idx, :]
+            d = {"wait": t[:, :, 1] - t[:, :, 0]}
+            if name == "attn":
+                d["phase"] = t[:, :, 4] - t[:, :, 1]
+            else:
+                d["staging"] = t[:, :, 2] - t[:, :, 1]
+                d["main"] = t[:, :, 3] - t[:, :, 2]
+            out[name] = {kk: v.T for kk, v in d.items()}
+        t = tr[:, [5 * nl], :]
+        out["output"] = {"wait": (t[:, :, 1] - t[:, :, 0]).T, "staging": (t[:, :, 2] - t[:, :, 1]).T, "main": (t[:, :, 3] - t[:, :, 2]).T}
+        out["_kernel_cycles"] = float((tr[:, 5 * nl, 3] - tr[:, 0, 0]).mean())
+        return out
+
     def mega_status(self) -> int:
         """Sticky status word of the persistent kernel (0 = fine; non-zero = a wait inside it timed out)."""
         return int(self._mega_state[12:16].view(torch.int32).item()) if self.mega else 0
