@@ -414,6 +414,17 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_dev, t_e2e = t.tolist()
 
+    # the persistent kernel alone (every rank launches: with tensor parallelism the kernels wait on one another)
+    mega_timing = None
+    if eng.mega:
+        eng.set_state(prompt[-1:].repeat(args.batch_size), PROMPT_LEN + (W + K) // 2)
+        barrier()
+        t_k, pos0_k, it_k = time_mega_kernel(eng, max(10, min(50, K // 4)))
+        if world > 1:
+            t = torch.tensor([t_k], device=device, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_k = float(t.item())
+        mega_timing = (t_k, pos0_k, it_k)
     toks = K * args.batch_size
     pos_value = (PROMPT_LEN, PROMPT_LEN + W + K)                       # positions decoded in the `value` window
     pos_e2e = (PROMPT_LEN + W + K, PROMPT_LEN + 2 * (W + K))           # ... and in the `e2e` window that follows it
@@ -468,8 +479,7 @@ def run_b200(args):
         tr = json.load(open(tp_path)) if os.path.exists(tp_path) else {}
         if eng.mega:
             # ---- the dominant kernel IS the step: the persistent decode kernel, timed alone
-            eng.set_state(prompt[-1:].repeat(args.batch_size), pos_value[0] + (pos_value[1] - pos_value[0]) // 2)
-            t_k, pos0, it_k = time_mega_kernel(eng, max(10, min(50, K // 4)))
+            t_k, pos0, it_k = mega_timing
             kv_bytes = 2 * len(eng.layers) * eng.Hkv * 128 * 2 * (pos0 + it_k // 2)      # K and V rows read per token
             alg = eng.weight_bytes + kv_bytes
             if tr.get("kernel") == "decode_mega":
@@ -479,28 +489,30 @@ def run_b200(args):
                                 "kernel": f"decode_mega_kernel<{eng.output.group_size}>: one launch = one decoded token (all 129 int4 linears, norms, RoPE, attention)",
                                 "algorithmic_bytes_per_launch": alg, "us_per_launch": t_k * 1e6, "peak_source": peak_src,
                                 "context_positions": [pos0, pos0 + it_k]}
+            line["roofline"]["note"] = "per rank" if world > 1 else "single GPU"
             # ---- inside the kernel: the streaming loops of the projections (clock64 stamps of every CTA)
-            cyc = eng.mega_phase_cycles()
-            phases, t_sum, b_sum = {}, 0.0, 0
-            for nm, key in (("wqkv", "wqkv"), ("wo", "wo"), ("w13", "w13"), ("w2", "w2")):
-                main = cyc[key]["main"] / sm_mhz                       # us [layers][ctas]
-                t_phase = float(main.max(axis=1).mean())               # a phase lasts until its slowest CTA is done
-                lin = eng.layers[0][nm]
-                alg1 = int4_gemv_bytes(1, lin.n, lin.k, lin.group_size)
-                phases[nm] = {"us": t_phase, "us_mean_cta": float(main.mean()), "gbs": alg1 / t_phase / 1e3, "frac": alg1 / t_phase / 1e3 / peak}
-                t_sum += t_phase
-                b_sum += alg1
-            om = cyc["output"]["main"] / sm_mhz
-            alg_o = int4_gemv_bytes(1, eng.output.n, eng.output.k, eng.output.group_size)
-            phases["output"] = {"us": float(om.max()), "gbs": alg_o / float(om.max()) / 1e3, "frac": alg_o / float(om.max()) / 1e3 / peak}
-            over = {nm: float((cyc[nm]["wait"] + cyc[nm].get("staging", cyc[nm].get("phase"))).mean() / sm_mhz) for nm in ("wqkv", "attn", "wo", "w13", "w2")}
-            line["roofline"]["all_layer_gemvs"] = {
-                "gbs": b_sum / t_sum / 1e3, "frac": b_sum / t_sum / 1e3 / peak, "share_of_kernel": t_sum * len(eng.layers) / (t_k * 1e6),
-                "per_projection": phases, "hand_over_us_per_layer": over,
-                "how": "streaming (main) loops of the 4 projections of a layer inside the persistent kernel, per phase the "
-                       "slowest CTA, mean over layers 1..31; clock64 stamps converted at the sampled SM clock "
-                       f"({sm_mhz:.0f} MHz); the ring prefetches the next projection's weights during the hand-over, so a "
-                       "loop can read above the HBM rate"}
+            cyc = eng.mega_phase_cycles() if world == 1 else None
+            if cyc is not None:
+                phases, t_sum, b_sum = {}, 0.0, 0
+                for nm, key in (("wqkv", "wqkv"), ("wo", "wo"), ("w13", "w13"), ("w2", "w2")):
+                    main = cyc[key]["main"] / sm_mhz                       # us [layers][ctas]
+                    t_phase = float(main.max(axis=1).mean())               # a phase lasts until its slowest CTA is done
+                    lin = eng.layers[0][nm]
+                    alg1 = int4_gemv_bytes(1, lin.n, lin.k, lin.group_size)
+                    phases[nm] = {"us": t_phase, "us_mean_cta": float(main.mean()), "gbs": alg1 / t_phase / 1e3, "frac": alg1 / t_phase / 1e3 / peak}
+                    t_sum += t_phase
+                    b_sum += alg1
+                om = cyc["output"]["main"] / sm_mhz
+                alg_o = int4_gemv_bytes(1, eng.output.n, eng.output.k, eng.output.group_size)
+                phases["output"] = {"us": float(om.max()), "gbs": alg_o / float(om.max()) / 1e3, "frac": alg_o / float(om.max()) / 1e3 / peak}
+                over = {nm: float((cyc[nm]["wait"] + cyc[nm].get("staging", cyc[nm].get("phase"))).mean() / sm_mhz) for nm in ("wqkv", "attn", "wo", "w13", "w2")}
+                line["roofline"]["all_layer_gemvs"] = {
+                    "gbs": b_sum / t_sum / 1e3, "frac": b_sum / t_sum / 1e3 / peak, "share_of_kernel": t_sum * len(eng.layers) / (t_k * 1e6),
+                    "per_projection": phases, "hand_over_us_per_layer": over,
+                    "how": "streaming (main) loops of the 4 projections of a layer inside the persistent kernel, per phase the "
+                           "slowest CTA, mean over layers 1..31; clock64 stamps converted at the sampled SM clock "
+                           f"({sm_mhz:.0f} MHz); the ring prefetches the next projection's weights during the hand-over, so a "
+                           "loop can read above the HBM rate"}
         else:
             which = "w13" if eng.layers[0]["w13"] is not None else "w2"
             st = standalone[which]

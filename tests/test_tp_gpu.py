@@ -162,6 +162,68 @@ def _peer_worker(rank, world, port, q):
         q.put((rank, "".join(traceback.format_exception(type(e), e, e.__traceback__)), 0.0, 0.0))
 
 
+def _mega_worker(rank, world, port, q):
+    """Batch 1: the persistent decode kernel with the wo / w2 exchange fused into it (partial sums pushed into the
+    peers' exchange regions from the GEMV epilogue, summed in rank order by the next projection's staging) against the
+    TP = 1 persistent kernel built from the same seed."""
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                          LOCAL_RANK=str(rank))
+        import torch.distributed as dist
+        from torchao_fork_b200._models.llama import Generator, ModelArgs
+        from torchao_fork_b200._models.llama.model import transformer_configs
+        from torchao_fork_b200._models.llama.tp import TPContext, build_tp_transformer
+        from torchao_fork_b200.quantization.utils import compute_error
+
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        ctx = TPContext.from_env(backend="nccl", device=dev)
+        kv = max(2, world)                       # whole kv heads per rank
+        cfg = ModelArgs(**{**transformer_configs["tiny-llama3"], "n_local_heads": kv, "n_head": 4 * kv, "dim": 512 * kv,
+                           "intermediate_size": 1024 * kv, "vocab_size": 128 * 16})
+        spec = dict(quant="int4", group_size=128)
+        S, T, steps = 96, 40, 6
+        prompt = torch.randint(0, cfg.vocab_size, (1, T), generator=torch.Generator().manual_seed(1)).to(dev)
+        forced = torch.randint(0, cfg.vocab_size, (steps, 1), generator=torch.Generator().manual_seed(2)).to(dev)
+        outs = {}
+        for name, c in (("tp1", None), ("tpN", ctx)):
+            model = build_tp_transformer(cfg, c, dev, spec, seed=11)
+            gen = Generator(model, 1, S, temperature=0.0, top_k=None, use_graph=True, tp=c, mega=True)
+            assert gen.engine.mega
+            model(prompt, torch.arange(T, device=dev, dtype=torch.int32))   # prefill fills the caches
+            step_logits = []
+            for i in range(steps):
+                gen.engine.set_state(forced[i], T + i)
+                gen.engine.step()
+                lg = gen.engine.logits if c is None else ctx.gather_logits(gen.engine.logits)
+                step_logits.append(lg.float().clone())
+            torch.cuda.synchronize()
+            gen.engine.check_status()
+            seq = gen.generate(prompt[0], 10)
+            outs[name] = (seq.clone(), torch.stack(step_logits))
+            gen.engine.graph = None
+            gen.engine.graph_stream = None
+        s1, l1 = outs["tp1"]
+        sN, lN = outs["tpN"]
+        per_step = [compute_error(l1[i], lN[i]).item() for i in range(steps)]
+        assert min(per_step) >= 35.0, per_step
+        # the replicated state cannot drift: every rank computed the same logits and decoded the same tokens
+        chk = lN.clone()
+        dist.broadcast(chk, 0)
+        assert torch.equal(chk, lN)
+        t = sN.clone()
+        dist.broadcast(t, 0)
+        assert torch.equal(t, sN)
+        q.put((rank, "ok", min(per_step), (s1 == sN).float().mean().item()))
+        q.close()
+        q.join_thread()
+        torch.cuda.synchronize()
+        os._exit(0)
+    except Exception as e:
+        import traceback
+        q.put((rank, "".join(traceback.format_exception(type(e), e, e.__traceback__)), 0.0, 0.0))
+
+
 def _run(worker, world=None, timeout=300):
     world = world or int(os.environ.get("AO_TP_TEST_WORLD", "2"))
     port = _free_port()
@@ -192,3 +254,11 @@ def test_tp2_int4_decode_matches_tp1():
     for rank, status, sq, same in _run(_worker, timeout=500):
         assert status == "ok", f"rank {rank}:\n{status}"
         print(f"rank {rank}: logits SQNR tp2 vs tp1 {sq:.1f} dB, tokens equal {same:.2f}")
+
+
+@pytest.mark.timeout(600)
+def test_tp_persistent_kernel_matches_tp1():
+    """AO_TP_TEST_WORLD = 2 (default), 4 or 8."""
+    for rank, status, sq, same in _run(_mega_worker, timeout=500):
+        assert status == "ok", f"rank {rank}:\n{status}"
+        print(f"rank {rank}: persistent kernel, logits SQNR tpN vs tp1 {sq:.1f} dB, tokens equal {same:.2f}")

@@ -204,7 +204,7 @@ class DecodeEngine:
         self.launches_per_step = 0
         self._host_pos = 0   # host mirror of *pos (set_state / step): decoding past the caches raises instead of corrupting them
         # one persistent launch per token (csrc/decode_mega.cu): batch 1, every linear int4 with one group size
-        can_mega = (batch_size == 1 and self.fused and tp is None
+        can_mega = (batch_size == 1 and self.fused
                     and all(l[k] is not None and l[k].kind == "int4" for l in self.layers for k in ("wqkv", "wo", "w13", "w2"))
                     and self.output.kind == "int4"
                     and len({l[k].group_size for l in self.layers for k in ("wqkv", "wo", "w13", "w2")} | {self.output.group_size}) == 1
@@ -239,7 +239,8 @@ class DecodeEngine:
         m = _lib.MegaModel()
         m.n_layer, m.dim, m.n_head, m.n_kv_head, m.head_dim = nl, self.cfg.dim, self.H, self.Hkv, self.hd
         m.inter, m.vocab, m.group_size, m.max_seq = self.I, self.output.n, self.output.group_size, self.S
-        m.world, m.rank = 1, 0
+        tp = self.tp if (self.tp is not None and self.tp.world_size > 1) else None
+        m.world, m.rank = (1, 0) if tp is None else (tp.world_size, tp.rank)
         m.n_cta = torch.cuda.get_device_properties(dev).multi_processor_count
         if os.environ.get("AO_B200_MEGA_CTAS"):
             m.n_cta = int(os.environ["AO_B200_MEGA_CTAS"])
@@ -258,8 +259,30 @@ class DecodeEngine:
         self._mega_layers, self._mega_model = arr, m   # keep the host structs alive
         xb = int(L.ao_b200_decode_mega_xchg_bytes(ctypes.byref(m)))
         assert xb > 0, "ao_b200_decode_mega: unsupported model shape"
-        self._mega_xchg = torch.zeros(xb, dtype=torch.uint8, device=dev)
-        m.xchg[0] = self._mega_xchg.data_ptr()
+        if tp is None:
+            self._mega_xchg = torch.zeros(xb, dtype=torch.uint8, device=dev)
+            m.xchg[0] = self._mega_xchg.data_ptr()
+        else:
+            # tensor parallel: every rank's exchange region is mapped into every peer (CUDA IPC) — the wo / w2 epilogues
+            # push their partial sums straight into the peers' regions over NVLink, the next projection's staging sums
+            # the ranks in rank order.  All ranks call this together.
+            import torch.distributed as dist
+            with torch.cuda.device(dev):
+                own, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+                _lib.check(L.ao_b200_tp_alloc(xb, ctypes.byref(own), handle), "tp_alloc")   # cudaMalloc, zeroed
+                handles = [None] * tp.world_size
+                dist.all_gather_object(handles, bytes(handle.raw), group=tp.group)
+                self._mega_xchg = own.value
+                self._mega_peers = []
+                for r, hnd in enumerate(handles):
+                    if r == tp.rank:
+                        m.xchg[r] = own.value
+                    else:
+                        peer = ctypes.c_void_p()
+                        _lib.check(L.ao_b200_tp_open(ctypes.create_string_buffer(hnd, 64), ctypes.byref(peer)), f"tp_open(rank {r})")
+                        m.xchg[r] = peer.value
+                        self._mega_peers.append(peer.value)
+            dist.barrier(group=tp.group)   # nobody pushes before everybody has zeroed and published its region
         pb = int(L.ao_b200_decode_mega_plan_bytes(ctypes.byref(m)))
         assert pb > 0, "ao_b200_decode_mega: unsupported model shape"
         self._mega_trace = None
@@ -329,7 +352,10 @@ class DecodeEngine:
         st = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(_lib.lib().ao_b200_decode_mega_step(ctypes.byref(self._mega_model), self._mega_plan.data_ptr(), st),
                    "decode_mega_step")
-        self._sample(self.logits)
+        logits = self.logits
+        if self.tp is not None and self.tp.world_size > 1:
+            logits = self.tp.gather_logits(self.logits)   # the output projection is sharded over the vocabulary
+        self._sample(logits)
         self.launches_per_step = 2 + (1 if self.temperature != 0.0 else 0)
 
     # ------------------------------------------------------------------ one step, eager launches

@@ -201,17 +201,17 @@ __device__ __forceinline__ void bulk_g2s_u(uint32_t dst, const void* src, uint32
 // by NVLink peers; on local memory it costs the same as `.gpu`.
 __device__ __forceinline__ uint64_t ld_pk(const uint64_t* p) {
   uint64_t v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ ulonglong2 ld_pk2(const uint64_t* p) {
   ulonglong2 v;
-  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_pk(uint64_t* p, uint32_t data, uint32_t tag) {
   const uint64_t v = (uint64_t)data | ((uint64_t)tag << 32);
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ uint64_t ld_ctr(const uint64_t* p) {
   uint64_t v;
