@@ -30,15 +30,28 @@ def main():
     spec = bench.WORKLOADS[args.workload]
     if args.layers:
         transformer_configs[spec["model"]]["n_layer"] = args.layers
-    model, cfg = bench.build_model(spec, torch.device("cuda"))
-    gen = Generator(model, 1, args.pos + 64, temperature=0.8, top_k=200, use_graph=False, mega=True)
+    # under torch.distributed.run: tensor parallel; every rank traces, rank 0 reports
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    tp = None
+    if world > 1:
+        import torch.distributed as dist
+        from torchao_fork_b200._models.llama.tp import TPContext
+        dist.init_process_group("nccl", device_id=device)
+        tp = TPContext(rank, world, device)
+    model, cfg = bench.build_model(spec, device, tp)
+    gen = Generator(model, 1, args.pos + 64, temperature=0.8, top_k=200, use_graph=False, mega=True, tp=tp)
     eng = gen.engine
     assert eng.mega
     eng._setup_mega(trace=True)
-    eng.set_state(torch.tensor([1], device="cuda"), args.pos)
+    eng.set_state(torch.tensor([1], device=device), args.pos)
     for _ in range(5):
         eng.step()
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     eng.step()
@@ -50,7 +63,12 @@ def main():
     n_cta, n_ph, _ = tr.shape
     nl = (n_ph - 1) // 5
     names = ["wqkv", "attn", "wo", "w13", "w2"]
-    rep = {"step_us_with_sampling": step_us, "n_cta": n_cta, "phases": {}}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return
+    rep = {"step_us_with_sampling": step_us, "n_cta": n_cta, "world": world, "phases": {}}
     rep["kernel_us_mean_over_ctas"] = float((tr[:, n_ph - 1, 3] - tr[:, 0, 0]).mean())
     rep["slow_polls_total"] = int(eng._mega_state[16:20].view(torch.int32).item())  # sweeps that ran ahead of their packets (all steps)
 
@@ -88,6 +106,14 @@ def main():
         rep["phases"][nm] = {kk: ([round(sum(x[j] for x in v) / len(v), 2) for j in range(3)] if isinstance(v[0], list) else v[0])
                              for kk, v in acc.items()}
     rep["phases"]["output"] = summarize(n_ph - 1, True)
+    # timeline: when the CTAs enter each phase (mean over CTAs, relative to their own entry into phase 0)
+    t_in = (tr[:, :, 0] - tr[:, :1, 0]).mean(axis=0)
+    t_end = float((tr[:, n_ph - 1, 3] - tr[:, 0, 0]).mean())
+    per_layer = [float(t_in[5 * (l + 1)] - t_in[5 * l]) if 5 * (l + 1) < n_ph else None for l in range(nl)]
+    rep["layer_us_timeline"] = [round(x, 2) for x in per_layer if x is not None]
+    rep["phase_entry_gaps_us"] = {nm: round(float(sum((t_in[5 * l + k + 1] - t_in[5 * l + k]) for l in range(1, nl)) / max(nl - 1, 1)), 2)
+                                  for k, nm in enumerate(names)}   # entry of a phase to entry of the next one
+    rep["output_phase_us_timeline"] = round(t_end - float(t_in[n_ph - 1]), 2)
     rep["layer_us"] = round(sum(rep["phases"][nm]["total"][0] for nm in names), 2)
     print(json.dumps({k: v for k, v in rep.items() if k != "phases"}))
     for nm, d in rep["phases"].items():

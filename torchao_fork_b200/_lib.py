@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libao_b200.so")
+# AO_B200_LIB: another build of the SAME library (A/B measurements, benchmarks/ab_build.sh); never a different implementation
+LIB_PATH = os.environ.get("AO_B200_LIB") or os.path.join(_HERE, "lib", "libao_b200.so")
 
 _vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
 

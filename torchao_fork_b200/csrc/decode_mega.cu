@@ -41,6 +41,22 @@
 
 #include "common.cuh"
 
+// build-time A/B switches (benchmarks/ab_build.sh)
+#ifndef AO_MEGA_POLL_SLEEP
+#define AO_MEGA_POLL_SLEEP 0    // ns between two polls of a packet that has not arrived
+#endif
+#ifndef AO_MEGA_INLINE_PHASES
+#define AO_MEGA_INLINE_PHASES 1  // staging / main loop / attention inlined into the consumers' phase loop (no ABI calls on the hand-over path)
+#endif
+#if AO_MEGA_INLINE_PHASES
+#define AO_PHASE_FN __device__ __forceinline__
+#else
+#define AO_PHASE_FN __device__ __noinline__
+#endif
+#ifndef AO_MEGA_BATCH_SWEEP
+#define AO_MEGA_BATCH_SWEEP 0   // a sweep has all its packet loads in flight before it looks at the first tag
+#endif
+
 namespace ao {
 namespace mega {
 
@@ -82,7 +98,7 @@ struct alignas(16) LayerPtrs {      // 112 bytes
 };
 enum { K_WQKV = 0, K_ATTN = 1, K_WO = 2, K_W13 = 3, K_W2 = 4, K_OUT = 5, kKinds = 6 };
 struct Kind {
-  uint32_t in_off;                // packet offset in the exchange region: IN_PK input, IN_H deltas [world][Kx / 2], ATTN qkv
+  uint32_t in_off;                // packet offset in the exchange region: IN_PK input, IN_H deltas [world (+ 1: their sum)][Kx / 2], ATTN qkv
   uint32_t out_off;               // packet offset of the output (OUT_DELTA: + rank * N_out / 2 in every peer's region)
   uint32_t aux_off;               // ATTN: split partials
   int type, in_kind, out_kind;
@@ -127,7 +143,8 @@ struct Params {
   uint32_t off_x, off_S, off_red, off_h, off_misc, off_lay;
   unsigned long long timeout_ns;
   unsigned long long* trace;      // optional: [n_cta][n_phases][8] clock64 stamps (benchmarks/mega_trace.py)
-  int dbg;                        // profiling switches (AO_B200_MEGA_DEBUG): 1 = main loops skip the math (stream only), 2 = count slow polls
+  int tp_reduce;                  // world > 1: sum the ranks' partial outputs once per rank (reduce_slice) instead of in every CTA
+  int dbg;                        // profiling switches (AO_B200_MEGA_DEBUG): 1 = main loops skip the math (stream only), 2 = count slow polls, 4 = no evict-first hint on the weight stream
 };
 
 // wait context at the start of dynamic shared memory: reachable from every (non-inlined) function without arguments
@@ -196,6 +213,17 @@ __device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void bulk_g2s_u(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                "r"(bytes), "r"(bar) : "memory");
+}
+// The weight stream (4 GB per token through a 126 MB L2) is marked evict-first: what the kernel re-reads every layer or
+// every token — its own code, the exchange packets, the norm weights, the K / V tiles — then stays resident in L2.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
 }
 // packets: single 8-byte accesses that bypass the (incoherent) L1.  `.sys` scope: the exchange regions are also written
 // by NVLink peers; on local memory it costs the same as `.gpu`.
@@ -279,6 +307,9 @@ __device__ __noinline__ uint32_t poll_pk_slow(const uint64_t* p, uint32_t tag) {
   for (;;) {
     const uint64_t v = ld_pk(p);
     if ((uint32_t)(v >> 32) == tag) return (uint32_t)v;
+#if AO_MEGA_POLL_SLEEP > 0
+    __nanosleep(AO_MEGA_POLL_SLEEP);
+#endif
     if ((++n & 63u) == 0) {
       if (aborted()) return 0u;
       if (globaltimer() - t0 > lim) {
@@ -305,6 +336,9 @@ __device__ __noinline__ uint4 poll_chunk_slow(const uint64_t* p, uint32_t tag) {
     if (((uint32_t)(a.x >> 32) == tag) & ((uint32_t)(a.y >> 32) == tag) & ((uint32_t)(b.x >> 32) == tag) &
         ((uint32_t)(b.y >> 32) == tag))
       return make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
+#if AO_MEGA_POLL_SLEEP > 0
+    __nanosleep(AO_MEGA_POLL_SLEEP);
+#endif
     if ((++n & 63u) == 0) {
       if (aborted()) break;
       if (globaltimer() - t0 > lim) {
@@ -320,6 +354,29 @@ __device__ __forceinline__ uint4 poll_chunk(const uint64_t* p, uint32_t tag) {
   const bool ok = ((uint32_t)(a.x >> 32) == tag) & ((uint32_t)(a.y >> 32) == tag) & ((uint32_t)(b.x >> 32) == tag) &
                   ((uint32_t)(b.y >> 32) == tag);
   if (ok) return make_uint4((uint32_t)a.x, (uint32_t)a.y, (uint32_t)b.x, (uint32_t)b.y);
+  return poll_chunk_slow(p, tag);
+}
+// the same in two halves, so that a sweep can have all its loads in flight before it looks at the first tag
+struct ChunkLd {
+  ulonglong2 a, b;
+};
+__device__ __forceinline__ ChunkLd chunk_load(const uint64_t* p) {
+  ChunkLd c;
+#if !AO_MEGA_BATCH_SWEEP
+  c.a = c.b = make_ulonglong2(0ull, 0ull);
+  return c;
+#endif
+  c.a = ld_pk2(p);
+  c.b = ld_pk2(p + 2);
+  return c;
+}
+__device__ __forceinline__ uint4 chunk_take(const ChunkLd& c, const uint64_t* p, uint32_t tag) {
+#if !AO_MEGA_BATCH_SWEEP
+  return poll_chunk(p, tag);
+#endif
+  const bool ok = ((uint32_t)(c.a.x >> 32) == tag) & ((uint32_t)(c.a.y >> 32) == tag) & ((uint32_t)(c.b.x >> 32) == tag) &
+                  ((uint32_t)(c.b.y >> 32) == tag);
+  if (ok) return make_uint4((uint32_t)c.a.x, (uint32_t)c.a.y, (uint32_t)c.b.x, (uint32_t)c.b.y);
   return poll_chunk_slow(p, tag);
 }
 // Staging chunk of (round c, lane, warp): the chunks a warp stages are exactly the ones its main loop reads (warp w owns
@@ -420,6 +477,8 @@ __device__ __noinline__ void producer_loop(int pos, uint32_t ring_u, uint32_t ba
   const Bars bars = make_bars(bar0, stages);
   int slot = 0, rot = 0;
   uint32_t par = 1;
+  const uint64_t pol = l2_evict_first_policy();
+  const bool stream_hint = (p.dbg & 4) == 0;  // AO_B200_MEGA_DEBUG=4: weights with the default L2 policy (A/B)
   for (int i = 0; i < n_phases; ++i) {
     const Phase phv = get_phase(p, i);
     const Phase* ph = &phv;
@@ -438,8 +497,13 @@ __device__ __noinline__ void producer_loop(int pos, uint32_t ring_u, uint32_t ba
           bar_wait(bars.empty + 8u * slot, par, 8u);
           const uint32_t sz_bytes = (uint32_t)(cnt * 64 / G) * 64u;
           bar_expect_tx(bars.full + 8u * slot, (uint32_t)(cnt * 512) + sz_bytes);
-          bulk_g2s_u(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), bars.full + 8u * slot);
-          bulk_g2s_u(dst + kStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, bars.full + 8u * slot);
+          if (stream_hint) {
+            bulk_g2s_hint(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), bars.full + 8u * slot, pol);
+            bulk_g2s_hint(dst + kStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, bars.full + 8u * slot, pol);
+          } else {
+            bulk_g2s_u(dst, wrow + (int64_t)kt0 * 512, (uint32_t)(cnt * 512), bars.full + 8u * slot);
+            bulk_g2s_u(dst + kStageW, srow + (int64_t)(kt0 * 64 / G) * 16, sz_bytes, bars.full + 8u * slot);
+          }
           if (++slot == stages) {
             slot = 0;
             par ^= 1u;
@@ -685,11 +749,42 @@ __device__ __forceinline__ float finish_stats(const float* part, int lane, int w
   return __uint_as_float((uint32_t)(e + 127) << 23);
 }
 
-// IN_H: h += sum over ranks of the published deltas (h stays in shared memory; rank order; world == 1: one packed bf16x2
+// world > 1: every rank sums the partial outputs of all ranks ONCE, its CTAs taking a slice of the vector each, and
+// publishes the bf16 sums in a local slot behind the ranks' slots; the sweep then reads one slot, as at world == 1.  (The
+// first version had every CTA read all `world` slots: 8 x 32 KB x 148 CTAs out of L2 per hand-over at world 8 — 6 us.)
+// One thread per (chunk, rank); butterfly sum over the ranks (every lane ends with the same bits; every rank computes
+// the same tree over the same packets, so the ranks stay bit-identical); bf16(sum) is what all_reduce(bf16) gives.
+__device__ __noinline__ void reduce_slice(const uint64_t* in_pk, int n_chunks, uint32_t tag_in) {
+  const Params& p = sparams();
+  const int world = p.world, tid = threadIdx.x;
+  const int sh = 31 - __clz(world);
+  const int cpc = (n_chunks + p.n_cta - 1) / p.n_cta;
+  if (((tid & ~31) >> sh) >= cpc) return;  // warp-uniform
+  const int j = tid >> sh, r = tid & (world - 1);
+  const int ci = (int)blockIdx.x * cpc + j;
+  const bool on = j < cpc && ci < n_chunks;
+  float f[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) f[e] = 0.f;
+  if (on) unpack8(poll_chunk(in_pk + (size_t)r * (size_t)(n_chunks * 4) + ci * 4, tag_in), f);
+  for (int o = 1; o < world; o <<= 1) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] += __shfl_xor_sync(0xffffffffu, f[e], o);
+  }
+  if (on && r == 0) {
+    uint64_t* dst = const_cast<uint64_t*>(in_pk) + (size_t)world * (size_t)(n_chunks * 4) + ci * 4;
+    const uint64_t t = (uint64_t)tag_in << 32;
+    const uint64_t a = cvt_bf2(f[0], f[1]) | t, b = cvt_bf2(f[2], f[3]) | t, c = cvt_bf2(f[4], f[5]) | t, d = cvt_bf2(f[6], f[7]) | t;
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst), "l"(a), "l"(b) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst + 2), "l"(c), "l"(d) : "memory");
+  }
+}
+
+// IN_H: h += the published delta (world > 1: the sum slot, see reduce_slice; h stays in shared memory; one packed bf16x2
 // add == bf16(h + d) exactly), then RMSNorm.forward (model.py:498-503): bf16(bf16(h * rsqrt(mean(h^2) + eps)) * w).
 // The norm weights are requested BEFORE the wait (a DRAM miss, once per token).  NCH = chunks of 8 per thread (K <= 4096 NCH).
 template <int G, int NCH>
-__device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_bfloat16* norm_w_p, float inv_k,
+AO_PHASE_FN void stage_h(int n_chunks, uint32_t in_off, const __nv_bfloat16* norm_w_p, float inv_k,
                                      int i, uint32_t tag_in, uint64_t cnt_target, float* row_scale_slot, uint32_t x_u,
                                      uint32_t S_u, uint4* h_s, float* part) {
   const Params& p = sparams();
@@ -697,7 +792,6 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
   const uint32_t limb_row = (uint32_t)n_chunks * 8u + 32u;
   const uint64_t* in_pk = in_off == kNone ? nullptr : p.xchg[p.rank] + in_off;
   const uint4* norm_w = reinterpret_cast<const uint4*>(norm_w_p);
-  const int world = p.world;
   uint4 wn[NCH], hv[NCH];
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
@@ -705,29 +799,45 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
     wn[c] = ci < n_chunks ? __ldg(norm_w + ci) : make_uint4(0u, 0u, 0u, 0u);
     hv[c] = make_uint4(0u, 0u, 0u, 0u);
   }
-  if (tid == 0) {
-    stamp(p.trace, p.n_phases, i, 0);
-    if (i > 0) wait_counter(p.counter, cnt_target);
+  if (tid == 0) stamp(p.trace, p.n_phases, i, 0);
+  int n_slot = p.world;
+  if (in_pk != nullptr && p.tp_reduce) {  // the first warps out of their main loop sum this CTA's slice of the partials
+    reduce_slice(in_pk, n_chunks, tag_in);
+    in_pk += (size_t)p.world * (size_t)(n_chunks * 4);  // the sum slot
+    n_slot = 1;
   }
+  if (tid == 0 && i > 0) wait_counter(p.counter, cnt_target);
   named_bar_sync(1, kCT);  // B1: phase i - 1 is published; every consumer warp of this CTA has left its main loop
   if (tid == 0) stamp(p.trace, p.n_phases, i, 1);
   float ss = 0.f;
   uint32_t am2 = 0u;  // packed max |bf16(h w)|
+  ChunkLd l0[NCH], l1[NCH];  // slot 0 (world 1; or the sum slot) and slot 1 (world 2 without reduce_slice): loads in flight first
+  if (in_pk != nullptr) {
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int ci = stage_chunk(c, lane, warp);
+      if (ci < n_chunks) {
+        l0[c] = chunk_load(in_pk + ci * 4);
+        if (n_slot > 1) l1[c] = chunk_load(in_pk + (size_t)(n_chunks * 4) + ci * 4);
+      }
+    }
+  }
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
     const int ci = stage_chunk(c, lane, warp);
     if (ci < n_chunks) {
       uint4 h = h_s[ci];
       if (in_pk != nullptr) {
-        if (world == 1) {
-          const uint4 d = poll_chunk(in_pk + ci * 4, tag_in);
+        const uint4 d = chunk_take(l0[c], in_pk + ci * 4, tag_in);
+        if (n_slot == 1) {
           h = make_uint4(bf2_add(h.x, d.x), bf2_add(h.y, d.y), bf2_add(h.z, d.z), bf2_add(h.w, d.w));
-        } else {
-          float acc[8], hf[8];
+        } else {  // world 2: summing both slots here is cheaper than the extra hand-over of reduce_slice (measured)
+          float acc[8], hf[8], df[8];
+          unpack8(d, acc);
+          unpack8(chunk_take(l1[c], in_pk + (size_t)(n_chunks * 4) + ci * 4, tag_in), df);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-          for (int r = 0; r < world; ++r) {
-            float df[8];
+          for (int e = 0; e < 8; ++e) acc[e] += df[e];
+          for (int r = 2; r < n_slot; ++r) {  // (AO_B200_MEGA_TP_REDUCE=0 at world > 2)
             unpack8(poll_chunk(in_pk + (size_t)r * (n_chunks * 4) + ci * 4, tag_in), df);
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[e] += df[e];
@@ -784,7 +894,7 @@ __device__ __noinline__ void stage_h(int n_chunks, uint32_t in_off, const __nv_b
 
 // IN_PK: the packets of the previous phase as they are.  The thread keeps its chunks in registers between the two passes.
 template <int G, int NCH>
-__device__ __noinline__ void stage_x(int n_chunks, uint32_t in_off, int i, uint32_t tag_in, uint64_t cnt_target,
+AO_PHASE_FN void stage_x(int n_chunks, uint32_t in_off, int i, uint32_t tag_in, uint64_t cnt_target,
                                      float* row_scale_slot, uint32_t x_u, uint32_t S_u, float* part) {
   const Params& p = sparams();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -798,13 +908,22 @@ __device__ __noinline__ void stage_x(int n_chunks, uint32_t in_off, int i, uint3
   if (tid == 0) stamp(p.trace, p.n_phases, i, 1);
   uint4 xv[NCH];
   uint32_t am2 = 0u;
+  {
+    // every load of the sweep is in flight before the first tag is looked at: one L2 round trip, not NCH of them
+    ChunkLd ld[NCH];
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    const int ci = stage_chunk(c, lane, warp);
-    xv[c] = make_uint4(0u, 0u, 0u, 0u);
-    if (ci < n_chunks) {
-      xv[c] = poll_chunk(in_pk + ci * 4, tag_in);
-      am2 = bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(am2, xv[c].x), xv[c].y), xv[c].z), xv[c].w);
+    for (int c = 0; c < NCH; ++c) {
+      const int ci = stage_chunk(c, lane, warp);
+      if (ci < n_chunks) ld[c] = chunk_load(in_pk + ci * 4);
+    }
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int ci = stage_chunk(c, lane, warp);
+      xv[c] = make_uint4(0u, 0u, 0u, 0u);
+      if (ci < n_chunks) {
+        xv[c] = chunk_take(ld[c], in_pk + ci * 4, tag_in);
+        am2 = bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(bf2_absmax_nan(am2, xv[c].x), xv[c].y), xv[c].z), xv[c].w);
+      }
     }
   }
   if (tid == 0) stamp(p.trace, p.n_phases, i, 7);
@@ -876,7 +995,7 @@ __device__ __forceinline__ void stage_math(const uint4 wa, const uint4 wb, const
 // loads are unconditional — a warp past the end of a short stage reads stale bytes it never uses).
 // Returns the ring state (slot | parity << 8).
 template <int G, bool XREG>
-__device__ __noinline__ uint32_t gemv_main(uint32_t ring_u, uint32_t bar0, int stages, int KT, int n_my, uint32_t x_u,
+AO_PHASE_FN uint32_t gemv_main(uint32_t ring_u, uint32_t bar0, int stages, int KT, int n_my, uint32_t x_u,
                                            uint32_t limb_row, uint32_t S_u, uint32_t red_u, uint32_t state, uint32_t li,
                                            int dbg) {
   using GE = Geom<G>;
@@ -1003,7 +1122,7 @@ __device__ __forceinline__ uint32_t movmatrix_t(uint32_t a) {
 }
 
 template <int GQ>
-__device__ __noinline__ uint32_t attention_phase(__nv_bfloat16* k_cache, __nv_bfloat16* v_cache, __nv_bfloat16* k_pad,
+AO_PHASE_FN uint32_t attention_phase(__nv_bfloat16* k_cache, __nv_bfloat16* v_cache, __nv_bfloat16* k_pad,
                                                  __nv_bfloat16* v_pad, uint32_t in_off, uint32_t out_off, uint32_t aux_off, int i,
                                                  int pos, uint32_t tag_in, uint64_t cnt_target, uint32_t ring_u,
                                                  uint32_t slot_bytes, uint32_t bar0, uint8_t* x_s, uint32_t state) {
@@ -1455,12 +1574,13 @@ static Offsets xchg_layout(const ao_b200_mega_model& m) {
   Offsets o;
   const uint32_t qkv_n = (uint32_t)(m.n_head + 2 * m.n_kv_head) * 128u;
   auto al = [](uint32_t v) { return (v + 15u) & ~15u; };  // 128-byte granules
+  const uint32_t slots = m.world > 1 ? (uint32_t)m.world + 1u : 1u;  // the ranks' partial sums + their local sum
   uint32_t off = 0;
   o.qkv = off; off += al(qkv_n / 2);
   o.att = off; off += al((uint32_t)m.n_head * 128u / 2);
-  o.d1 = off; off += al((uint32_t)m.world * (uint32_t)m.dim / 2);
+  o.d1 = off; off += al(slots * (uint32_t)m.dim / 2);
   o.mid = off; off += al((uint32_t)m.inter / 2);
-  o.d2 = off; off += al((uint32_t)m.world * (uint32_t)m.dim / 2);
+  o.d2 = off; off += al(slots * (uint32_t)m.dim / 2);
   o.aux = off; off += al((uint32_t)m.n_head * (uint32_t)(m.n_cta / (m.n_kv_head > 0 ? m.n_kv_head : 1) + 1) * kPartStride);
   o.total = off;
   return o;
@@ -1473,7 +1593,7 @@ static int check_model(const ao_b200_mega_model* m) {
   AO_CHECK_ARG(gq == 1 || gq == 2 || gq == 4 || gq == 8);
   AO_CHECK_ARG(m->dim % 128 == 0 && m->inter % 128 == 0 && m->vocab > 0);
   if (m->dim > 8192 || m->inter > 32768 || m->n_head * 128 > 32768) return AO_B200_ERR_UNSUPPORTED;  // staging: <= 2 / 8 chunks of 8 per thread
-  AO_CHECK_ARG(m->world >= 1 && m->world <= kMaxWorld && m->rank >= 0 && m->rank < m->world);
+  AO_CHECK_ARG(m->world >= 1 && m->world <= kMaxWorld && (m->world & (m->world - 1)) == 0 && m->rank >= 0 && m->rank < m->world);
   AO_CHECK_ARG(m->emb && m->freqs && m->tok && m->pos && m->logits && m->state && m->out_packed && m->out_sz && m->out_norm);
   AO_CHECK_ARG(m->max_seq > 0 && m->n_kv_head <= m->n_cta);
   for (int r = 0; r < m->world; ++r) AO_CHECK_ARG(m->xchg[r] != nullptr);
@@ -1586,6 +1706,8 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   {
     static const int dbg = []() { const char* e = std::getenv("AO_B200_MEGA_DEBUG"); return e ? std::atoi(e) : 0; }();
     p.dbg = dbg;
+    static const int tpr = []() { const char* e = std::getenv("AO_B200_MEGA_TP_REDUCE"); return e ? std::atoi(e) : -1; }();
+    p.tp_reduce = m->world > 1 && (tpr >= 0 ? tpr != 0 : m->world >= 4);
     static const int gate_env = []() { const char* e = std::getenv("AO_B200_MEGA_GATE"); return e ? std::atoi(e) : 32; }();
     const int gate = gate_env < 0 ? 0 : (gate_env > m->n_cta - 1 ? m->n_cta - 1 : gate_env);
     for (int k = 0; k < kKinds; ++k) p.kinds[k].gate = gate;
