@@ -209,3 +209,4 @@ def test_mega_gqa_group_of_eight_and_odd_layer_count():
     torch.cuda.synchronize()
     assert eng.mega_status() == 0
     assert _sqnr(ref, eng.logits[0]) > 30.0
+

@@ -603,21 +603,26 @@ __device__ __noinline__ void epilogue_loop(int pos, uint32_t step, uint32_t red_
       } else {
         const uint32_t o0 = float_to_bf16_bits(v0), o1 = float_to_bf16_bits(v1);
         const uint32_t o0n = __shfl_down_sync(0xffffffffu, o0, 4), o1n = __shfl_down_sync(0xffffffffu, o1, 4);
-        const int n0 = 16 * strip + g;
-        if (c == 0 && (g & 1) == 0) {
-          const uint32_t d0 = o0 | (o0n << 16), d1 = o1 | (o1n << 16);
-          if (out_kind == OUT_PK) {
+        const uint32_t d0 = o0 | (o0n << 16), d1 = o1 | (o1n << 16);  // valid on lanes c == 0, g even (lanes 0, 8, 16, 24)
+        if (out_kind == OUT_PK || p.world == 1) {
+          const int n0 = 16 * strip + g;
+          if (c == 0 && (g & 1) == 0) {
             if (n0 < N_out) st_pk(xq + out_off + (n0 >> 1), d0, tag);
             if (n0 + 8 < N_out) st_pk(xq + out_off + ((n0 + 8) >> 1), d1, tag);
-          } else {  // OUT_DELTA: this rank's slot in every rank's region (own first, then staggered over the peers)
-            const uint32_t off = out_off + (uint32_t)p.rank * (uint32_t)(N_out >> 1);
-            for (int d = 0; d < p.world; ++d) {
-              int r = p.rank + d;
-              if (r >= p.world) r -= p.world;
-              uint64_t* dst = p.xchg[r] + off;
-              if (n0 < N_out) st_pk(dst + (n0 >> 1), d0, tag);
-              if (n0 + 8 < N_out) st_pk(dst + ((n0 + 8) >> 1), d1, tag);
-            }
+          }
+        } else {
+          // OUT_DELTA, world > 1: this rank's slot in every rank's region.  The 4 packet pairs x 8 ranks are spread over
+          // the 32 lanes (one destination rank per lane group) instead of 16 stores in a row from 4 lanes: the stores to
+          // the peers leave in one issue slot each, and the arrival count is not held back by them.
+          const int src = (lane & 3) * 8, rd = lane >> 2;  // source lane (row pair g = 2 (lane & 3)), destination rank offset
+          const uint32_t e0 = __shfl_sync(0xffffffffu, d0, src), e1 = __shfl_sync(0xffffffffu, d1, src);
+          const int n0 = 16 * strip + 2 * (lane & 3);
+          if (rd < p.world) {
+            int r = p.rank + rd;  // own region first, then staggered over the peers
+            if (r >= p.world) r -= p.world;
+            uint64_t* dst = p.xchg[r] + out_off + (uint32_t)p.rank * (uint32_t)(N_out >> 1);
+            if (n0 < N_out) st_pk(dst + (n0 >> 1), e0, tag);
+            if (n0 + 8 < N_out) st_pk(dst + ((n0 + 8) >> 1), e1, tag);
           }
         }
       }
@@ -1410,7 +1415,114 @@ AO_PHASE_FN uint32_t attention_phase(__nv_bfloat16* k_cache, __nv_bfloat16* v_ca
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
-template <int G>
+// ------------------------------------------------------------------------------------------------ consumers: one phase
+struct ConsumerCtx {
+  uint32_t tag0;
+  uint64_t cnt0;
+  int pos;
+  uint32_t ring_u, bar0, red_u, x_u, S_u;
+  uint8_t* x_s;
+  uint4* h_s;
+  float* part;
+  float* row_scale;
+  uint32_t state;  // ring slot | parity << 8
+  uint32_t li;     // strips handed to the epilogue warp so far
+  int gphase, rot;
+};
+
+// phase i = kind KIND of layer l (the shape-specialised loop: no division, no select on the kind)
+template <int KIND>
+__device__ __forceinline__ Phase get_phase_k(const Params& p, int l, int i) {
+  extern __shared__ __align__(128) uint8_t smem_mega[];
+  const LayerPtrs* lay_s = reinterpret_cast<const LayerPtrs*>(smem_mega + p.off_lay);
+  const Kind& k = p.kinds[KIND];
+  Phase ph;
+  ph.in_off = (i == 0) ? kNone : k.in_off;
+  ph.out_off = k.out_off; ph.aux_off = k.aux_off;
+  ph.type = k.type; ph.in_kind = k.in_kind; ph.out_kind = k.out_kind;
+  ph.KT = k.KT; ph.n_strips = k.n_strips; ph.N_out = k.N_out; ph.Kx = k.Kx; ph.rot_inc = k.rot_inc; ph.gate = k.gate;
+  ph.packed = nullptr; ph.sz = nullptr; ph.norm_w = nullptr; ph.out_plain = nullptr; ph.k_cache = nullptr; ph.v_cache = nullptr;
+  ph.k_pad = nullptr; ph.v_pad = nullptr;
+  if constexpr (KIND == K_OUT) {
+    ph.norm_w = p.out_norm;
+  } else if constexpr (KIND == K_ATTN) {
+    ph.k_cache = lay_s[l].kc; ph.v_cache = lay_s[l].vc; ph.k_pad = lay_s[l].kp; ph.v_pad = lay_s[l].vp;
+  } else if constexpr (KIND == K_WQKV) {
+    ph.norm_w = lay_s[l].norm[0];
+  } else if constexpr (KIND == K_W13) {
+    ph.norm_w = lay_s[l].norm[1];
+  }
+  return ph;  // (the consumers need neither the weight pointers nor the output pointer: producer / epilogue warp)
+}
+
+template <int G, int GQ>
+__device__ __forceinline__ void consumer_attn(const Phase& ph, int i, ConsumerCtx& cx) {
+  const Params& p = sparams();
+  const uint32_t tag_in = cx.tag0 + (uint32_t)i;
+  const uint64_t cnt_target = cx.cnt0 + (uint64_t)i * (uint64_t)p.n_cta - (uint64_t)ph.gate;
+  cx.state = attention_phase<GQ>(ph.k_cache, ph.v_cache, ph.k_pad, ph.v_pad, ph.in_off, ph.out_off, ph.aux_off, i, cx.pos, tag_in,
+                                 cnt_target, cx.ring_u, Geom<G>::kSlotBytes, cx.bar0, cx.x_s, cx.state);
+}
+
+// INK / NCH: the phase's input kind and staging width when known at compile time (-1 / 0: decided here)
+template <int G, int INK, int NCH>
+__device__ __forceinline__ void consumer_gemv(const Phase& ph, int i, ConsumerCtx& cx) {
+  const Params& p = sparams();
+  const int n_cta = p.n_cta;
+  const uint32_t tag_in = cx.tag0 + (uint32_t)i;  // tag of phase i - 1
+  // arrivals to wait for before sweeping: all but `gate` — the stragglers' packets are polled directly, which takes one
+  // L2 round trip off the critical path (measured: profiles/)
+  const uint64_t cnt_target = cx.cnt0 + (uint64_t)i * (uint64_t)n_cta - (uint64_t)ph.gate;
+  const int KT = ph.KT;
+  const int n_chunks = KT * 8;  // Kp == Kx in this kernel (check_model)
+  const int nch = NCH > 0 ? NCH : ((KT + kStageTiles - 1) / kStageTiles + 1) / 2;  // stages of the strip, two per staging round
+  float* rs = cx.row_scale + (cx.gphase & 1);
+  float* part_g = cx.part + (cx.gphase & 1) * 2 * kC;
+  bool in_h;
+  if constexpr (INK < 0) in_h = ph.in_kind == IN_H; else in_h = INK == IN_H;
+  if (in_h) {
+    if constexpr (INK < 0 || INK == IN_H) {
+      const float inv_k = 1.0f / (float)ph.Kx;
+      if constexpr (NCH == 0) {
+        if (nch <= 1) stage_h<G, 1>(n_chunks, ph.in_off, ph.norm_w, inv_k, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, cx.h_s, part_g);
+        else stage_h<G, 2>(n_chunks, ph.in_off, ph.norm_w, inv_k, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, cx.h_s, part_g);
+      } else {
+        stage_h<G, (NCH <= 1 ? 1 : 2)>(n_chunks, ph.in_off, ph.norm_w, inv_k, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, cx.h_s, part_g);
+      }
+    }
+  } else {
+    if constexpr (INK < 0 || INK == IN_PK) {
+      if constexpr (NCH == 0) {
+        if (nch <= 1) stage_x<G, 1>(n_chunks, ph.in_off, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, part_g);
+        else if (nch <= 2) stage_x<G, 2>(n_chunks, ph.in_off, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, part_g);
+        else if (nch <= 4) stage_x<G, 4>(n_chunks, ph.in_off, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, part_g);
+        else stage_x<G, 8>(n_chunks, ph.in_off, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, part_g);
+      } else {
+        stage_x<G, NCH>(n_chunks, ph.in_off, i, tag_in, cnt_target, rs, cx.x_u, cx.S_u, part_g);
+      }
+    }
+  }
+  int s0, s1;
+  strip_range((int)blockIdx.x, n_cta, ph.n_strips, cx.rot, s0, s1);
+  cx.rot = next_rot(cx.rot, ph.rot_inc, n_cta);
+  const uint32_t limb_row = (uint32_t)KT * 64u + 32u;
+  bool xreg;
+  if constexpr (NCH == 0) xreg = KT <= 2 * kStageTiles; else xreg = NCH == 1;
+  if (xreg) {
+    if constexpr (NCH <= 1)
+      cx.state = gemv_main<G, true>(cx.ring_u, cx.bar0, p.stages, KT, s1 - s0, cx.x_u, limb_row, cx.S_u, cx.red_u, cx.state, cx.li, p.dbg);
+  } else {
+    if constexpr (NCH != 1)
+      cx.state = gemv_main<G, false>(cx.ring_u, cx.bar0, p.stages, KT, s1 - s0, cx.x_u, limb_row, cx.S_u, cx.red_u, cx.state, cx.li, p.dbg);
+  }
+  cx.li += (uint32_t)(s1 - s0);
+  if (threadIdx.x == 0) stamp(p.trace, p.n_phases, i, 3);
+  ++cx.gphase;
+}
+
+// GQ_T == 0: any shape.  Otherwise the model's shape class is a template argument: q heads per kv head, and the chunks of
+// 8 activations per thread when staging dim (NH_T), the attention output (NWO_T) and the intermediate vector (NW2_T).
+template <int G, int GQ_T, int NH_T, int NWO_T, int NW2_T>
 __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_constant__ Params p_arg) {
   using GE = Geom<G>;
   constexpr int kStageBytes = GE::kSlotBytes;
@@ -1474,57 +1586,42 @@ __global__ void __launch_bounds__(kThreads, 1) decode_mega_kernel(const __grid_c
     const uint4* erow = reinterpret_cast<const uint4*>(p.emb + tok * (int64_t)p.dim);
     for (int ci = tid; ci < p.dim / 8; ci += kCT) h_s[ci] = __ldg(erow + ci);
   }
-  const uint32_t tag0 = step * (uint32_t)n_phases;                              // phase i publishes with tag tag0 + i + 1
-  const uint64_t cnt0 = (uint64_t)step * (uint64_t)n_phases * (uint64_t)n_cta;  // counter before this launch
-  const int GQ = p.H / p.Hkv;
-  uint32_t state = 0;  // ring slot | parity << 8
-  uint32_t li = 0;
-  int gphase = 0, rot = 0;
-  for (int i = 0; i < n_phases; ++i) {
-    const Phase phv = get_phase(p, i);
-    const Phase* ph = &phv;
-    const uint32_t tag_in = tag0 + (uint32_t)i;  // tag of phase i - 1
-    // arrivals to wait for before sweeping: all but `gate` — the stragglers' packets are polled directly, which takes one
-    // L2 round trip off the critical path (measured: profiles/)
-    const uint64_t cnt_target = cnt0 + (uint64_t)i * (uint64_t)n_cta - (uint64_t)ph->gate;
-    if (ph->type != PH_GEMV) {
-      switch (GQ) {
-        case 1: state = attention_phase<1>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        case 2: state = attention_phase<2>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        case 4: state = attention_phase<4>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-        default: state = attention_phase<8>(ph->k_cache, ph->v_cache, ph->k_pad, ph->v_pad, ph->in_off, ph->out_off, ph->aux_off, i, pos, tag_in, cnt_target, ring_u, kStageBytes, bar0, x_s, state); break;
-      }
-      continue;
-    }
-    {
-      const int n_chunks = ph->KT * 8;  // Kp == Kx in this kernel (check_model)
-      const int nch = ((ph->KT + kStageTiles - 1) / kStageTiles + 1) / 2;  // stages of the strip, two per staging round
-      float* rs = row_scale + (gphase & 1);
-      float* part_g = part + (gphase & 1) * 2 * kC;
-      const uint32_t x_u = smem_u32(x_s), S_u = smem_u32(S_s);
-      if (ph->in_kind == IN_H) {
-        const float inv_k = 1.0f / (float)ph->Kx;
-        if (nch <= 1) stage_h<G, 1>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part_g);
-        else stage_h<G, 2>(n_chunks, ph->in_off, ph->norm_w, inv_k, i, tag_in, cnt_target, rs, x_u, S_u, h_s, part_g);
+  ConsumerCtx cx;
+  cx.tag0 = step * (uint32_t)n_phases;                              // phase i publishes with tag tag0 + i + 1
+  cx.cnt0 = (uint64_t)step * (uint64_t)n_phases * (uint64_t)n_cta;  // counter before this launch
+  cx.pos = pos;
+  cx.ring_u = ring_u; cx.bar0 = bar0; cx.red_u = red_u;
+  cx.x_s = x_s; cx.x_u = smem_u32(x_s); cx.S_u = smem_u32(S_s);
+  cx.h_s = h_s; cx.part = part; cx.row_scale = row_scale;
+  cx.state = 0u; cx.li = 0u; cx.gphase = 0; cx.rot = 0;
+  if constexpr (GQ_T == 0) {
+    // any shape: one dispatcher per phase (every phase switch jumps through it: instruction-cache misses on the critical path)
+    const int GQ = p.H / p.Hkv;
+    for (int i = 0; i < n_phases; ++i) {
+      const Phase ph = get_phase(p, i);
+      if (ph.type != PH_GEMV) {
+        switch (GQ) {
+          case 1: consumer_attn<G, 1>(ph, i, cx); break;
+          case 2: consumer_attn<G, 2>(ph, i, cx); break;
+          case 4: consumer_attn<G, 4>(ph, i, cx); break;
+          default: consumer_attn<G, 8>(ph, i, cx); break;
+        }
       } else {
-        if (nch <= 1) stage_x<G, 1>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
-        else if (nch <= 2) stage_x<G, 2>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
-        else if (nch <= 4) stage_x<G, 4>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
-        else stage_x<G, 8>(n_chunks, ph->in_off, i, tag_in, cnt_target, rs, x_u, S_u, part_g);
+        consumer_gemv<G, -1, 0>(ph, i, cx);
       }
     }
-    int s0, s1;
-    strip_range(b, n_cta, ph->n_strips, rot, s0, s1);
-    rot = next_rot(rot, ph->rot_inc, n_cta);
-    const int KT = ph->KT;
-    const uint32_t limb_row = (uint32_t)KT * 64u + 32u;
-    if (KT <= 2 * kStageTiles)
-      state = gemv_main<G, true>(ring_u, bar0, stages, KT, s1 - s0, smem_u32(x_s), limb_row, smem_u32(S_s), red_u, state, li, p.dbg);
-    else
-      state = gemv_main<G, false>(ring_u, bar0, stages, KT, s1 - s0, smem_u32(x_s), limb_row, smem_u32(S_s), red_u, state, li, p.dbg);
-    li += (uint32_t)(s1 - s0);
-    if (tid == 0) stamp(p.trace, n_phases, i, 3);
-    ++gphase;
+  } else {
+    // a known shape: the layer is straight-line code in execution order (see `variants` on the host side: measured, not used)
+    const int n_layer = p.n_layer;
+    for (int l = 0; l < n_layer; ++l) {
+      const int i = 5 * l;
+      consumer_gemv<G, IN_H, NH_T>(get_phase_k<K_WQKV>(p, l, i), i, cx);
+      consumer_attn<G, GQ_T>(get_phase_k<K_ATTN>(p, l, i + 1), i + 1, cx);
+      consumer_gemv<G, IN_PK, NWO_T>(get_phase_k<K_WO>(p, l, i + 2), i + 2, cx);
+      consumer_gemv<G, IN_H, NH_T>(get_phase_k<K_W13>(p, l, i + 3), i + 3, cx);
+      consumer_gemv<G, IN_PK, NW2_T>(get_phase_k<K_W2>(p, l, i + 4), i + 4, cx);
+    }
+    consumer_gemv<G, IN_H, NH_T>(get_phase_k<K_OUT>(p, n_layer, 5 * n_layer), 5 * n_layer, cx);
   }
 }
 
@@ -1713,16 +1810,30 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
     for (int k = 0; k < kKinds; ++k) p.kinds[k].gate = gate;
   }
   using KernelFn = void (*)(const Params);
+  struct Variant {
+    int G;
+    KernelFn fn;
+  };
+  // One kernel per group size, any shape.  (Instantiations per shape class — GQ_T / NH_T / NWO_T / NW2_T > 0: the layer as
+  // straight-line code in execution order, no dispatcher between the phases — were measured on Llama-3-8B / 70B: the
+  // consumers reach the next phase's wait 0.5 - 1 us earlier and wait that much longer, because the hand-over is bound by
+  // the slowest CTA's epilogue, not by the consumers' instruction path: 828 vs 833 tok/s.  Not instantiated.)
+  static const Variant variants[] = {
+      {32, decode_mega_kernel<32, 0, 0, 0, 0>},   {64, decode_mega_kernel<64, 0, 0, 0, 0>},
+      {128, decode_mega_kernel<128, 0, 0, 0, 0>}, {256, decode_mega_kernel<256, 0, 0, 0, 0>},
+  };
+  constexpr int kVariants = (int)(sizeof(variants) / sizeof(variants[0]));
   KernelFn kern = nullptr;
   int gi = 0;
-  switch (m->group_size) {
-    case 32: kern = decode_mega_kernel<32>; gi = 0; break;
-    case 64: kern = decode_mega_kernel<64>; gi = 1; break;
-    case 128: kern = decode_mega_kernel<128>; gi = 2; break;
-    default: kern = decode_mega_kernel<256>; gi = 3; break;
+  for (int v = 0; v < kVariants && kern == nullptr; ++v) {
+    if (variants[v].G == m->group_size) {
+      kern = variants[v].fn;
+      gi = v;
+    }
   }
+  if (kern == nullptr) return AO_B200_ERR_UNSUPPORTED;
   static const bool debug = std::getenv("AO_B200_DEBUG") != nullptr;
-  static bool attr_done[4] = {};
+  static bool attr_done[kVariants] = {};
   if (!attr_done[gi]) {
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
@@ -1742,7 +1853,7 @@ extern "C" int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void*
   // wait in the kernel is bounded — AO_B200_MEGA_COOP=0 selects it (a cooperative kernel node costs the serving loop
   // extra launch latency per token: profiles/).  The grid is checked against the occupancy either way.
   static const bool coop = []() { const char* e = std::getenv("AO_B200_MEGA_COOP"); return e ? std::atoi(e) != 0 : true; }();
-  static int max_ctas[4] = {0, 0, 0, 0};
+  static int max_ctas[kVariants] = {};
   if (max_ctas[gi] == 0) {
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev);
