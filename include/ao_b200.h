@@ -252,6 +252,17 @@ AO_B200_API int ao_b200_decode_attention_fused(const void* qkv, const void* freq
                                                int head_dim, int S, float scale, int n_split, void* workspace,
                                                int64_t workspace_bytes, void* stream);
 
+/* The same launch over an int8 KV cache — the decode side of AffineQuantizedKVCache (model.py:198-240): the new k (after
+ * RoPE) and v rows are quantized per token and head as _quantize_activation_per_token_absmax does
+ * (torchao/quantization/utils.py:152-182: symmetric, -127..127, eps 1e-5, bf16 scale; bit-exact with the reference's
+ * eager CUDA evaluation) and stored at *input_pos; the walk reads k_out = bf16(q * scale) for the older positions and
+ * the UNQUANTIZED new row (model.py:222-225, 230-232).  caches int8 [B][Hkv][S][128], scales bf16 [B][Hkv][S] (the
+ * reference's [B][Hkv][S][1]).  Workspace as for ao_b200_decode_attention_fused. */
+AO_B200_API int ao_b200_decode_attention_fused_q8(const void* qkv, const void* freqs_cis, const int32_t* input_pos,
+                                      void* k_cache, void* v_cache, void* k_scale, void* v_scale, void* out,
+                                      int B, int H, int Hkv, int head_dim, int S, float scale, int n_split,
+                                      void* workspace, int64_t workspace_bytes, void* stream);
+
 /* FeedForward gate (model.py:486): out = bf16( bf16(silu(gate)) * up ), gate_up bf16 [B][2*I] = [w1 x | w3 x]. */
 AO_B200_API int ao_b200_silu_mul(const void* gate_up, void* out, int64_t B, int64_t I, void* stream);
 

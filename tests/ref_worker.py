@@ -14,7 +14,11 @@ modes
               "group_size": G or None}
          out: the reference Transformer (torchao/_models/llama/model.py:243), optionally quantize_'d by the reference,
               run like generate.py:103-117: prefill logits [T][V], then n single-token steps fed with the argmax of its
-              own logits: logits [n][V], tokens [n + 1]
+              own logits: logits [n][V], tokens [n + 1].  "kv_cache_quantization": True builds the caches as
+              AffineQuantizedKVCache (model.py:198-240, 302-315).
+  kvq    in: {"k", "v": bf16 [B][H][T][D]}
+         out: AffineQuantizedKVCache.update (model.py:215-232) called once per position t = 0..T-1 with the rows of t:
+              k_cache / v_cache int8, k_cache_scale / v_cache_scale, and the k_out / v_out the LAST call returned
 """
 import sys
 
@@ -63,7 +67,8 @@ def run_model(inp):
     if inp.get("group_size"):
         quantize_(model, Int4WeightOnlyConfig(group_size=inp["group_size"]))
     with torch.device("cuda"):
-        model.setup_caches(max_batch_size=1, max_seq_length=inp["max_seq"])
+        model.setup_caches(max_batch_size=1, max_seq_length=inp["max_seq"],
+                           kv_cache_quantization=bool(inp.get("kv_cache_quantization")))
     prompt = inp["prompt"].cuda().view(1, -1)
     T = prompt.shape[1]
     with torch.no_grad():
@@ -79,12 +84,26 @@ def run_model(inp):
     return {"prefill_logits": prefill_logits, "step_logits": torch.stack(step_logits), "tokens": torch.tensor(tokens)}
 
 
+def run_kvq(inp):
+    from torchao._models.llama.model import AffineQuantizedKVCache
+
+    k, v = inp["k"].cuda(), inp["v"].cuda()
+    B, H, T, D = k.shape
+    with torch.device("cuda"):
+        cache = AffineQuantizedKVCache(B, T, H, D, scale_dtype=torch.bfloat16)
+    with torch.no_grad():
+        for t in range(T):
+            k_out, v_out = cache.update(torch.tensor([t], device="cuda"), k[:, :, t : t + 1], v[:, :, t : t + 1])
+    return {"k_cache": cache.k_cache.cpu(), "v_cache": cache.v_cache.cpu(), "k_cache_scale": cache.k_cache_scale.cpu(),
+            "v_cache_scale": cache.v_cache_scale.cpu(), "k_out": k_out.cpu(), "v_out": v_out.cpu()}
+
+
 if __name__ == "__main__":
     mode, fin, fout = sys.argv[1:4]
     import torchao
 
     assert "oracle/_ref" in torchao.__file__.replace("\\", "/"), f"not the reference install: {torchao.__file__}"
     inp = torch.load(fin, weights_only=True)
-    res = run_quant(inp) if mode == "quant" else run_model(inp)
+    res = {"quant": run_quant, "model": run_model, "kvq": run_kvq}[mode](inp)
     res["_torchao_file"] = torchao.__file__
     torch.save(res, fout)

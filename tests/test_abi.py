@@ -45,7 +45,7 @@ def test_version_and_argument_validation_without_a_gpu():
     if not os.path.exists(_lib.LIB_PATH):
         pytest.skip("libao_b200.so not built")
     L = _lib.lib()
-    assert L.ao_b200_abi_version() == 4
+    assert L.ao_b200_abi_version() == 5
     assert L.ao_b200_error_string(0) == b"ok"
     assert b"invalid" in L.ao_b200_error_string(1)
     # null pointers / bad shapes are rejected before any launch

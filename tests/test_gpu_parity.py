@@ -372,6 +372,44 @@ def test_aqt_mechanics():
     assert compute_error(y.float(), ysum).item() >= 40.0
 
 
+def test_moe_expert_stack_select_and_index():
+    """3-D expert weights [E, N, K] (reference: tensor_core_tiled_layout.py:283-294 `for moe quant`) and the two ops the
+    reference's MoE modules pick experts with — aten.select.int (dim 0) / aten.index.Tensor on the AQT
+    (affine_quantized_tensor_ops.py:519-562) and on the int4 impl (tensor_core_tiled_layout.py:363-372)."""
+    from torchao_fork_b200.dtypes import TensorCoreTiledLayout, to_affine_quantized_intx
+    from torchao_fork_b200.quantization.quant_primitives import MappingType, ZeroPointDomain
+    torch.manual_seed(0)
+    E, N, K, G = 4, 256, 512, 64
+    w3 = torch.randn(E, N, K, dtype=torch.bfloat16, device=DEV)
+    kw = dict(quant_min=0, quant_max=15, eps=1e-6, zero_point_dtype=torch.bfloat16, preserve_zero=False,
+              zero_point_domain=ZeroPointDomain.FLOAT, _layout=TensorCoreTiledLayout(8))
+    q3 = to_affine_quantized_intx(w3, MappingType.ASYMMETRIC, (1, 1, G), torch.int32, **kw)
+    assert q3.shape == (E, N, K) and q3.block_size == (1, 1, G)
+    assert q3.tensor_impl.packed_weight.shape == (E, N // 16, K // 64, 32, 4)
+    x = torch.randn(5, K, dtype=torch.bfloat16, device=DEV)
+    for e in range(E):
+        q2 = to_affine_quantized_intx(w3[e], MappingType.ASYMMETRIC, (1, G), torch.int32, **kw)
+        sel = q3[e]                                                      # aten.select.int
+        assert sel.shape == (N, K) and sel.block_size == (1, G)
+        assert torch.equal(sel.tensor_impl.packed_weight, q2.tensor_impl.packed_weight)
+        assert torch.equal(sel.tensor_impl.scale_and_zero, q2.tensor_impl.scale_and_zero)
+        assert torch.equal(torch.nn.functional.linear(x, sel), torch.nn.functional.linear(x, q2))
+    idx = torch.tensor([2, 0], device=DEV)
+    picked = q3[idx]                                                     # aten.index.Tensor
+    assert picked.shape == (2, N, K)
+    assert torch.equal(picked[0].tensor_impl.packed_weight, q3[2].tensor_impl.packed_weight)
+    assert torch.equal(picked[1].tensor_impl.scale_and_zero, q3[0].tensor_impl.scale_and_zero)
+    assert torch.equal(q3.dequantize()[1], q3[1].dequantize())
+    # from_plain with 3-D int_data == the stack of the per-expert constructions
+    data, scale, zero = q3.tensor_impl.get_plain()
+    assert data.shape == (E, N, K)
+    again = type(q3.tensor_impl).from_plain(data, scale, zero, TensorCoreTiledLayout(8))
+    assert torch.equal(again.packed_weight, q3.tensor_impl.packed_weight)
+    assert torch.equal(again.scale_and_zero, q3.tensor_impl.scale_and_zero)
+    with pytest.raises(AssertionError):
+        torch.ops.aten.select.int(q3, 1, 0)
+
+
 def test_opcheck():
     from torch.library import opcheck
     # the four utilities of the reference's own op tests (test/test_ops.py:300-307): test_aot_dispatch_dynamic is what

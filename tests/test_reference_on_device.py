@@ -178,3 +178,109 @@ def test_llama_decode_matches_the_reference_transformer(mega):
         top2 = r.topk(2).values
         if float(top2[0] - top2[1]) > 0.25:
             assert int(eng.logits[0].float().argmax()) == int(toks[i + 1]), f"step {i}: token differs from the reference's"
+
+
+def _kv_rows(B, H, T, D, seed):
+    g = torch.Generator().manual_seed(seed)
+    k = torch.randn(B, H, T, D, generator=g)
+    v = torch.randn(B, H, T, D, generator=g) * 3.0
+    k[0, 0, 1] = 0.0                      # a zero row: the scale clamps to eps
+    k[0, 0, 2] *= 1e4                     # large magnitudes
+    v[0, 0, 3] *= 1e-6                    # tiny magnitudes (below eps * 127)
+    k[0, 1, 4] = 0.5                      # constant row: every value lands on +127 / a tie
+    v[0, 1, 5, ::2] = -v[0, 1, 5, 1::2]   # symmetric pairs
+    return k.to(torch.bfloat16), v.to(torch.bfloat16)
+
+
+def test_int8_kv_cache_matches_the_reference_running_on_the_gpu():
+    """Row N2: AffineQuantizedKVCache (model.py:198-240).  The checker is the UNMODIFIED reference class updated position
+    by position on the GPU.  (a) this repo's eager module: all four buffers and the returned k_out / v_out bit-exact;
+    (b) the decode kernel (csrc/decode_attn_q8.cu) fed the same rows through an identity RoPE: int8 rows and scales
+    bit-exact, attention output against softmax(q k_out^T / sqrt(d)) v_out of the reference's k_out / v_out within
+    mean-abs-rel 1e-2 (bf16 output, fp32 accumulation order)."""
+    import math
+    from torchao_fork_b200 import _lib
+    from torchao_fork_b200._models.llama.model import AffineQuantizedKVCache
+
+    B, Hkv, T, D, G = 2, 2, 40, 128, 4
+    H = Hkv * G
+    k, v = _kv_rows(B, Hkv, T, D, 5)
+    ref = _run_worker("kvq", {"k": k, "v": v})
+    kc, vc = k.cuda(), v.cuda()
+    # (a) the eager mirror
+    with torch.device("cuda"):
+        mine = AffineQuantizedKVCache(B, T, Hkv, D, scale_dtype=torch.bfloat16)
+    with torch.no_grad():
+        for t in range(T):
+            k_out, v_out = mine.update(torch.tensor([t], device="cuda"), kc[:, :, t : t + 1], vc[:, :, t : t + 1])
+    for name in ("k_cache", "v_cache", "k_cache_scale", "v_cache_scale"):
+        assert torch.equal(getattr(mine, name).cpu(), ref[name]), name
+    assert torch.equal(k_out.cpu(), ref["k_out"]) and torch.equal(v_out.cpu(), ref["v_out"])
+    # (b) the kernel, one launch per position
+    L = _lib.lib()
+    k8 = torch.zeros(B, Hkv, T, D, dtype=torch.int8, device="cuda")
+    v8 = torch.zeros_like(k8)
+    ks = torch.ones(B, Hkv, T, 1, dtype=torch.bfloat16, device="cuda")
+    vs = torch.ones_like(ks)
+    freqs = torch.zeros(T, D // 2, 2, dtype=torch.bfloat16, device="cuda")
+    freqs[..., 0] = 1.0                                                   # cos = 1, sin = 0
+    q = torch.randn(B, H, D, generator=torch.Generator().manual_seed(9)).to(torch.bfloat16).cuda()
+    pos = torch.zeros(1, dtype=torch.int32, device="cuda")
+    out = torch.zeros(B, H * D, dtype=torch.bfloat16, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for n_split in (1, 3):
+        k8.zero_(); v8.zero_(); ks.fill_(1); vs.fill_(1)
+        ws = torch.zeros(int(L.ao_b200_decode_attention_fused_workspace_bytes(B, H, Hkv, n_split)), dtype=torch.uint8, device="cuda")
+        for t in range(T):
+            qkv = torch.cat([q.reshape(B, H * D), kc[:, :, t].reshape(B, Hkv * D), vc[:, :, t].reshape(B, Hkv * D)], dim=1).contiguous()
+            pos.fill_(t)
+            _lib.check(L.ao_b200_decode_attention_fused_q8(
+                qkv.data_ptr(), freqs.data_ptr(), pos.data_ptr(), k8.data_ptr(), v8.data_ptr(), ks.data_ptr(), vs.data_ptr(),
+                out.data_ptr(), B, H, Hkv, D, T, 1.0 / math.sqrt(D), n_split, ws.data_ptr(), ws.numel(), st), "attention_q8")
+        torch.cuda.synchronize()
+        assert torch.equal(k8.cpu(), ref["k_cache"]) and torch.equal(v8.cpu(), ref["v_cache"]), n_split
+        assert torch.equal(ks.cpu(), ref["k_cache_scale"]) and torch.equal(vs.cpu(), ref["v_cache_scale"]), n_split
+        ko, vo = ref["k_out"].cuda().float(), ref["v_out"].cuda().float()       # [B][Hkv][T][D], row T-1 unquantized
+        qf = q.float().view(B, Hkv, G, D)
+        att = torch.softmax(torch.einsum("bhgd,bhtd->bhgt", qf, ko) / math.sqrt(D), dim=-1)
+        want = torch.einsum("bhgt,bhtd->bhgd", att, vo).reshape(B, H * D)
+        assert _mean_abs_rel(want, out.float()) < 1e-2, n_split
+        assert _sqnr(want, out.float()) > 40.0, n_split
+
+
+def test_llama_decode_with_int8_kv_cache_matches_the_reference_transformer():
+    """generate.py --kv_cache_quantization: the reference Transformer with AffineQuantizedKVCache against this repo's
+    prefill (eager module) + decode engine (int8 attention kernel), fed the reference's tokens; logits >= 33 dB (the
+    int8 rows differ by at most one step wherever the wqkv outputs differ in their last bf16 bit)."""
+    from torchao_fork_b200._models.llama import ModelArgs, Transformer
+    from torchao_fork_b200._models.llama.decode_engine import DecodeEngine
+    from torchao_fork_b200._models.llama.model import transformer_configs
+
+    cfg_d = dict(transformer_configs["tiny-llama3"])
+    torch.manual_seed(11)
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        with torch.device("cuda"):
+            model = Transformer(ModelArgs(**cfg_d)).eval()
+    finally:
+        torch.set_default_dtype(old)
+    state = {k: v.detach().cpu() for k, v in model.state_dict().items() if v.dtype == torch.bfloat16 and "kv_cache" not in k}
+    T, steps, S = 9, 6, 64
+    prompt = torch.randint(0, cfg_d["vocab_size"], (T,), generator=torch.Generator().manual_seed(3))
+    ref = _run_worker("model", {"cfg": cfg_d, "state": state, "prompt": prompt, "steps": steps, "max_seq": S, "group_size": 128,
+                                "kv_cache_quantization": True})
+    ao.quantize_(model, ao.Int4WeightOnlyConfig(group_size=128))
+    model.setup_caches(1, S, device="cuda", kv_cache_quantization=True)
+    eng = DecodeEngine(model, 1, 0.0, None)
+    assert eng.kv_int8 and not eng.mega
+    with torch.no_grad():
+        lg = model(prompt.view(1, -1).cuda(), torch.arange(T, device="cuda", dtype=torch.int32))[0].float()
+    assert _sqnr(ref["prefill_logits"].cuda(), lg) >= 35.0
+    toks = ref["tokens"]
+    for i in range(steps):
+        eng.set_state(toks[i : i + 1].cuda(), T + i)
+        eng.step()
+        torch.cuda.synchronize()
+        snr = _sqnr(ref["step_logits"][i].cuda(), eng.logits[0])
+        assert snr >= 33.0, f"decode step {i}: logits vs the reference Transformer with the int8 KV cache {snr:.1f} dB"

@@ -162,7 +162,14 @@ class DecodeEngine:
                 w13=_Linear([ff.w1.weight, ff.w3.weight], interleave_gate_up=self.fused) if fuse else None,
                 w1=None if fuse else _Linear([ff.w1.weight]), w3=None if fuse else _Linear([ff.w3.weight]),
                 w2=_Linear([ff.w2.weight]),
-                k_cache=blk.attention.kv_cache.k_cache, v_cache=blk.attention.kv_cache.v_cache))
+                k_cache=blk.attention.kv_cache.k_cache, v_cache=blk.attention.kv_cache.v_cache,
+                k_scale=getattr(blk.attention.kv_cache, "k_cache_scale", None),
+                v_scale=getattr(blk.attention.kv_cache, "v_cache_scale", None)))
+        # int8 KV cache (AffineQuantizedKVCache, model.py:198-240): the attention launch quantizes the new row and walks
+        # the int8 rows (csrc/decode_attn_q8.cu)
+        self.kv_int8 = self.layers[0]["k_cache"].dtype == torch.int8
+        if self.kv_int8:
+            assert self.layers[0]["k_scale"].dtype == torch.bfloat16, "int8 KV cache: bf16 scales"
         self.I = int(model.layers[0].feed_forward.w1.weight.shape[0])
         self.out_norm = model.norm.weight.detach()
         self.output = _Linear([model.output.weight])
@@ -204,7 +211,7 @@ class DecodeEngine:
         self.launches_per_step = 0
         self._host_pos = 0   # host mirror of *pos (set_state / step): decoding past the caches raises instead of corrupting them
         # one persistent launch per token (csrc/decode_mega.cu): batch 1, every linear int4 with one group size
-        can_mega = (batch_size == 1 and self.fused
+        can_mega = (batch_size == 1 and self.fused and not self.kv_int8
                     and all(l[k] is not None and l[k].kind == "int4" for l in self.layers for k in ("wqkv", "wo", "w13", "w2"))
                     and self.output.kind == "int4"
                     and len({l[k].group_size for l in self.layers for k in ("wqkv", "wo", "w13", "w2")} | {self.output.group_size}) == 1
@@ -373,11 +380,18 @@ class DecodeEngine:
         torch.index_select(self.emb, 0, self.tok, out=self.h)
         for l in self.layers:
             l["wqkv"].launch_fused(self.h, self.qkv, st, norm_w=l["attn_norm"], eps=self.eps, ws=self.ws)
-            _lib.check(L.ao_b200_decode_attention_fused(
-                self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(), l["k_cache"].data_ptr(),
-                l["v_cache"].data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd, self.S,
-                1.0 / math.sqrt(self.hd), self.n_split, self.attn_fused_ws.data_ptr(), self.attn_fused_ws.numel(), st),
-                "decode_attention_fused")
+            if self.kv_int8:
+                _lib.check(L.ao_b200_decode_attention_fused_q8(
+                    self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(), l["k_cache"].data_ptr(),
+                    l["v_cache"].data_ptr(), l["k_scale"].data_ptr(), l["v_scale"].data_ptr(), self.o.data_ptr(), B, self.H,
+                    self.Hkv, self.hd, self.S, 1.0 / math.sqrt(self.hd), self.n_split, self.attn_fused_ws.data_ptr(),
+                    self.attn_fused_ws.numel(), st), "decode_attention_fused_q8")
+            else:
+                _lib.check(L.ao_b200_decode_attention_fused(
+                    self.qkv.data_ptr(), self.freqs.data_ptr(), self.pos.data_ptr(), l["k_cache"].data_ptr(),
+                    l["v_cache"].data_ptr(), self.o.data_ptr(), B, self.H, self.Hkv, self.hd, self.S,
+                    1.0 / math.sqrt(self.hd), self.n_split, self.attn_fused_ws.data_ptr(), self.attn_fused_ws.numel(), st),
+                    "decode_attention_fused")
             if self.tp is None:
                 l["wo"].launch_fused(self.o, self.h, st, residual=self.h, epilogue=1, ws=self.ws)
             else:
@@ -404,6 +418,8 @@ class DecodeEngine:
             return self._launch_step_mega()
         if self.fused:
             return self._launch_step_fused()
+        if self.kv_int8:
+            raise NotImplementedError("int8 KV cache: only with the fused decode step (M * K must fit the GEMV staging)")
         L = _lib.lib()
         st = torch.cuda.current_stream(self.device).cuda_stream
         B, D = self.B, self.cfg.dim

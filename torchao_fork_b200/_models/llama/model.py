@@ -89,6 +89,41 @@ class KVCache(nn.Module):
         return self.k_cache, self.v_cache
 
 
+class AffineQuantizedKVCache(nn.Module):
+    """reference: model.py:198-240.  int8 rows [B][n_local_heads][S][head_dim] + one scale per row
+    [B][n_local_heads][S][1]; update() returns the dequantized caches with the positions just written replaced by the
+    unquantized values.  (Decode steps do not call update(): csrc/decode_attn_q8.cu does the same thing for the new
+    row inside the attention launch and never materialises the dequantized cache.)"""
+
+    def __init__(self, max_batch_size, max_seq_length, n_heads, head_dim, scale_dtype=torch.bfloat16):
+        super().__init__()
+        cache_shape = (max_batch_size, n_heads, max_seq_length, head_dim)
+        scale_shape = (max_batch_size, n_heads, max_seq_length, 1)
+        self.register_buffer("k_cache", torch.zeros(cache_shape, dtype=torch.int8))
+        self.register_buffer("v_cache", torch.zeros(cache_shape, dtype=torch.int8))
+        self.register_buffer("k_cache_scale", torch.ones(scale_shape, dtype=scale_dtype))
+        self.register_buffer("v_cache_scale", torch.ones(scale_shape, dtype=scale_dtype))
+
+    def update(self, input_pos, k_val, v_val):
+        from ...quantization.utils import _quantize_activation_per_token_absmax
+        q_k_val, k_scale = _quantize_activation_per_token_absmax(k_val)
+        self.k_cache[:, :, input_pos] = q_k_val
+        self.k_cache_scale[:, :, input_pos] = k_scale.unsqueeze(-1)
+        k_out = self.k_cache * self.k_cache_scale
+        k_out[:, :, input_pos] = k_val
+        q_v_val, v_scale = _quantize_activation_per_token_absmax(v_val)
+        self.v_cache[:, :, input_pos] = q_v_val
+        self.v_cache_scale[:, :, input_pos] = v_scale.unsqueeze(-1)
+        v_out = self.v_cache * self.v_cache_scale
+        v_out[:, :, input_pos] = v_val
+        return k_out, v_out
+
+    @classmethod
+    def from_float(cls, kv_cache):
+        max_batch_size, n_heads, max_seq_length, head_dim = kv_cache.k_cache.shape
+        return cls(max_batch_size, max_seq_length, n_heads, head_dim, kv_cache.k_cache.dtype)
+
+
 class RMSNorm(nn.Module):
     """reference: model.py:489-503 — normalise in fp32, cast back, multiply by the weight."""
 
@@ -221,8 +256,11 @@ class Transformer(nn.Module):
     def from_name(cls, name: str):
         return cls(ModelArgs.from_name(name))
 
-    def setup_caches(self, max_batch_size, max_seq_length, dtype=torch.bfloat16, device=None):
-        if self.max_seq_length >= max_seq_length and self.max_batch_size >= max_batch_size:
+    def setup_caches(self, max_batch_size, max_seq_length, dtype=torch.bfloat16, device=None, kv_cache_quantization=False):
+        """reference: model.py:259-330 (`training`, `linear_causal_mask` are outside this path)"""
+        want = AffineQuantizedKVCache if kv_cache_quantization else KVCache
+        have = type(self.layers[0].attention.kv_cache) if len(self.layers) else want
+        if self.max_seq_length >= max_seq_length and self.max_batch_size >= max_batch_size and have is want:
             return
         cfg = self.config
         device = device or self.tok_embeddings.weight.device
@@ -230,8 +268,12 @@ class Transformer(nn.Module):
         self.max_seq_length, self.max_batch_size = max_seq_length, max_batch_size
         self.causal_mask = torch.tril(torch.ones(max_seq_length, max_seq_length, dtype=torch.bool, device=device))
         for blk in self.layers:
-            blk.attention.kv_cache = KVCache(max_batch_size, max_seq_length, blk.attention.n_local_heads,
-                                             cfg.head_dim, dtype).to(device)
+            if kv_cache_quantization:
+                blk.attention.kv_cache = AffineQuantizedKVCache(max_batch_size, max_seq_length, blk.attention.n_local_heads,
+                                                                cfg.head_dim, dtype).to(device)
+            else:
+                blk.attention.kv_cache = KVCache(max_batch_size, max_seq_length, blk.attention.n_local_heads,
+                                                 cfg.head_dim, dtype).to(device)
         self.freqs_cis = precompute_freqs_cis(cfg.block_size, cfg.head_dim, cfg.rope_base, dtype,
                                               cfg.use_scaled_rope).to(device)
 

@@ -38,7 +38,7 @@ extern "C" const char* ao_b200_error_string(int code) {
   return "unknown error";
 }
 
-extern "C" int ao_b200_abi_version(void) { return 4; }
+extern "C" int ao_b200_abi_version(void) { return 5; }
 
 #include <cstdlib>
 namespace {

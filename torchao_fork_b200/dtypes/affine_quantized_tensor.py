@@ -5,7 +5,7 @@ affine_quantized_tensor_ops.py:113-598 restricted to the weight-only int4 / int8
 same constructor fields, `from_hp_to_intx`, `dequantize`, layout registry
 (`register_layout` / `get_tensor_impl_constructor`), linear dispatch table
 (`register_aqt_quantized_linear_dispatch`), and the aten ops a weight needs
-(detach / clone / _to_copy / copy_ / t / slice / view / linear / mm / addmm).
+(detach / clone / _to_copy / copy_ / t / slice / view / select / index / linear / mm / addmm).
 """
 import logging
 from typing import Callable, Dict, Optional, Tuple
@@ -115,8 +115,21 @@ class AffineQuantizedTensor(torch.Tensor):
             raise NotImplementedError("custom scale/zero_point are outside the B200 hot path")
         if not input_float.is_cuda:
             raise NotImplementedError("the B200 path quantizes CUDA tensors only (no CPU fallback)")
+        if input_float.dim() == 3:
+            # MoE expert weights [E, N, K] (reference: tensor_core_tiled_layout.py:283-294, block_size (1, 1, G)):
+            # every expert is quantized by the 2-D path, the storage tensors get a leading expert dimension
+            if not (isinstance(_layout, TensorCoreTiledLayout) and len(block_size) == 3 and block_size[0] == 1):
+                raise NotImplementedError("3-D weights: TensorCoreTiledLayout with block_size (1, 1, G)")
+            per_expert = [cls.from_hp_to_intx(input_float[e], mapping_type, tuple(block_size[1:]), target_dtype, quant_min,
+                                              quant_max, eps, scale_dtype, zero_point_dtype, preserve_zero,
+                                              zero_point_domain, _layout, use_hqq) for e in range(input_float.shape[0])]
+            impl0 = per_expert[0].tensor_impl
+            tensor_impl = impl0.__class__(torch.stack([w.tensor_impl.packed_weight for w in per_expert]),
+                                          torch.stack([w.tensor_impl.scale_and_zero for w in per_expert]), False, _layout)
+            return cls(tensor_impl, block_size, input_float.shape, per_expert[0].quant_min, per_expert[0].quant_max,
+                       zero_point_domain, dtype=input_float.dtype)
         if input_float.dim() != 2:
-            raise NotImplementedError("the B200 path quantizes 2-D linear weights")
+            raise NotImplementedError("the B200 path quantizes 2-D linear weights (and 3-D MoE expert stacks)")
         original_shape = input_float.shape
         input_float = input_float.detach()
         qmin, qmax = _get_and_check_qmin_qmax(target_dtype, quant_min, quant_max)
@@ -170,6 +183,8 @@ class AffineQuantizedTensor(torch.Tensor):
         """reference: affine_quantized_tensor.py:134-191"""
         if output_dtype is None:
             output_dtype = self.dtype
+        if self.dim() == 3:
+            return torch.stack([aten.select.int(self, 0, e).dequantize(output_dtype) for e in range(self.shape[0])])
         data, scale, zero_point = self.tensor_impl.get_plain()
         n, k = self.shape[-2], self.shape[-1]
         if self.zero_point_domain is ZeroPointDomain.FLOAT:
@@ -339,6 +354,26 @@ def _view(func, args, kwargs):
     raise ValueError(f"{w.__class__.__name__} only supports .view() with same shape")
 
 
+def _index(func, args, kwargs):
+    """reference: affine_quantized_tensor_ops.py:519-538 (a single index tensor, on dim 0)"""
+    w, indices = args
+    assert len(indices) == 1, f"op {func} currently only implemented for single dimensional indexing but got indices: {indices}"
+    new_impl = aten.index.Tensor(w.tensor_impl, indices)
+    shape = (indices[0].numel(), *w.shape[1:])
+    new = w.__class__(new_impl, w.block_size, shape, w.quant_min, w.quant_max, w.zero_point_domain, dtype=w.dtype)
+    return return_and_correct_aliasing(func, args, kwargs, new)
+
+
+def _select(func, args, kwargs):
+    """reference: affine_quantized_tensor_ops.py:541-562 (dim 0 of a 3-D weight: one expert)"""
+    w, dim, index = fill_defaults(args, 3, [0, 0])
+    assert dim == 0, f"op {func} currently only implemented for dim=0 but got dim={dim}"
+    assert w.dim() == 3, f"op {func} currently only implemented for 3 dimensional tensors but got shape={w.shape}"
+    new_impl = aten.select.int(w.tensor_impl, dim, index)
+    new = w.__class__(new_impl, w.block_size[1:], w.shape[1:], w.quant_min, w.quant_max, w.zero_point_domain, dtype=w.dtype)
+    return return_and_correct_aliasing(func, args, kwargs, new)
+
+
 _ATEN_TABLE = {
     aten.linear.default: _linear,
     aten.mm.default: _mm_like,
@@ -352,4 +387,6 @@ _ATEN_TABLE = {
     aten.t.default: _t,
     aten.slice.Tensor: _slice,
     aten.view.default: _view,
+    aten.index.Tensor: _index,
+    aten.select.int: _select,
 }

@@ -94,6 +94,12 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         """reference: tensor_core_tiled_layout.py:262-307.  int_data int32 (N, K) in 0..15,
         scale / zero_point (N, K/G) bf16."""
         assert isinstance(_layout, TensorCoreTiledLayout)
+        if int_data.dim() == 3:  # for moe quant (reference :283-294): one packed weight per expert, stacked
+            e_n = int_data.shape[0]
+            scale = scale.reshape(e_n, int_data.shape[-2], -1)
+            zero_point = zero_point.reshape(e_n, int_data.shape[-2], -1)
+            per = [cls.from_plain(int_data[e], scale[e], zero_point[e], _layout) for e in range(e_n)]
+            return cls(torch.stack([p.packed_weight for p in per]), torch.stack([p.scale_and_zero for p in per]), False, _layout)
         assert int_data.dtype == torch.int32 and int_data.dim() == 2, "int_data must be 2-D int32"
         n, k = int_data.shape
         scale = scale.reshape(n, -1)
@@ -116,11 +122,11 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
     # -- views ----------------------------------------------------------------------------
     @property
     def padded_shape(self) -> Tuple[int, int]:
-        return self.packed_weight.shape[0] * 16, self.packed_weight.shape[1] * 64
+        return self.packed_weight.shape[-4] * 16, self.packed_weight.shape[-3] * 64
 
     @property
     def group_size(self) -> int:
-        return self.padded_shape[1] // self.scale_and_zero.shape[1]
+        return self.padded_shape[1] // self.scale_and_zero.shape[-3]
 
     @property
     def block_size(self):
@@ -130,6 +136,10 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
         """-> int_data int32 (Np, Kp), scale (Np, Kp/G), zero (Np, Kp/G).  The reference recovers
         int_data with an identity matmul + re-quantize (tensor_core_tiled_layout.py:465-517); here it
         is a plain unpack kernel (exact by construction)."""
+        if self.packed_weight.dim() == 5:  # expert stack
+            per = [self.__class__(self.packed_weight[e], self.scale_and_zero[e], self.transposed, self._layout).get_plain()
+                   for e in range(self.packed_weight.shape[0])]
+            return tuple(torch.stack([p[i] for p in per]) for i in range(3))
         int_data = torch.ops.torchao.b200_int4_unpack(self.packed_weight)
         s, z = _ops.unpack_scales_and_zeros_b200(self.scale_and_zero)
         return int_data, s, z
@@ -169,7 +179,14 @@ class TensorCoreTiledAQTTensorImpl(AQTTensorImpl):
             return self.copy_(args[1])
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
+        if func in (aten.select.int, aten.index.Tensor):
+            # reference :363-372: experts of a 3-D weight.  Both storage tensors carry the expert dimension in front.
+            assert not (func is aten.select.int and args[1] != 0), "aten.select.int currently only has support for dim=0"
+            assert self.packed_weight.dim() == 5, f"{func}: only on a stack of expert weights"
+            return return_and_correct_aliasing(
+                func, args, kwargs, self._apply_fn_to_data(lambda x: func(x, *args[1:], **kwargs).contiguous()))
         if func is aten.slice.Tensor:
+            assert self.packed_weight.dim() == 4, "slice: 2-D weights only"
             # logical (N, K) ranges -> 16-row strips / 64-wide k-tiles / groups (reference: :386-440 does the same on
             # its tiles).  Both tensors are strip-major: dim 0 = strip, dim 1 = k-tile (weight) or group (qparams).
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])
@@ -321,7 +338,14 @@ class PlainAQTTensorImpl(AQTTensorImpl):
             return self.copy_(args[1])
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
+        if func in (aten.select.int, aten.index.Tensor):
+            # reference :363-372: experts of a 3-D weight.  Both storage tensors carry the expert dimension in front.
+            assert not (func is aten.select.int and args[1] != 0), "aten.select.int currently only has support for dim=0"
+            assert self.packed_weight.dim() == 5, f"{func}: only on a stack of expert weights"
+            return return_and_correct_aliasing(
+                func, args, kwargs, self._apply_fn_to_data(lambda x: func(x, *args[1:], **kwargs).contiguous()))
         if func is aten.slice.Tensor:
+            assert self.packed_weight.dim() == 4, "slice: 2-D weights only"
             # reference: plain_layout.py:160-200 — rows slice data + qparams, columns slice data only.  Done on the plain
             # view (unpack -> slice -> pack): slicing happens at load / shard time, not on the hot path.
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])

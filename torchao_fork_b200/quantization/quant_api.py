@@ -109,8 +109,20 @@ def _int4_weight_only_quantize_tensor(weight, config):
         logger.info(f"Skipping quantizing weight with int4 weight only quantization because the shape of weight "
                     f"{weight.shape} is not compatible with group_size {group_size}")
         return weight
-    if config.version != 1:
-        raise NotImplementedError("Int4WeightOnlyConfig(version=2) tensors are a 'next' row (SURVEY.md §8 N3)")
+    if config.version == 2:
+        # reference: quant_api.py:1062-1084
+        block_size = [1 for _ in range(weight.ndim - 1)] + [group_size]
+        fmt = config.packing_format
+        fmt = fmt.value if isinstance(fmt, PackingFormat) else str(fmt)
+        if fmt == PackingFormat.PLAIN.value:
+            from .int4_tensor import Int4Tensor
+            return Int4Tensor.from_hp(weight, block_size)
+        if fmt in ("preshuffled", "marlin_sparse"):
+            raise NotImplementedError(
+                f"packing_format={fmt!r}: a storage order of fbgemm's / marlin's own kernels; on B200 every int4 weight is "
+                "served from the strip-major storage — use packing_format='plain'")
+        raise ValueError(f"Unsupported packing format: {config.packing_format}")
+    assert config.version == 1
     assert type(layout) in LAYOUT_TO_ZERO_POINT_DOMAIN, f"Only support layout: {LAYOUT_TO_ZERO_POINT_DOMAIN.keys()}"
     zero_point_domain = config.zero_point_domain
     if zero_point_domain == ZeroPointDomain.NONE:

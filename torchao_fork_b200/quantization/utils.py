@@ -56,3 +56,24 @@ def groupwise_affine_dequantize_tensor_from_qparams(w_int4x8, scales, zeros, n_b
         w_int32 = w_int4x8
     return _dequantize_affine_tinygemm(w_int32, (1, groupsize), scales, zeros, torch.int32, 0, 15,
                                        output_dtype=scales.dtype)
+
+
+@torch.no_grad()
+def _quantize_activation_per_token_absmax(t):
+    """reference: torchao/quantization/utils.py:152-182 — symmetric int8 per row of the last dimension, -127..127,
+    eps 1e-5, scale in t's dtype (fp32 for fp16 inputs).  Written out as the tensor expressions choose_qparams_affine
+    (quant_primitives.py:1537-1575, SYMMETRIC branch) and _quantize_affine_no_dtype_cast (:433-459) evaluate, in the same
+    order and dtypes, so that eager results equal the reference's bit for bit on the same device.  The decode kernel
+    (csrc/decode_attn_q8.cu) does the same arithmetic for one new row."""
+    quant_min, quant_max, eps = -127, 127, 1e-5
+    scale_dtype = torch.float32 if t.dtype == torch.float16 else t.dtype
+    min_val = torch.amin(t, dim=-1, keepdim=False)
+    max_val = torch.amax(t, dim=-1, keepdim=False)
+    min_val_neg = torch.min(min_val, torch.zeros_like(min_val))
+    max_val_pos = torch.max(max_val, torch.zeros_like(max_val))
+    max_val_pos = torch.max(-min_val_neg, max_val_pos)
+    scale = max_val_pos / (float(quant_max - quant_min) / 2)
+    zero_point = torch.full_like(scale, int((quant_max + quant_min + 1) / 2))
+    scale = torch.clamp(scale, min=eps).to(dtype=scale_dtype)
+    quant = torch.clamp(torch.round(t * (1.0 / scale.unsqueeze(-1))) + zero_point.unsqueeze(-1), quant_min, quant_max)
+    return quant.to(torch.int8), scale
