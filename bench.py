@@ -517,8 +517,9 @@ def run_b200(args):
             which = "w13" if eng.layers[0]["w13"] is not None else "w2"
             st = standalone[which]
             lin = eng.layers[0][which]
-            if tr.get("n") == lin.n and tr.get("k") == lin.k and tr.get("kind") == lin.kind:
-                traffic = tr.get("dram_bytes_per_launch")
+            for ent in (tr, tr.get("gemv_int4") or {}, tr.get("int8") or {}):   # per-kernel entries of profiles/traffic.json
+                if ent.get("n") == lin.n and ent.get("k") == lin.k and ent.get("kind") == lin.kind:
+                    traffic = ent.get("dram_bytes_per_launch")
             alg = st["gbs"] * 1e9 * st["us_per_launch"] * 1e-6
             line["roofline"] = {"bound": "hbm", "achieved": st["gbs"], "peak": peak, "unit": "GB/s", "frac": st["frac"], "traffic": traffic,
                                 "kernel": f"{lin.kind} weight-only GEMV {lin.n}x{lin.k} (fused w1|w3), M={args.batch_size}",

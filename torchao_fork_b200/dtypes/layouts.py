@@ -338,14 +338,7 @@ class PlainAQTTensorImpl(AQTTensorImpl):
             return self.copy_(args[1])
         if func is aten.t.default:
             return return_and_correct_aliasing(func, args, kwargs, self.t())
-        if func in (aten.select.int, aten.index.Tensor):
-            # reference :363-372: experts of a 3-D weight.  Both storage tensors carry the expert dimension in front.
-            assert not (func is aten.select.int and args[1] != 0), "aten.select.int currently only has support for dim=0"
-            assert self.packed_weight.dim() == 5, f"{func}: only on a stack of expert weights"
-            return return_and_correct_aliasing(
-                func, args, kwargs, self._apply_fn_to_data(lambda x: func(x, *args[1:], **kwargs).contiguous()))
         if func is aten.slice.Tensor:
-            assert self.packed_weight.dim() == 4, "slice: 2-D weights only"
             # reference: plain_layout.py:160-200 — rows slice data + qparams, columns slice data only.  Done on the plain
             # view (unpack -> slice -> pack): slicing happens at load / shard time, not on the hot path.
             _, dim, start, end, step = fill_defaults(args, 5, [0, None, None, 1])
