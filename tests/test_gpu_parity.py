@@ -459,3 +459,20 @@ def test_errors_are_loud():
         T.b200_int4_quantize_pack(w.float(), 32, 1e-6, True)  # not bf16
     with pytest.raises(NotImplementedError):
         T.b200_int4_quantize_pack(w.cpu(), 4, 1e-6, True)     # no CPU backend
+
+
+@pytest.mark.parametrize("bad", [float("nan"), float("inf")])
+@pytest.mark.parametrize("m", [1, 2])
+def test_int4_decode_gemv_propagates_nan_and_inf(bad, m):
+    """The bs=1 GEMV stages activations as fixed-point int8 limbs; a NaN / Inf in the activation row must still come out
+    as NaN (the reference's bf16 matmul propagates it) — for the row that holds it only."""
+    torch.manual_seed(0)
+    w = torch.randn(256, 512, dtype=torch.bfloat16, device=DEV)
+    packed, sz = T.b200_int4_quantize_pack(w, 128, 1e-6, True)
+    x = torch.randn(m, 512, dtype=torch.bfloat16, device=DEV)
+    good = T.b200_int4_weight_only_mm(x, packed, 128, sz, 256)
+    x[0, 37] = bad
+    y = T.b200_int4_weight_only_mm(x, packed, 128, sz, 256)
+    assert torch.isnan(y[0]).all()
+    if m > 1:
+        assert torch.equal(y[1:], good[1:])

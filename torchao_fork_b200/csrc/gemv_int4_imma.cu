@@ -63,6 +63,12 @@ __device__ __forceinline__ float warp_max_i(float v) {
   for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
+__device__ __forceinline__ uint32_t absmax_bits(uint32_t m, float v) { return max(m, __float_as_uint(v) & 0x7fffffffu); }
+__device__ __forceinline__ uint32_t warp_max_bits(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
 // D(16x8, s32) += A(16x32, u8, row) * B(32x8, s8, col)
 __device__ __forceinline__ void imma_16832(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
                                            uint32_t b1) {
@@ -256,7 +262,8 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
   };
   {
     if constexpr (hold) {
-      float ss = 0.f, amax = 0.f;
+      float ss = 0.f;
+      uint32_t amax = 0u;  // bits of the largest |x| (a NaN has the largest bits: it propagates)
 #pragma unroll
       for (int i = 0; i < kHold; ++i) {
         const int ci = i * kCT + tid;
@@ -276,30 +283,31 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
         }
         unpack8(xr[i], f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
+        for (int e = 0; e < 8; ++e) amax = absmax_bits(amax, f[e]);
       }
       ss = warp_sum_i(ss);
-      amax = warp_max_i(amax);
+      amax = warp_max_bits(amax);
       if (lane == 0) {
         part[warp * 2] = ss;
-        part[warp * 2 + 1] = amax;
+        part[warp * 2 + 1] = __uint_as_float(amax);
       }
     } else {
       for (int m = 0; m < p.M; ++m) {
-        float ss = 0.f, amax = 0.f;
+        float ss = 0.f;
+        uint32_t amax = 0u;
         for (int ci = tid; ci < chunks_per_row; ci += kCT) {
           const int64_t k0 = (int64_t)ci * 8;
           if (k0 >= p.Kx) continue;
           float f[8];
           load_norm(m, k0, f, ss);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
+          for (int e = 0; e < 8; ++e) amax = absmax_bits(amax, f[e]);
         }
         ss = warp_sum_i(ss);
-        amax = warp_max_i(amax);
+        amax = warp_max_bits(amax);
         if (lane == 0) {
           part[(m * kIConsumers + warp) * 2] = ss;
-          part[(m * kIConsumers + warp) * 2 + 1] = amax;
+          part[(m * kIConsumers + warp) * 2 + 1] = __uint_as_float(amax);
         }
       }
     }
@@ -309,13 +317,16 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
     constexpr int kRows = hold ? 1 : 2;  // the register-held path is M = 1
 #pragma unroll
     for (int m = 0; m < kRows; ++m) {
-      float t = 0.f, amax = 0.f;
+      float t = 0.f;
+      uint32_t amax_b = 0u;
       if (m < p.M && lane < kIConsumers) {
         t = part[(m * kIConsumers + lane) * 2];
-        amax = part[(m * kIConsumers + lane) * 2 + 1];
+        amax_b = __float_as_uint(part[(m * kIConsumers + lane) * 2 + 1]);
       }
       t = warp_sum_i(t);
-      amax = warp_max_i(amax);
+      amax_b = warp_max_bits(amax_b);
+      const bool bad = amax_b >= 0x7f800000u;  // an Inf / NaN activation: the reference's bf16 matmul propagates it, so do we
+      const float amax = bad ? 0.f : __uint_as_float(amax_b);
       // 2^e brings the row's largest magnitude into [2^21, 2^22): |round(x 2^e)| <= 2^22 fits three balanced int8 limbs
       int e = 0;
       if (amax > 0.f) e = 21 - ((int)((__float_as_uint(amax) >> 23) & 0xFF) - 127);
@@ -323,7 +334,8 @@ __global__ void __launch_bounds__(kIThreads, 2) int4_gemv_imma_kernel(const Gemv
       up_m[m] = __uint_as_float((uint32_t)(e + 127) << 23);
       if (warp == m && lane == 0 && m < p.M) {
         const float dn = __uint_as_float((uint32_t)(127 - e) << 23);
-        row_scale[m] = (p.norm_w != nullptr) ? dn * rsqrtf(t / (float)p.Kx + p.eps) : dn;  // read by the epilogue warp (after barrier 2)
+        const float rs = (p.norm_w != nullptr) ? dn * rsqrtf(t / (float)p.Kx + p.eps) : dn;
+        row_scale[m] = bad ? __uint_as_float(0x7fc00000u) : rs;  // read by the epilogue warp (after barrier 2)
       }
     }
     // one chunk (8 activations f[] of row m at chunk index ci) -> limbs in shared memory + group sums.  Executed by whole
