@@ -170,6 +170,14 @@ AO_B200_API int64_t ao_b200_hqq_blocks(int64_t n_groups);
 AO_B200_API int ao_b200_hqq_init(const void* w, int64_t n_groups, int group_size, float* scale, float* zero, void* stream);
 AO_B200_API int ao_b200_hqq_step(const void* w, int64_t n_groups, int group_size, const float* scale, float* zero,
                                  double beta, double lp_norm, float* err_partial, void* stream);
+/* The whole solver loop without a host round trip (ABI v5): `iters` step launches, each followed by a one-block kernel
+ * that applies the reference's global early stop on the device (quant_primitives.py:1964-1972: stop at the first
+ * iteration whose mean |W - W_r| does not improve; that iteration's zero is kept) — the remaining step launches return
+ * at once.  beta is multiplied by kappa between iterations.  state: 16 bytes of device memory, 8-byte aligned:
+ * [double best][int32 stopped][int32 iterations run] (written here; readable after the stream has caught up). */
+AO_B200_API int ao_b200_hqq_solve(const void* w, int64_t n_groups, int group_size, const float* scale, float* zero,
+                                  double beta, double kappa, double lp_norm, int iters, float* err_partial, void* state,
+                                  void* stream);
 AO_B200_API int ao_b200_hqq_finalize(const void* w, int64_t n_groups, int group_size, const float* scale, const float* zero,
                                      int32_t* q, void* scale_out, void* zero_out, void* stream);
 

@@ -82,3 +82,48 @@ def test_hqq_constant_and_zero_groups():
     assert np.array_equal(o.to_bits(f32_of(s)), o.to_bits(os_)) and np.array_equal(o.to_bits(f32_of(z)), o.to_bits(oz))
     deq = (q.float() - 8) * s.float().repeat_interleave(128, 1) + z.float().repeat_interleave(128, 1)
     assert torch.allclose(deq, w.float(), atol=1e-2)
+
+
+@pytest.mark.parametrize("shape,gs", [((256, 512), 64), ((512, 1024), 128), ((64, 256), 32)])
+def test_hqq_device_side_early_stop_equals_the_host_driven_loop(shape, gs):
+    """ao_b200_hqq_solve (the early stop of quant_primitives.py:1964-1972 decided by a one-block kernel, no host round
+    trip) against the same iterations driven from the host with ao_b200_hqq_step: same number of iterations, bit-identical
+    zero."""
+    from torchao_fork_b200 import _lib
+    from torchao_fork_b200.ops import HQQ_BETA, HQQ_ITERS, HQQ_KAPPA, HQQ_LP_NORM
+    torch.manual_seed(3)
+    w = (torch.randn(*shape, device="cuda") * torch.rand(shape[0], 1, device="cuda")).to(torch.bfloat16).contiguous()
+    w[0, :gs] = 0.25                                   # a constant group
+    L = _lib.lib()
+    n_groups = shape[0] * shape[1] // gs
+    st = torch.cuda.current_stream().cuda_stream
+    err = torch.empty(int(L.ao_b200_hqq_blocks(n_groups)), dtype=torch.float32, device="cuda")
+
+    def init():
+        scale = torch.empty(n_groups, dtype=torch.float32, device="cuda")
+        zero = torch.empty_like(scale)
+        _lib.check(L.ao_b200_hqq_init(w.data_ptr(), n_groups, gs, scale.data_ptr(), zero.data_ptr(), st), "init")
+        return scale, zero
+
+    scale_h, zero_h = init()
+    beta, best, ran = HQQ_BETA, 1e4, 0
+    for _ in range(HQQ_ITERS):
+        _lib.check(L.ao_b200_hqq_step(w.data_ptr(), n_groups, gs, scale_h.data_ptr(), zero_h.data_ptr(), beta, HQQ_LP_NORM,
+                                      err.data_ptr(), st), "step")
+        beta *= HQQ_KAPPA
+        ran += 1
+        current = float(err.sum(dtype=torch.float64)) / w.numel()
+        if current < best:
+            best = current
+        else:
+            break
+    scale_d, zero_d = init()
+    state = torch.empty(2, dtype=torch.float64, device="cuda")
+    _lib.check(L.ao_b200_hqq_solve(w.data_ptr(), n_groups, gs, scale_d.data_ptr(), zero_d.data_ptr(), HQQ_BETA, HQQ_KAPPA,
+                                   HQQ_LP_NORM, HQQ_ITERS, err.data_ptr(), state.data_ptr(), st), "solve")
+    torch.cuda.synchronize()
+    flags = state[1:].view(torch.int32).cpu()
+    assert int(flags[1]) == ran, (int(flags[1]), ran)
+    assert int(flags[0]) == (1 if ran < HQQ_ITERS else int(flags[0]))
+    assert torch.equal(zero_d, zero_h) and torch.equal(scale_d, scale_h)
+    assert abs(float(state[0]) - best) <= 1e-12 * max(best, 1.0)

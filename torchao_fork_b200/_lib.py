@@ -55,6 +55,7 @@ SIGNATURES = {
     "ao_b200_hqq_blocks": [_i64],
     "ao_b200_hqq_init": [_vp, _i64, _i32, _vp, _vp, _vp],
     "ao_b200_hqq_step": [_vp, _i64, _i32, _vp, _vp, ctypes.c_double, ctypes.c_double, _vp, _vp],
+    "ao_b200_hqq_solve": [_vp, _i64, _i32, _vp, _vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, _i32, _vp, _vp, _vp],
     "ao_b200_hqq_finalize": [_vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp],
     "ao_b200_int8_mm": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp],
     "ao_b200_int8_gemv_fused": [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _f32, _vp, _i64, _i32,

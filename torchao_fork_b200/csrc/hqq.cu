@@ -62,8 +62,10 @@ __global__ void __launch_bounds__(kHqqWarps * 32) hqq_init_kernel(const __nv_bfl
 template <int G>
 __global__ void __launch_bounds__(kHqqWarps * 32) hqq_step_kernel(const __nv_bfloat16* __restrict__ w, int64_t n_groups,
                                                                   const float* __restrict__ scale, float* __restrict__ zero,
-                                                                  float inv_beta, float lp_m1, float* __restrict__ err_partial) {
+                                                                  float inv_beta, float lp_m1, float* __restrict__ err_partial,
+                                                                  const int* __restrict__ stop) {
   __shared__ float s_err[kHqqWarps];
+  if (stop != nullptr && *reinterpret_cast<const volatile int*>(stop) != 0) return;  // ao_b200_hqq_solve: the early stop has fired
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t group = (int64_t)blockIdx.x * kHqqWarps + warp;
   float err = 0.f;
@@ -149,7 +151,58 @@ extern "C" int ao_b200_hqq_step(const void* w, int64_t n_groups, int group_size,
   auto s = static_cast<cudaStream_t>(stream);
   const unsigned grid = (unsigned)ao_b200_hqq_blocks(n_groups);
   const float inv_beta = (float)(1.0 / beta), lp_m1 = (float)(lp_norm - 1.0);
-  AO_HQQ_DISPATCH(hqq_step_kernel, static_cast<const __nv_bfloat16*>(w), n_groups, scale, zero, inv_beta, lp_m1, err_partial);
+  AO_HQQ_DISPATCH(hqq_step_kernel, static_cast<const __nv_bfloat16*>(w), n_groups, scale, zero, inv_beta, lp_m1, err_partial, nullptr);
+  return ao_launch_status();
+}
+
+// The reference's global early stop (:1964-1972) decided on the device: current = mean |W - W_r| of the iteration that
+// just ran (per-block partial sums added in a fixed order, in double); the first iteration that does not improve on the
+// best so far sets `stop`, which makes the remaining step launches return at once (its zero is kept, as in the reference).
+// state: [double best][int stop][int iterations run]
+__global__ void __launch_bounds__(256) hqq_judge_kernel(const float* __restrict__ err_partial, int64_t n_blocks, double inv_numel,
+                                                        double* __restrict__ state) {
+  __shared__ double s_sum[256];
+  int* flags = reinterpret_cast<int*>(state + 1);
+  if (*reinterpret_cast<volatile int*>(flags) != 0) return;
+  double t = 0.0;
+  for (int64_t i = threadIdx.x; i < n_blocks; i += 256) t += (double)err_partial[i];
+  s_sum[threadIdx.x] = t;
+  __syncthreads();
+  for (int o = 128; o; o >>= 1) {
+    if ((int)threadIdx.x < o) s_sum[threadIdx.x] += s_sum[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double current = s_sum[0] * inv_numel;
+    flags[1] += 1;
+    if (current < state[0]) state[0] = current;
+    else flags[0] = 1;
+  }
+}
+
+__global__ void hqq_state_init_kernel(double* state) {
+  state[0] = 1e4;
+  reinterpret_cast<int*>(state + 1)[0] = 0;
+  reinterpret_cast<int*>(state + 1)[1] = 0;
+}
+
+extern "C" int ao_b200_hqq_solve(const void* w, int64_t n_groups, int group_size, const float* scale, float* zero,
+                                 double beta, double kappa, double lp_norm, int iters, float* err_partial, void* state,
+                                 void* stream) {
+  AO_CHECK_ARG(w && scale && zero && err_partial && state && n_groups > 0 && beta > 0.0 && kappa > 0.0 && iters >= 1);
+  AO_CHECK_ARG(ao_aligned(state, 8));
+  auto s = static_cast<cudaStream_t>(stream);
+  const unsigned grid = (unsigned)ao_b200_hqq_blocks(n_groups);
+  hqq_state_init_kernel<<<1, 1, 0, s>>>(static_cast<double*>(state));  // best = 1e4 (:1956), stop = iterations = 0
+  const double inv_numel = 1.0 / ((double)n_groups * (double)group_size);
+  const float lp_m1 = (float)(lp_norm - 1.0);
+  const int* stop = reinterpret_cast<const int*>(static_cast<const double*>(state) + 1);
+  for (int it = 0; it < iters; ++it) {
+    const float inv_beta = (float)(1.0 / beta);
+    AO_HQQ_DISPATCH(hqq_step_kernel, static_cast<const __nv_bfloat16*>(w), n_groups, scale, zero, inv_beta, lp_m1, err_partial, stop);
+    hqq_judge_kernel<<<1, 256, 0, s>>>(err_partial, (int64_t)grid, inv_numel, static_cast<double*>(state));
+    beta *= kappa;
+  }
   return ao_launch_status();
 }
 

@@ -261,8 +261,8 @@ def _(w: Tensor, group_size: int):
 def _int4_hqq_quantize_cuda(w: Tensor, group_size: int):
     """`_choose_qparams_and_quantize_affine_hqq(w, nbits=4, group_size, axis=1, compute_dtype=bf16, raw_output=False)`
     (quant_primitives.py:1998-2111): q int32 (N, K) in 0..15, scale / zero bf16 (N, K/G) in the tinygemm convention.
-    One kernel per solver iteration; the reference's early stop is a mean over the whole tensor, so the host reads one
-    float per iteration (a one-off cost at quantization time, <= 20 iterations)."""
+    One kernel per solver iteration plus a one-block kernel that applies the reference's global early stop (a mean over
+    the whole tensor) on the device: the launches after the stop return at once, the host never waits."""
     _w_checks(w, group_size)
     w = w.contiguous()
     n, k = w.shape
@@ -277,16 +277,10 @@ def _int4_hqq_quantize_cuda(w: Tensor, group_size: int):
     with torch.cuda.device(w.device):
         st = _stream(w)
         _lib.check(L.ao_b200_hqq_init(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(), st), "hqq_init")
-        beta, best = HQQ_BETA, 1e4
-        for _ in range(HQQ_ITERS):
-            _lib.check(L.ao_b200_hqq_step(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(), beta,
-                                          HQQ_LP_NORM, err.data_ptr(), st), "hqq_step")
-            beta *= HQQ_KAPPA
-            current = float(err.sum(dtype=torch.float64)) / (n * k)
-            if current < best:  # early_stop=True (:1968-1972): the zero of the non-improving iteration is kept
-                best = current
-            else:
-                break
+        # early_stop=True (:1968-1972) is decided on the device: no host round trip per iteration
+        state = torch.empty(2, dtype=torch.float64, device=w.device)
+        _lib.check(L.ao_b200_hqq_solve(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(), HQQ_BETA,
+                                       HQQ_KAPPA, HQQ_LP_NORM, HQQ_ITERS, err.data_ptr(), state.data_ptr(), st), "hqq_solve")
         _lib.check(L.ao_b200_hqq_finalize(w.data_ptr(), n_groups, group_size, scale.data_ptr(), zero.data_ptr(),
                                           q.data_ptr(), scale_out.data_ptr(), zero_out.data_ptr(), st), "hqq_finalize")
     return q, scale_out, zero_out
