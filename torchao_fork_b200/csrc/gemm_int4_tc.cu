@@ -36,7 +36,11 @@
 
 namespace ao {
 
-constexpr int kGmEpiWarps = 4, kGmDqWarps = 16;  // dequant warps: two sets of 8 (one strip each), alternating stages
+#ifndef AO_GM_DQ_SETS
+#define AO_GM_DQ_SETS 2   // 3 sets (960 threads) measured: no gain, the dequant is bound by ALU issue (profiles/r02_gemm_trace.txt)
+#endif
+constexpr int kGmDqSets = AO_GM_DQ_SETS;            // sets of 8 dequant warps (one strip each); set s takes the 64-k tiles s, s + sets, ...
+constexpr int kGmEpiWarps = 4, kGmDqWarps = 8 * kGmDqSets;
 constexpr int kGmProducerWarp = kGmEpiWarps + kGmDqWarps, kGmMmaWarp = kGmProducerWarp + 1;
 constexpr int kGmThreads = (kGmMmaWarp + 1) * 32;  // 704
 constexpr int kGmWSlots = 3, kGmWSlotBytes = 8 * 4 * 512;  // weight ring: 16 KB slices of the 128-row block (256 k of int4, 128 k of int8)
@@ -274,7 +278,7 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
         szn[h][1] = __ldg(szp + (grp + h) * 16 + 8);
       }
     }
-    for (int it = set; it < KT; it += 2) {
+    for (int it = set; it < KT; it += kGmDqSets) {
       const int slot = it % stages;
       uint32_t s2[kGroupsPerTile][2], z2[kGroupsPerTile][2];
       if constexpr (!kI8) {
@@ -285,8 +289,8 @@ __global__ void __launch_bounds__(kGmThreads, 1) int4_gemm_tc_kernel(const GemmT
             s2[h][r] = __byte_perm(szn[h][r], 0, 0x1010);
             z2[h][r] = __byte_perm(szn[h][r], 0, 0x3232);
           }
-        if (it + 2 < KT) {
-          const int64_t grp = GG >= 64 ? (int64_t)(kt_lo + it + 2) * 64 / GG : (int64_t)(kt_lo + it + 2) * kGroupsPerTile;
+        if (it + kGmDqSets < KT) {
+          const int64_t grp = GG >= 64 ? (int64_t)(kt_lo + it + kGmDqSets) * 64 / GG : (int64_t)(kt_lo + it + kGmDqSets) * kGroupsPerTile;
 #pragma unroll
           for (int h = 0; h < kGroupsPerTile; ++h) {
             szn[h][0] = __ldg(szp + (grp + h) * 16);
