@@ -362,6 +362,12 @@ AO_B200_API int64_t ao_b200_decode_mega_state_bytes(void);
 AO_B200_API int ao_b200_decode_mega_setup(const ao_b200_mega_model* m, void* plan_dev, int64_t plan_bytes, void* stream);
 AO_B200_API int ao_b200_decode_mega_step(const ao_b200_mega_model* m, const void* plan_dev, void* stream);
 
+/* Serving-loop plumbing, NO COUNTERPART IN THE REFERENCE: a stream-ordered wait until *flag >= value, `flag` a 32-bit
+ * word in pinned host memory (cuStreamWaitValue32, resolved through the runtime).  The host loop of
+ * _models/llama/generate.py enqueues the next decode step behind such a wait while it reads the current token, and
+ * releases it by storing the token and then the flag.  AO_B200_ERR_UNSUPPORTED when the driver lacks the entry point. */
+AO_B200_API int ao_b200_stream_wait_value32(void* stream, void* flag, uint32_t value);
+
 #ifdef __cplusplus
 }
 #endif

@@ -210,3 +210,26 @@ def test_mega_gqa_group_of_eight_and_odd_layer_count():
     assert eng.mega_status() == 0
     assert _sqnr(ref, eng.logits[0]) > 30.0
 
+
+
+def test_prelaunching_serving_loop_equals_plain_loop():
+    """decode_tokens(stream_to_host=True): the loop that enqueues step i + 1 behind a stream-ordered wait on a pinned flag
+    (generate.py `_decode_prelaunched`, ao_b200_stream_wait_value32) must deliver the tokens of the plain replay + event
+    loop, call after call (the flag keeps counting across calls)."""
+    m = _tiny(128)
+    gen = Generator(m, 1, 96, temperature=0.0, top_k=None, mega=True)
+    assert gen._prelaunch
+    _fill_caches(m, 5)
+    outs = {}
+    for pre in (True, False, True):
+        gen._prelaunch = pre
+        gen.engine.set_state(torch.tensor([3], device="cuda"), 5)
+        a = gen.decode_tokens(20, stream_to_host=True).clone()
+        b = gen.decode_tokens(11, stream_to_host=True).clone()      # a second call continues from the engine's state
+        outs.setdefault(pre, []).append(torch.cat([a, b], dim=1))
+    assert torch.equal(outs[True][0], outs[False][0]) and torch.equal(outs[True][0], outs[True][1])
+    seen = []
+    gen._prelaunch = True
+    gen.engine.set_state(torch.tensor([3], device="cuda"), 5)
+    got = gen.decode_tokens(6, stream_to_host=True, callback=lambda t: seen.append(int(t[0])))
+    assert seen == got[0].tolist() == outs[True][0][0, :6].tolist()

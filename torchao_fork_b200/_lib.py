@@ -71,6 +71,7 @@ SIGNATURES = {
     "ao_b200_decode_attention_fused_q8": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _f32, _i32,
                                           _vp, _i64, _vp],
     "ao_b200_silu_mul": [_vp, _vp, _i64, _i64, _vp],
+    "ao_b200_stream_wait_value32": [_vp, _vp, ctypes.c_uint32],
     "ao_b200_sample": [_vp, _i64, _i64, _i64, _f32, _i32, _vp, _i64, _vp, _vp],
     "ao_b200_tp_buffer_bytes": [_i32, _i64],
     "ao_b200_tp_alloc": [_i64, ctypes.POINTER(ctypes.c_void_p), _vp],

@@ -59,6 +59,9 @@ class Generator:
         self.h_tok = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
         self.h_out = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
         self._done = torch.cuda.Event()
+        self.h_flag = torch.zeros(1, dtype=torch.int32).pin_memory()   # release counter of the pre-launching serving loop
+        import os
+        self._prelaunch = os.environ.get("AO_B200_E2E_PRELAUNCH", "1") != "0"
 
     @torch.no_grad()
     def generate(self, prompt: torch.Tensor, max_new_tokens: int, stream_to_host: bool = False,
@@ -85,6 +88,53 @@ class Generator:
         return seq.to(out_device)
 
 
+    def _decode_prelaunched(self, n: int, out: torch.Tensor, callback) -> torch.Tensor:
+        """The serving loop with the NEXT step's launch hidden behind the current step: step i + 1 is enqueued while the
+        host still waits for token i, behind a stream-ordered wait (ao_b200_stream_wait_value32) on a flag in pinned host
+        memory that the host bumps once it has stored the token to feed; the step's own H2D copy node runs after that
+        wait.  The host learns of a token by watching the pinned result word (a token id is never negative) instead of an
+        event.  Same copies per step as the plain loop (8 B in, 8 B out).  Measured: profiles/r02_e2e_prelaunch.txt."""
+        from ... import _lib
+        eng = self.engine
+        L = _lib.lib()
+        stream = torch.cuda.current_stream(eng.device)
+        sp = stream.cuda_stream
+        h_tok, h_out, o, flag = self.h_tok.numpy(), self.h_out.numpy(), out.numpy(), self.h_flag.numpy()
+        fptr = self.h_flag.data_ptr()
+        seq = int(flag[0])
+        h_out[:] = -1
+
+        def enqueue(i):
+            _lib.check(L.ao_b200_stream_wait_value32(sp, fptr, (seq + i + 1) & 0xFFFFFFFF), "stream_wait_value32")
+            eng.graph_stream.replay()
+
+        try:
+            enqueue(0)
+            flag[0] = seq + 1                      # h_tok already holds the first token to feed
+            for i in range(n):
+                if i + 1 < n:
+                    enqueue(i + 1)
+                spins = 0
+                while h_out.min() < 0:
+                    spins += 1
+                    if spins % 500000 == 0 and stream.query():
+                        if h_out.min() < 0:
+                            raise RuntimeError("decode step finished without delivering a token")
+                callback(self.h_out)
+                o[:, i] = h_out
+                h_tok[:] = h_out
+                h_out[:] = -1
+                flag[0] = seq + i + 2              # releases step i + 1 (if enqueued)
+        except BaseException:
+            flag[0] = seq + n + 2                  # never leave the stream waiting: releases every step that was enqueued
+            stream.synchronize()
+            raise
+        stream.synchronize()
+        if seq + n > 0x3FFFFFFF:                   # the wait compares cyclically ((int32)(*flag - value) >= 0): stay far from the wrap
+            flag[0] = 0
+        eng.check_status()
+        return out
+
     @torch.no_grad()
     def decode_tokens(self, n: int, stream_to_host: bool = False, callback=lambda x: x) -> torch.Tensor:
         """Decode n tokens from the engine's current state (decode_n_tokens, generate.py:120-143) -> int64 [B][n].
@@ -106,6 +156,8 @@ class Generator:
                 h_tok, h_out, o = self.h_tok.numpy(), self.h_out.numpy(), out.numpy()
                 eng._host_pos += n
                 done = self._done
+                if self._prelaunch:
+                    return self._decode_prelaunched(n, out, callback)
                 for i in range(n):
                     eng.graph_stream.replay()
                     # an event recorded behind the graph reaches the host sooner than the stream's own completion

@@ -220,3 +220,31 @@ extern "C" int ao_b200_int8_gemv_fused(const void* x, int64_t M, int64_t Kx, int
   return ao::int8_gemv_fused(x, M, Kx, ldx, packed, scale, Np, Kp, y, N_out, ldy, norm_weight, norm_eps, residual, ld_res,
                              epilogue, tunables().stages, tunables().pdl != 0, static_cast<cudaStream_t>(stream));
 }
+
+
+// ---- serving-loop plumbing (no reference counterpart) ----------------------------------------------------------------
+// Stream-ordered wait on a 32-bit word in pinned host memory: everything enqueued on `stream` after this call starts only
+// once *flag >= value.  Lets a host loop enqueue the NEXT decode step (its launch latency) while it is still reading the
+// current step's token: the step's own input copy runs behind the wait, after the host has stored the token and bumped the
+// flag.  Driver entry point resolved through the runtime (no link dependency on libcuda).
+#include <cuda.h>
+extern "C" int ao_b200_stream_wait_value32(void* stream, void* flag, uint32_t value) {
+  AO_CHECK_ARG(flag != nullptr && ao_aligned(flag, 4));
+  using Fn = CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+  static Fn fn = []() -> Fn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<Fn>(p);
+  }();
+  if (fn == nullptr) return AO_B200_ERR_UNSUPPORTED;
+  void* dptr = nullptr;
+  if (cudaHostGetDevicePointer(&dptr, flag, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return AO_B200_ERR_INVALID_ARG;  // not pinned / mapped host memory
+  }
+  if (fn(static_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(dptr), value, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
+    return AO_B200_ERR_CUDA;
+  return AO_B200_OK;
+}
