@@ -263,3 +263,14 @@ def test_tp_persistent_kernel_matches_tp1():
     for rank, status, sq, same in _run(_mega_worker, timeout=500):
         assert status == "ok", f"rank {rank}:\n{status}"
         print(f"rank {rank}: persistent kernel, logits SQNR tpN vs tp1 {sq:.1f} dB, tokens equal {same:.2f}")
+
+
+@pytest.mark.timeout(600)
+def test_tp_persistent_kernel_reduce_slice_on_a_small_grid(monkeypatch):
+    """The once-per-rank sum of the partial slots (reduce_slice, the world >= 4 default) forced at world 2 on a grid of 8
+    CTAs: each CTA's slice is 16 chunks x 2 ranks, several passes of the (chunk, rank) loop."""
+    monkeypatch.setenv("AO_B200_MEGA_TP_REDUCE", "1")
+    monkeypatch.setenv("AO_B200_MEGA_CTAS", "8")
+    for rank, status, sq, same in _run(_mega_worker, world=2, timeout=500):
+        assert status == "ok", f"rank {rank}:\n{status}"
+        print(f"rank {rank}: persistent kernel (reduce_slice, 8 CTAs), logits SQNR tp2 vs tp1 {sq:.1f} dB")

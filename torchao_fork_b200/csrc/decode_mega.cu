@@ -764,24 +764,28 @@ __device__ __noinline__ void reduce_slice(const uint64_t* in_pk, int n_chunks, u
   const int world = p.world, tid = threadIdx.x;
   const int sh = 31 - __clz(world);
   const int cpc = (n_chunks + p.n_cta - 1) / p.n_cta;
-  if (((tid & ~31) >> sh) >= cpc) return;  // warp-uniform
-  const int j = tid >> sh, r = tid & (world - 1);
-  const int ci = (int)blockIdx.x * cpc + j;
-  const bool on = j < cpc && ci < n_chunks;
-  float f[8];
+  const int r = tid & (world - 1);
+  // (chunk, rank) pairs of this CTA's slice, kCT >> sh chunks per pass (one pass on a full grid: 4 - 7 chunks per CTA);
+  // the trip count is warp-uniform (the butterfly needs whole warps)
+  for (int jb = (tid & ~31) >> sh; jb < cpc; jb += kCT >> sh) {
+    const int j = jb + ((tid & 31) >> sh);
+    const int ci = (int)blockIdx.x * cpc + j;
+    const bool on = j < cpc && ci < n_chunks;
+    float f[8];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) f[e] = 0.f;
-  if (on) unpack8(poll_chunk(in_pk + (size_t)r * (size_t)(n_chunks * 4) + ci * 4, tag_in), f);
-  for (int o = 1; o < world; o <<= 1) {
+    for (int e = 0; e < 8; ++e) f[e] = 0.f;
+    if (on) unpack8(poll_chunk(in_pk + (size_t)r * (size_t)(n_chunks * 4) + ci * 4, tag_in), f);
+    for (int o = 1; o < world; o <<= 1) {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) f[e] += __shfl_xor_sync(0xffffffffu, f[e], o);
-  }
-  if (on && r == 0) {
-    uint64_t* dst = const_cast<uint64_t*>(in_pk) + (size_t)world * (size_t)(n_chunks * 4) + ci * 4;
-    const uint64_t t = (uint64_t)tag_in << 32;
-    const uint64_t a = cvt_bf2(f[0], f[1]) | t, b = cvt_bf2(f[2], f[3]) | t, c = cvt_bf2(f[4], f[5]) | t, d = cvt_bf2(f[6], f[7]) | t;
-    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst), "l"(a), "l"(b) : "memory");
-    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst + 2), "l"(c), "l"(d) : "memory");
+      for (int e = 0; e < 8; ++e) f[e] += __shfl_xor_sync(0xffffffffu, f[e], o);
+    }
+    if (on && r == 0) {
+      uint64_t* dst = const_cast<uint64_t*>(in_pk) + (size_t)world * (size_t)(n_chunks * 4) + ci * 4;
+      const uint64_t t = (uint64_t)tag_in << 32;
+      const uint64_t a = cvt_bf2(f[0], f[1]) | t, b = cvt_bf2(f[2], f[3]) | t, c = cvt_bf2(f[4], f[5]) | t, d = cvt_bf2(f[6], f[7]) | t;
+      asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst), "l"(a), "l"(b) : "memory");
+      asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1,%2};" ::"l"(dst + 2), "l"(c), "l"(d) : "memory");
+    }
   }
 }
 
