@@ -324,8 +324,11 @@ AO_B200_API int ao_b200_tp_allreduce_add(const void* partial, void* h, int64_t n
  *           world > 1 (tensor parallel: wqkv / w13 / output column shards, wo / w2 row shards, n_head / n_kv_head / inter /
  *           vocab are the LOCAL sizes): xchg[r] = rank r's region as mapped into this process (CUDA IPC, like
  *           ao_b200_tp_alloc / ao_b200_tp_open); the wo / w2 partial sums are pushed into every peer's region from the
- *           GEMV epilogue and summed in rank order by the consumers of the next projection — no separate all-reduce
- *           launch.  All ranks must launch the same sequence of steps.
+ *           GEMV epilogue and summed by the consumers of the next projection — at world >= 4 once per rank (its CTAs
+ *           take a slice of the vector each and publish the bf16 sum in a local slot of the region), at world 2 in every
+ *           CTA's sweep — no separate all-reduce launch; every rank adds in the same order, so the replicated residual
+ *           stream is bit-identical on all ranks.  world must be a power of two (<= 8).  All ranks must launch the same
+ *           sequence of steps.
  * ao_b200_decode_mega_step is CUDA-graph-capturable (cooperative kernel node). */
 typedef struct ao_b200_mega_layer {
   const void* wqkv_packed; const void* wqkv_sz;
