@@ -8,7 +8,10 @@ reference`` legs may import it.
 Parity status: PINNED.  ``tests/test_oracle_golden.py`` checks every function
 below bit-for-bit against ``tests/golden/*.npz``, which were produced by the
 reference's own Python functions run on CPU in the build container
-(``tests/golden/make_golden.py``; torch 2.11.0).
+(``tests/golden/make_golden.py``, ``make_golden_hqq.py``, ``make_golden_kvq.py``; torch 2.11.0).
+One exception, marked where it is defined: ``int4_row_quantize_zp`` / ``pack_int4``
+restate a third-party dependency of the reference that is absent here (parity
+with it is unpinned).
 
 Conventions
 -----------
@@ -450,6 +453,59 @@ def hqq_quantize(w, group_size, nbits=4, lp_norm=0.7, beta=10.0, kappa=1.01, ite
     s_inv = (F32(1.0) / scale).astype(F32)
     zero_ao = ((F32(2 ** (nbits - 1)) - zero) * s_inv).astype(F32)
     return q, bf16_round(s_inv).reshape(n, -1), bf16_round(zero_ao).reshape(n, -1)
+
+
+# --------------------------------------------------------------------------
+# int8 KV cache (row N2): per-token symmetric absmax quantizer and the cache update
+# --------------------------------------------------------------------------
+def quantize_activation_per_token_absmax(x, div_mode="ieee"):
+    """reference: torchao/quantization/utils.py:152-182 -> choose_qparams_affine SYMMETRIC (quant_primitives.py:1537-1575)
+    + _quantize_affine_no_dtype_cast (:433-459) with quant_min = -127, quant_max = 127, eps = 1e-5, on bf16 rows
+    (every op rounds to bf16).  x: bf16-valued fp32 [..., D] -> (q int8 [..., D], scale bf16-valued fp32 [...])."""
+    x = np.ascontiguousarray(x, dtype=F32)
+    min_val, max_val = x.min(axis=-1), x.max(axis=-1)
+    max_val_pos = np.maximum(-np.minimum(min_val, F32(0)), np.maximum(max_val, F32(0)))
+    scale = _div_scalar(max_val_pos, 127.0, div_mode)                      # max_val_pos / (float(quant_max - quant_min) / 2)
+    scale = bf16_round(np.maximum(scale, F32(1e-5)))                        # torch.clamp(scale, min=eps), result in bf16
+    recip = bf16_round(F32(1.0) / scale)                                    # 1.0 / scale == scale.reciprocal() * 1.0
+    q = np.rint(bf16_round(x * recip[..., None]))                           # torch.round(input * (1.0 / scale)); zero_point = 0
+    return np.clip(q, -127, 127).astype(np.int8), scale
+
+
+def kv_cache_update(cache, cache_scale, pos, val, div_mode="ieee"):
+    """reference: AffineQuantizedKVCache.update for ONE of k / v (torchao/_models/llama/model.py:215-232): writes the
+    quantized rows and their scales at `pos` (in place) and returns the dequantized cache bf16(q * scale) with the rows at
+    `pos` replaced by the unquantized values.  cache int8 [B][H][S][D], cache_scale bf16-valued fp32 [B][H][S][1],
+    val bf16-valued fp32 [B][H][len(pos)][D]."""
+    q, s = quantize_activation_per_token_absmax(val, div_mode)
+    cache[:, :, pos] = q
+    cache_scale[:, :, pos] = s[..., None]
+    out = bf16_round(cache.astype(F32) * cache_scale)
+    out[:, :, pos] = val
+    return out
+
+
+# --------------------------------------------------------------------------
+# Int4Tensor (row N3): fbgemm-gpu-genai's int4_row_quantize_zp + pack_int4, restated
+# (third-party, absent from /root/reference: fbgemm_gpu/experimental/gen_ai/quantize.py, >= 1.2.0 as required by
+# torchao/quantization/quantize_/workflows/int4/int4_tensor.py:22-26,71-73) -- parity with fbgemm itself is UNPINNED.
+# --------------------------------------------------------------------------
+def int4_row_quantize_zp(w, group_size, div_mode="ieee"):
+    """w bf16-valued fp32 [N][K] -> q int8 [N][K] in [-8, 7], scale / zero fp32 [K/G][N] (fp32 arithmetic throughout;
+    the caller casts scale / zero to the weight's dtype, int4_tensor.py:94-95)."""
+    n, k = w.shape
+    x = np.ascontiguousarray(w, dtype=F32).reshape(-1, group_size)
+    lo, hi = x.min(axis=1, keepdims=True), x.max(axis=1, keepdims=True)
+    rng = np.maximum(hi - lo, F32(1e-6))
+    scale = rng / F32(15) if div_mode == "ieee" else rng * (F32(1) / F32(15))
+    zero = lo + scale * F32(8)
+    q = (np.clip(np.rint((x - lo) / scale), 0, 15) - 8).astype(np.int8).reshape(n, k)
+    return q, scale.reshape(n, -1).T.copy(), zero.reshape(n, -1).T.copy()
+
+
+def pack_int4(q):
+    """int8 [N][K] in [-8, 7] -> int8 [N][K/2]: even k in the low nibble (fbgemm pack_int4)."""
+    return ((q[:, 0::2] & 0xF) | (q[:, 1::2] << 4)).astype(np.int8)
 
 
 def sqnr_db(ref, x):

@@ -20,13 +20,11 @@ def _make(n=32, k=256, g=64, seed=0):
 
 def test_row_quantize_and_pack_follow_the_recipe():
     w, q, t = _make()
-    x = w.float().numpy().reshape(-1, 64)
-    lo, hi = x.min(1, keepdims=True), x.max(1, keepdims=True)
-    scale = np.maximum(hi - lo, np.float32(1e-6)) / np.float32(15)          # CPU: tensor / scalar is a true division
-    zero = lo + scale * np.float32(8)
-    qn = (np.clip(np.rint((x - lo) / scale), 0, 15) - 8).astype(np.int8).reshape(32, 256)
+    import ao_oracle as o
+    qn, scale_t, zero_t = o.int4_row_quantize_zp(w.float().numpy(), 64)      # CPU: tensor / scalar is a true division
+    scale, zero = scale_t.T.reshape(-1, 1), zero_t.T.reshape(-1, 1)
     assert np.array_equal(q.numpy(), qn)
-    assert np.array_equal(t.qdata.numpy(), ((qn[:, 0::2] & 0xF) | (qn[:, 1::2] << 4)).astype(np.int8))
+    assert np.array_equal(t.qdata.numpy(), o.pack_int4(qn))
     assert torch.equal(unpack_int4(t.qdata), q) and int(q.min()) >= -8 and int(q.max()) <= 7
     assert t.scale.shape == (4, 32) and t.zero_point.shape == (4, 32)
     assert torch.equal(t.scale, torch.from_numpy(scale.reshape(32, 4).T.copy()).to(torch.bfloat16))

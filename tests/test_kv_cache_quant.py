@@ -54,3 +54,24 @@ def test_setup_caches_switches_cache_type():
     assert isinstance(m.layers[0].attention.kv_cache, AffineQuantizedKVCache)
     m.setup_caches(1, 8, device="cpu", kv_cache_quantization=True)      # smaller request: kept
     assert m.layers[0].attention.kv_cache.k_cache.shape[2] == 16
+
+
+@pytest.mark.parametrize("path", KVQ, ids=os.path.basename)
+def test_oracle_kv_quantizer_matches_reference_golden(path):
+    """The numpy oracle's restatement (oracle/ao_oracle.py, ieee division = the CPU reference) against the same vectors."""
+    import ao_oracle as o
+    g = np.load(path)
+    k, v = o.from_bits(g["k"]), o.from_bits(g["v"])
+    B, H, T, D = k.shape
+    q, s = o.quantize_activation_per_token_absmax(k)
+    assert np.array_equal(q, g["q_all"]) and np.array_equal(o.to_bits(s), g["s_all"])
+    kc, vc = np.zeros((B, H, T, D), np.int8), np.zeros((B, H, T, D), np.int8)
+    ks, vs = np.ones((B, H, T, 1), np.float32), np.ones((B, H, T, 1), np.float32)
+    k_out = o.kv_cache_update(kc, ks, np.arange(5), k[:, :, :5])
+    v_out = o.kv_cache_update(vc, vs, np.arange(5), v[:, :, :5])
+    for t in range(5, T):
+        k_out = o.kv_cache_update(kc, ks, np.array([t]), k[:, :, t : t + 1])
+        v_out = o.kv_cache_update(vc, vs, np.array([t]), v[:, :, t : t + 1])
+    assert np.array_equal(kc, g["k_cache"]) and np.array_equal(vc, g["v_cache"])
+    assert np.array_equal(o.to_bits(ks), g["k_cache_scale"]) and np.array_equal(o.to_bits(vs), g["v_cache_scale"])
+    assert np.array_equal(o.to_bits(k_out), g["k_out"]) and np.array_equal(o.to_bits(v_out), g["v_out"])
