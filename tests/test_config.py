@@ -82,3 +82,14 @@ def test_rejecting_does_not_run_anything():
             "    print('rejected')\n") % (str(__import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__)))),)
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert "rejected" in out.stdout and "PWNED" not in out.stdout + out.stderr
+
+
+def test_fp8_activation_int4_config_exists_and_says_why_it_is_not_applied():
+    """quant_api.py:1159-1197 is not a weight-only path: the name imports, applying it raises with the reason."""
+    import pytest
+    import torch
+    from torchao_fork_b200.quantization import Float8DynamicActivationInt4WeightConfig, quantize_
+    cfg = Float8DynamicActivationInt4WeightConfig()
+    assert str(getattr(cfg.packing_format, "value", cfg.packing_format)) == "preshuffled"
+    with pytest.raises(NotImplementedError, match="weight-only"):
+        quantize_(torch.nn.Sequential(torch.nn.Linear(128, 128, bias=False)), cfg)

@@ -150,6 +150,22 @@ def _int4_weight_only_transform(module, config):
 
 
 @dataclass
+class Float8DynamicActivationInt4WeightConfig(AOBaseConfig):
+    """reference: quant_api.py:1159-1197 — float8 per-row DYNAMIC ACTIVATION quantization on top of preshuffled int4
+    weights (fbgemm's Int4PreshuffledTensor and its fp8 x int4 kernel).  The config exists so that code naming it imports;
+    applying it raises: it is not a weight-only path (the activations are quantized too), outside SURVEY.md section 8."""
+
+    packing_format: PackingFormat = PackingFormat.PRESHUFFLED
+
+
+@register_quantize_module_handler(Float8DynamicActivationInt4WeightConfig)
+def _float8_dynamic_activation_int4_weight_transform(module, config):
+    raise NotImplementedError(
+        "Float8DynamicActivationInt4WeightConfig quantizes the activations to float8 and needs fbgemm's preshuffled int4 "
+        "kernel; the B200 path is weight-only (bf16 activations): use Int4WeightOnlyConfig(group_size=128[, version=2])")
+
+
+@dataclass
 class Int8WeightOnlyConfig(AOBaseConfig):
     """int8 weight-only symmetric per-channel quantization.  reference: quant_api.py:1200-1216"""
 
