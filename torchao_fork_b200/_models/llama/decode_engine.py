@@ -224,7 +224,7 @@ class DecodeEngine:
             self._setup_mega()
 
     # ------------------------------------------------------------------ one persistent launch per token
-    def _setup_mega(self, attn_blocks_per_cta: int = 0, timeout_ms: int = 2000, trace: bool = False):
+    def _setup_mega(self, attn_blocks_per_cta: int = 0, timeout_ms: int = 0, trace: bool = False):
         import ctypes
         L = _lib.lib()
         dev = self.device
@@ -253,6 +253,10 @@ class DecodeEngine:
             m.n_cta = int(os.environ["AO_B200_MEGA_CTAS"])
         if not attn_blocks_per_cta and os.environ.get("AO_B200_MEGA_ATTN_SPC"):  # tuning knob: 32-position tiles per CTA
             attn_blocks_per_cta = int(os.environ["AO_B200_MEGA_ATTN_SPC"])
+        if not timeout_ms:
+            # bound of every wait inside the kernel.  Tensor parallel: the ranks' launches are only loosely aligned (a busy
+            # host on one rank delays its launch), so the bound is generous there; AO_B200_MEGA_TIMEOUT_MS overrides
+            timeout_ms = int(os.environ.get("AO_B200_MEGA_TIMEOUT_MS", "10000" if tp is not None else "2000"))
         m.timeout_ms, m.attn_blocks_per_cta = timeout_ms, attn_blocks_per_cta
         m.eps = self.eps
         m.layers = ctypes.cast(arr, ctypes.POINTER(_lib.MegaLayer))
