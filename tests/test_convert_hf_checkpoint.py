@@ -91,3 +91,20 @@ def test_checkpoint_directory_converts_into_the_models_state_dict(tmp_path):
         raise AssertionError("unknown tensor accepted")
     except KeyError:
         pass
+
+
+def test_every_reference_model_name_resolves():
+    """torchao/_models/llama/model.py:75-158: the names generate.py / eval.py / the converter look up from a checkpoint path."""
+    want = {"CodeLlama-7b-Python-hf": (32, 4096, 32, 32, 128), "7B": (32, 4096, 32, 32, 128), "13B": (40, 5120, 40, 40, 128),
+            "30B": (60, 6656, 52, 52, 128), "34B": (48, 8192, 64, 8, 128), "70B": (80, 8192, 64, 8, 128),
+            "Mistral-7B": (32, 4096, 32, 8, 128), "stories15M": (6, 288, 6, 6, 48), "stories110M": (12, 768, 12, 12, 64),
+            "Llama-3-8B": (32, 4096, 32, 8, 128), "Llama-3.1-8B": (32, 4096, 32, 8, 128), "Llama-3.1-70B": (80, 8192, 64, 8, 128),
+            "Llama-3.1-405B": (126, 16384, 128, 8, 128), "Llama-3.2-3B": (28, 3072, 24, 8, 128)}
+    for name, (nl, dim, h, hkv, hd) in want.items():
+        c = ModelArgs.from_name(name)
+        assert (c.n_layer, c.dim, c.n_head, c.n_local_heads, c.head_dim) == (nl, dim, h, hkv, hd), name
+    # a checkpoint path resolves to the longest matching name (generate.py:247 `Transformer.from_name(checkpoint_path)`)
+    assert ModelArgs.from_name("checkpoints/meta-llama/Meta-Llama-3.1-70B/model.pth").use_scaled_rope
+    assert ModelArgs.from_name("checkpoints/meta-llama/Llama-3.2-3B/model.pth").tie_word_embeddings
+    assert ModelArgs.from_name("Llama-3.1-405B").intermediate_size == 53248
+    assert ModelArgs.from_name("7B").intermediate_size == 11008      # find_multiple(2 * 4 * dim / 3, 256)

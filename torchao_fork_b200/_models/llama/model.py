@@ -55,8 +55,12 @@ _L3 = dict(n_local_heads=8, vocab_size=128256, rope_base=500000)
 # reference: model.py:75-158.  "Llama-3-70B" is the harness's addition: the reference only
 # has "70B" (Llama-2 vocab) and "Llama-3.1-70B" (scaled rope); BASELINE.json config 4 names Llama-3-70B.
 transformer_configs = {
+    "CodeLlama-7b-Python-hf": dict(block_size=16384, vocab_size=32000, n_layer=32, dim=4096, rope_base=1000000),
     "7B": dict(n_layer=32, n_head=32, dim=4096),
     "13B": dict(n_layer=40, n_head=40, dim=5120),
+    "30B": dict(n_layer=60, n_head=52, dim=6656),
+    "34B": dict(n_layer=48, n_head=64, dim=8192, vocab_size=32000, n_local_heads=8, intermediate_size=22016,
+                rope_base=1000000),  # CodeLlama-34B-Python-hf
     "70B": dict(n_layer=80, n_head=64, dim=8192, n_local_heads=8, intermediate_size=28672),
     "Mistral-7B": dict(n_layer=32, n_head=32, n_local_heads=8, dim=4096, intermediate_size=14336, vocab_size=32000),
     "stories15M": dict(n_layer=6, n_head=6, dim=288),
@@ -67,6 +71,10 @@ transformer_configs = {
     "Llama-3-70B": dict(block_size=8192, n_layer=80, n_head=64, dim=8192, intermediate_size=28672, **_L3),
     "Llama-3.1-70B": dict(block_size=131072, n_layer=80, n_head=64, dim=8192, intermediate_size=28672,
                           use_scaled_rope=True, **_L3),
+    "Llama-3.1-405B": dict(block_size=131072, n_layer=126, n_head=128, dim=16384, intermediate_size=53248,
+                           use_scaled_rope=True, **_L3),
+    "Llama-3.2-3B": dict(block_size=131072, n_layer=28, n_head=24, dim=3072, intermediate_size=8192, use_scaled_rope=True,
+                         tie_word_embeddings=True, **_L3),
     # small shapes with head_dim 128 for tests (not in the reference)
     "tiny-llama3": dict(block_size=256, n_layer=2, n_head=8, n_local_heads=2, dim=1024, intermediate_size=2048,
                         vocab_size=1024, rope_base=500000),
