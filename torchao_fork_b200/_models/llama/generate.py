@@ -263,7 +263,7 @@ def main(prefill_size: Optional[int] = None, prompt="Hello, my name is", num_sam
          save: bool = False, device="cuda", precision=torch.bfloat16, write_result=None):
     """reference: generate.py:258-1115 (`main`), the arguments that exist on this path.  `--compile` has no counterpart:
     decode always runs the captured graph / persistent kernel.  The prompt is token ids (comma separated) unless a
-    sentencepiece `tokenizer.model` sits next to the checkpoint."""
+    `tokenizer.model` (sentencepiece, or tiktoken BPE for Llama-3 names) sits next to the checkpoint."""
     import os
     import time
     from datetime import datetime
@@ -277,8 +277,8 @@ def main(prefill_size: Optional[int] = None, prompt="Hello, my name is", num_sam
         model = _load_model(checkpoint_path, device, precision)
         tok_path = checkpoint_path.parent / "tokenizer.model"
         if tok_path.is_file():
-            import sentencepiece as spm
-            tokenizer = spm.SentencePieceProcessor(model_file=str(tok_path))
+            from .tokenizer import get_tokenizer
+            tokenizer = get_tokenizer(tok_path, checkpoint_path)  # generate.py:314 — the path carries the model name
     else:
         model = _random_init_model(random_init, device, precision)
     torch.cuda.synchronize()
