@@ -33,41 +33,39 @@ def llama3_special_tokens(num_base_tokens: int) -> Dict[str, int]:
 
 
 class TokenizerInterface:
+    """What generate / eval call.  Subclasses set the `_enc` / `_dec` callables and the two ids;
+    a bare instance raises, as the reference's abstract base does."""
+
     def __init__(self, model_path):
         self.model_path = model_path
+        self._enc = self._dec = None
+        self.bos_token_id = self.eos_token_id = None
+
+    def _need(self, what):
+        if what is None:
+            raise NotImplementedError("This method should be overridden by subclasses.")
+        return what
 
     def encode(self, text: str) -> List[int]:
-        raise NotImplementedError("This method should be overridden by subclasses.")
+        return self._need(self._enc)(text)
 
     def decode(self, tokens: List[int]) -> str:
-        raise NotImplementedError("This method should be overridden by subclasses.")
+        return self._need(self._dec)(tokens)
 
     def bos_id(self) -> int:
-        raise NotImplementedError("This method should be overridden by subclasses.")
+        return self._need(self.bos_token_id)
 
     def eos_id(self) -> int:
-        raise NotImplementedError("This method should be overridden by subclasses.")
+        return self._need(self.eos_token_id)
 
 
 class SentencePieceWrapper(TokenizerInterface):
     def __init__(self, model_path):
         from sentencepiece import SentencePieceProcessor
         super().__init__(model_path)
-        self.processor = SentencePieceProcessor(str(model_path))
-        self.bos_token_id = self.bos_id()
-        self.eos_token_id = self.eos_id()
-
-    def encode(self, text):
-        return self.processor.EncodeAsIds(text)
-
-    def decode(self, tokens):
-        return self.processor.DecodeIds(tokens)
-
-    def bos_id(self):
-        return self.processor.bos_id()
-
-    def eos_id(self):
-        return self.processor.eos_id()
+        self.processor = sp = SentencePieceProcessor(str(model_path))
+        self._enc, self._dec = sp.EncodeAsIds, sp.DecodeIds
+        self.bos_token_id, self.eos_token_id = sp.bos_id(), sp.eos_id()
 
 
 class TiktokenWrapper(TokenizerInterface):
@@ -81,20 +79,9 @@ class TiktokenWrapper(TokenizerInterface):
         self.special_tokens = llama3_special_tokens(len(ranks))
         self.model = tiktoken.Encoding(name=Path(model_path).name, pat_str=_LLAMA3_SPLIT, mergeable_ranks=ranks,
                                        special_tokens=self.special_tokens)
+        self._enc, self._dec = self.model.encode, self.model.decode  # encode: specials in the text are an error, as upstream
         self.bos_token_id = self.special_tokens["<|begin_of_text|>"]
         self.eos_token_id = self.special_tokens["<|end_of_text|>"]
-
-    def encode(self, text):
-        return self.model.encode(text)
-
-    def decode(self, tokens):
-        return self.model.decode(tokens)
-
-    def bos_id(self):
-        return self.bos_token_id
-
-    def eos_id(self):
-        return self.eos_token_id
 
 
 def get_tokenizer(tokenizer_model_path, model_name) -> TokenizerInterface:
