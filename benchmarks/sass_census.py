@@ -5,6 +5,9 @@ SASS mnemonics that identify the hardware paths (B200_PROFILING.md "What proves 
     UTMALDG / UTMASTG  tensor-map TMA      SYNCS  mbarrier      HMMA / IMMA  mma.sync (legacy tensor path)
     LDSM  ldmatrix      MOVM  movmatrix      LDGSTS  cp.async
 
+The last four columns are the kernel's static resources (`cuobjdump --dump-resource-usage`): registers per thread, stack
+and local bytes per thread (local > 0 = spills or indexed private arrays), static shared bytes.
+
     python benchmarks/sass_census.py [lib] > profiles/r02_sass_census.txt
 """
 import collections
@@ -36,13 +39,21 @@ for line in out.split("\n"):
     for name, pat in PATTERNS:
         if re.search(pat, line):
             counts[cur][name] += 1
+res = {}
+ru = subprocess.run(["cuobjdump", "--dump-resource-usage", lib], capture_output=True, text=True).stdout.split("\n")
+for i, line in enumerate(ru):
+    m = re.search(r"Function (\S+):", line)
+    if m and i + 1 < len(ru):
+        res[m.group(1)] = {k: int(v) for k, v in re.findall(r"\b(REG|STACK|SHARED|LOCAL):(\d+)", ru[i + 1])}
 cols = [n for n, _ in PATTERNS]
+rcols = ["REG", "STACK", "LOCAL", "SHARED"]
 print(f"# SASS census of {os.path.relpath(lib, ROOT)} (cuobjdump -sass, sm_100a); one row per kernel")
-print("  ".join(f"{c:>7s}" for c in cols) + "  kernel")
+print("  ".join(f"{c:>7s}" for c in cols + rcols) + "  kernel")
 tot = collections.Counter()
 for fn, c in counts.items():
     tot.update(c)
     short = re.sub(r"\(.*", "", demangle.get(fn, fn))
     short = re.sub(r"^void ", "", short)
-    print("  ".join(f"{c[k]:7d}" for k in cols) + "  " + short)
+    r = res.get(fn, {})
+    print("  ".join([f"{c[k]:7d}" for k in cols] + [f"{r.get(k, -1):7d}" for k in rcols]) + "  " + short)
 print("  ".join(f"{tot[k]:7d}" for k in cols) + "  TOTAL")
